@@ -1,0 +1,354 @@
+"""Round engine: selection -> local training -> election -> merge -> broadcast/verify -> evaluate.
+
+This is the framework's equivalent of the reference's top-level round loop
+(``src/main.py:267-365``) and of the peer protocol methods of ``ClientTrainer``
+(``src/Trainer/client_trainer.py:249-335``), restructured so that the host
+touches the device O(1) times per round instead of O(clients x steps x ops):
+
+* the host decides only what needs no device data: which clients are selected
+  (python RNG, ``src/main.py:270-271``), which selected client is the effective
+  voter (a function of the aggregation quotas alone) and the tie-break jitter
+  draws (``client_trainer.py:243-245``);
+* everything else -- local training of all selected clients, vote scoring, the
+  argmin election with quota, merge weights, the weighted parameter reduction,
+  the verification gate for every client and the evaluation of every client --
+  runs on the device through ``ops.backend`` and is read back once per round.
+
+Two aggregation modes: ``elected`` (the reference's algorithm: one peer-elected
+aggregator per round, result broadcast to *all* clients and gated by each
+client's verifier) and ``gossip`` (every selected client merges its topology
+neighbours' models weighted by their MSE on its own validation data -- the
+all-to-all API the reference defines but never calls, quirk Q21).
+"""
+from __future__ import annotations
+
+import logging
+import random
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from ..config import ExperimentConfig
+from ..data.shards import ShardStore
+from ..layout import ParamLayout
+from ..models import init_packed_models
+from ..ops.backend import MergeSpec, OracleBackend, RoundControl
+from ..ops.oracle import TrainHP
+from ..parallel import Comm, topology
+from ..utils import artefacts
+from ..utils.timers import PhaseTimer
+from .state import FederationState
+
+log = logging.getLogger(__name__)
+
+
+@dataclass
+class RoundResult:
+    round: int
+    selected: List[int]
+    aggregator: int                        # global client id, -1 = no aggregation
+    client_metrics: List[float]            # all global clients
+    verification: List[Dict]               # [{'client_id','rejected_updates','is_verified'}]
+    epochs_run: Dict[int, int]             # global id -> epochs of this round's local training
+    samples: int = 0                       # local training rows processed (train+valid) x epochs
+
+
+class GlobalStop:
+    """The reference's global early stop (``src/main.py:55-57``, ``:358-365``).
+
+    "loss" is ``min(client_metrics)``, i.e. the worst client's AUC, and *lower is
+    better*; the counters are module globals that are never reset between
+    combinations (quirk Q2).  ``reference_compat`` keeps one instance for the whole
+    sweep; otherwise the runner makes a fresh one per combination.
+    """
+
+    def __init__(self, patience: int = 1):
+        self.patience = patience
+        self.min_val_loss = float("inf")
+        self.worse = 0
+
+    def update(self, client_metrics: Sequence[float]) -> bool:
+        cur = min(client_metrics)
+        if cur < self.min_val_loss:
+            self.min_val_loss, self.worse = cur, 0
+            return False
+        self.worse += 1
+        return self.worse > self.patience
+
+
+def make_backend(name: str, layout: ParamLayout, device: torch.device):
+    if name == "auto":
+        name = "cuda" if device.type == "cuda" else "oracle"
+    if name == "oracle":
+        return OracleBackend(layout, device)
+    if name == "cuda":
+        from ..ops.cuda_backend import CudaBackend
+        return CudaBackend(layout, device)
+    raise ValueError(f"unknown backend {name!r}")
+
+
+class FederationEngine:
+    def __init__(self, cfg: ExperimentConfig, shards: ShardStore, model_type: str, update_type: str,
+                 run: int = 0, comm: Optional[Comm] = None, backend=None,
+                 init_params: Optional[torch.Tensor] = None, names_global: Optional[List[str]] = None):
+        self.cfg, self.sh, self.model_type, self.update_type, self.run = cfg, shards, model_type, update_type, run
+        self.comm = comm or Comm(device=shards.device)
+        self.layout = ParamLayout(cfg.dim_features, cfg.hidden_neus, cfg.latent_dim)
+        self.N = shards.n_global
+        self.first, self.n_local = shards.first_client, shards.n_clients
+        self.names_global = names_global or list(shards.names)
+        dev = shards.device
+        if init_params is None:
+            # same RNG order as the reference: one module per client on the global torch generator
+            init_params = init_packed_models(self.N, model_type, self.layout, cfg.shrink_lambda)
+        self.backend = backend if backend is not None and not isinstance(backend, str) else \
+            make_backend(backend or cfg.backend, self.layout, dev)
+        storage = None
+        if hasattr(self.backend, "alloc_param_slab"):
+            storage = self.backend.alloc_param_slab(self.n_local, self.layout.padded, self.comm)
+        self.state = FederationState.create(
+            init_params[self.first:self.first + self.n_local], self.layout, cfg.epoch, dev,
+            params_storage=storage, n_global=self.N)
+        self.hp = TrainHP(
+            epochs=cfg.epoch, batch_size=cfg.batch_size, lr=cfg.lr_rate,
+            shrink_lambda=float(cfg.shrink_lambda) if model_type == "hybrid" else 0.0,
+            fedprox_mu=cfg.fedprox_mu if update_type == "fedprox" else 0.0,
+            patience=cfg.local_patience)
+        self.spec = MergeSpec(
+            update_type=update_type,
+            compat_alias=cfg.reference_compat and update_type == "mse_avg",
+            vote_chunk=cfg.vote_chunk, max_aggregations=cfg.max_aggregation_threshold,
+            verification_threshold=cfg.verification_threshold,
+            performance_threshold=cfg.performance_threshold,
+            verification_method=cfg.verification_method)
+        self.agg_count_host = [0] * self.N
+        self.timer = PhaseTimer(enabled=True, cuda=dev.type == "cuda")
+        self.latents: Dict[int, Dict[str, Tuple[np.ndarray, np.ndarray]]] = {}
+        self.last_metrics: Optional[List[float]] = None
+        self.history: List[RoundResult] = []
+        self._neigh_cache = None
+        if hasattr(self.backend, "bind"):
+            self.backend.bind(self.state, self.sh, self.comm, self.hp, self.spec, model_type)
+
+    # ------------------------------------------------------------------ control (host RNG)
+    def make_control(self, round_idx: int) -> RoundControl:
+        cfg = self.cfg
+        n_sel = max(1, int(cfg.num_participants * self.N))
+        sel = random.sample(range(self.N), n_sel)
+        quota = cfg.max_aggregation_threshold
+        voter_pos, jitter = -1, [1.0] * n_sel
+        for k in range(n_sel):
+            draws = [1.0 + (torch.rand(1).item() - 0.5) * 0.0002 for _ in range(n_sel - 1)]
+            if any(self.agg_count_host[g] < quota for p, g in enumerate(sel) if p != k):
+                voter_pos = k
+                it = iter(draws)
+                jitter = [1.0 if p == k else next(it) for p in range(n_sel)]
+                break
+        if voter_pos >= 0 and self.update_type == "mse_avg":
+            for _ in range(n_sel):          # quirk Q7: aggregate_models draws once per client
+                torch.rand(1)
+        verify_client = self.N - 1 if (cfg.reference_compat and cfg.verification_method == "val") else -1
+        return RoundControl(round=round_idx, sel=sel, voter_pos=voter_pos, jitter=jitter,
+                            vote_client=sel[0], verify_client=verify_client)
+
+    def _sel_local(self, sel: Sequence[int]) -> List[int]:
+        return [g - self.first for g in sel if self.first <= g < self.first + self.n_local]
+
+    # ------------------------------------------------------------------ one round
+    def run_round(self, round_idx: int, ctl: Optional[RoundControl] = None,
+                  evaluate: bool = True, want_latents: Optional[bool] = None) -> RoundResult:
+        if self.cfg.aggregation == "gossip":
+            return self._run_round_gossip(round_idx, ctl, evaluate, want_latents)
+        be, st, sh, cm, tm = self.backend, self.state, self.sh, self.comm, self.timer
+        ctl = ctl or self.make_control(round_idx)
+        if hasattr(be, "begin_round"):
+            be.begin_round(ctl)
+        with tm.phase("train"):
+            be.train(st, sh, self._sel_local(ctl.sel), self.hp)
+        agg_pos = None
+        if ctl.voter_pos >= 0:
+            with tm.phase("vote"):
+                scores = cm.sum_(be.vote_scores(st, sh, ctl, self.spec))
+                agg_pos = be.elect(st, scores, ctl, self.spec)
+            with tm.phase("merge"):
+                mse = None
+                if self.update_type == "mse_avg":
+                    mse = cm.sum_(be.merge_scores(st, sh, ctl))
+                rows = None
+                if cm.is_dist and not getattr(be, "reads_peers", False):
+                    rows = cm.gather_rows(st.params, ctl.sel, self.first)
+                theta = be.merge(st, sh, ctl, self.spec, mse, agg_pos, rows)
+            with tm.phase("verify"):
+                be.verify_update(st, sh, ctl, self.spec, theta, agg_pos)
+        return self._finish_round(ctl, agg_pos, evaluate, want_latents)
+
+    def _finish_round(self, ctl: RoundControl, agg_pos, evaluate: bool,
+                      want_latents: Optional[bool]) -> RoundResult:
+        be, st, sh, cm, tm, cfg = self.backend, self.state, self.sh, self.comm, self.timer, self.cfg
+        if want_latents is None:
+            want_latents = cfg.write_latents and self.model_type == "hybrid"
+        metrics: List[float] = []
+        lat = None
+        if evaluate:
+            with tm.phase("evaluate"):
+                auc_dev, auc64, lat = be.evaluate(st, sh, self.model_type, want_latents, cfg.metric)
+        # ---- single readback of the round's results --------------------------------
+        a = int(agg_pos.item()) if agg_pos is not None else -1
+        aggregator = ctl.sel[a] if a >= 0 else -1
+        if aggregator >= 0:
+            self.agg_count_host[aggregator] += 1
+        epochs_local = st.epochs_run.tolist()
+        rejected_local = st.rejected.tolist()
+        if evaluate:
+            if auc64 is None:
+                auc64 = [float(x) for x in auc_dev.tolist()]
+            metrics = self._gather_list(auc64)
+        rejected = self._gather_list(rejected_local)
+        epochs_all = self._gather_list(epochs_local)
+        verification = []
+        if aggregator >= 0:
+            for g in range(self.N):
+                if g != aggregator:
+                    verification.append({"client_id": g, "rejected_updates": int(rejected[g]),
+                                         "is_verified": int(rejected[g]) == 0})
+        ep = {g: int(epochs_all[g]) for g in ctl.sel}
+        samples = 0
+        for g in self._sel_global_local(ctl.sel):
+            c = g - self.first
+            samples += ep[g] * (sh.train.count(c) + sh.valid.count(g))
+        if want_latents and lat is not None:
+            self._stash_latents(ctl.round, lat)
+        res = RoundResult(ctl.round, list(ctl.sel), aggregator, metrics, verification, ep, samples)
+        if evaluate:
+            self.last_metrics = metrics
+        self.history.append(res)
+        return res
+
+    def _sel_global_local(self, sel):
+        return [g for g in sel if self.first <= g < self.first + self.n_local]
+
+    def _gather_list(self, local: Sequence) -> List:
+        if not self.comm.is_dist:
+            return list(local)
+        parts = self.comm.all_gather_object(list(local))
+        out: List = []
+        for p in parts:
+            out.extend(p)
+        return out
+
+    def _stash_latents(self, round_idx: int, lat: List[np.ndarray]) -> None:
+        labels = [self.sh.test.labels(c).detach().cpu().numpy().astype("float32")
+                  for c in range(self.n_local)]
+        local = {self.sh.names[c]: (lat[c], labels[c]) for c in range(self.n_local)}
+        merged: Dict[str, Tuple[np.ndarray, np.ndarray]] = {}
+        for part in self.comm.all_gather_object(local):
+            merged.update(part)
+        self.latents[round_idx] = merged
+
+    # ------------------------------------------------------------------ gossip round
+    def neighbours(self, round_idx: int) -> List[List[int]]:
+        cfg = self.cfg
+        if cfg.topology.startswith("random") or self._neigh_cache is None:
+            self._neigh_cache = topology.build(cfg.topology, self.N, cfg.topology_k,
+                                               cfg.topology_seed, round_idx)
+        return self._neigh_cache
+
+    def _run_round_gossip(self, round_idx, ctl, evaluate, want_latents) -> RoundResult:
+        be, st, sh, cm, tm = self.backend, self.state, self.sh, self.comm, self.timer
+        if ctl is None:
+            n_sel = max(1, int(self.cfg.num_participants * self.N))
+            sel = random.sample(range(self.N), n_sel)
+            ctl = RoundControl(round_idx, sel, -1, [1.0] * n_sel, sel[0], -1)
+        if hasattr(be, "begin_round"):
+            be.begin_round(ctl)
+        with tm.phase("train"):
+            be.train(st, sh, self._sel_local(ctl.sel), self.hp)
+        with tm.phase("gossip"):
+            neigh = self.neighbours(round_idx)
+            be_gossip = getattr(be, "gossip", None)
+            if be_gossip is None:
+                raise RuntimeError(f"backend {be.name} has no gossip op")
+            rows = None
+            if cm.is_dist and not getattr(be, "reads_peers", False):
+                rows = cm.gather_rows(st.params, list(range(self.N)), self.first)
+            be_gossip(st, sh, ctl, self.spec, neigh, rows)
+        return self._finish_round(ctl, None, evaluate, want_latents)
+
+    # ------------------------------------------------------------------ full experiment for one combination
+    def fit(self, stop: Optional[GlobalStop] = None, write: bool = True) -> List[RoundResult]:
+        cfg = self.cfg
+        stop = stop or GlobalStop(cfg.global_patience)
+        root = cfg.output_root
+        res_file = artefacts.results_file(root, cfg.network_size, cfg.no_Exp, self.run, cfg.metric,
+                                          cfg.scen_name, cfg.num_participants, self.model_type,
+                                          self.update_type)
+        ver_file = f"{root}/{cfg.checkpoint_dir}/Run_{self.run}/verification_results.json"
+        out = []
+        for r in range(cfg.num_rounds):
+            log.info("Starting round %d/%d", r + 1, cfg.num_rounds)
+            res = self.run_round(r)
+            out.append(res)
+            if res.aggregator >= 0:
+                log.info("Client %d selected as aggregator", res.aggregator + 1)
+            else:
+                log.warning("No aggregator selected for this round")
+            for i, m in enumerate(res.client_metrics):
+                log.info("Client %d %s score: %s", i + 1, cfg.metric, m)
+            if write:
+                if cfg.save_client_models:
+                    self.save_client_models(res)
+                if self.comm.rank == 0:
+                    if res.aggregator >= 0:
+                        artefacts.append_verification(ver_file, r + 1, res.verification)
+                    artefacts.append_round_metrics(res_file, r + 1, res.client_metrics,
+                                                   self.update_type, self.model_type)
+            if stop.update(res.client_metrics):
+                log.info("Early stopping in global round!")
+                break
+        if write and self.comm.rank == 0 and self.latents:
+            artefacts.write_latents(
+                artefacts.latent_file(root, cfg.network_size, cfg.no_Exp, self.run, self.model_type,
+                                      self.update_type), self.latents)
+        return out
+
+    def final_best(self) -> float:
+        """Max client metric after the last round (``src/main.py:368-374``, quirk Q18)."""
+        if self.last_metrics is None:
+            _, auc64, _ = self.backend.evaluate(self.state, self.sh, self.model_type, False, self.cfg.metric)
+            self.last_metrics = self._gather_list(auc64)
+        return max(self.last_metrics)
+
+    def save_client_models(self, res: RoundResult) -> None:
+        """Write ``model.cpt`` (best-validation weights of this round's run) and
+        ``training_tracking.pkl`` for every locally-owned client that trained."""
+        cfg, st = self.cfg, self.state
+        sel_local = self._sel_local(res.selected)
+        if not sel_local:
+            return
+        idx = torch.tensor(sel_local, dtype=torch.long, device=st.device)
+        best = st.best[idx].cpu()
+        logs = st.loss_log[idx].cpu()
+        for k, c in enumerate(sel_local):
+            g = self.first + c
+            d = artefacts.client_model_dir(cfg.output_root, cfg.network_size, cfg.no_Exp, self.run,
+                                           cfg.scen_name, self.model_type, self.update_type,
+                                           self.names_global[g])
+            artefacts.save_client_model(d, self.layout.unpack(best[k]))
+            n = res.epochs_run.get(g, 0)
+            artefacts.save_tracking(d, [(float(logs[k, e, 0]), float(logs[k, e, 1])) for e in range(n)])
+
+    # ------------------------------------------------------------------ resume (absent in the reference)
+    def snapshot(self) -> Dict:
+        return {"state": self.state.state_dict(), "agg_count_host": list(self.agg_count_host),
+                "py_random": random.getstate(), "np_random": np.random.get_state(),
+                "torch_random": torch.get_rng_state(), "rounds_done": len(self.history),
+                "model_type": self.model_type, "update_type": self.update_type, "run": self.run}
+
+    def restore(self, snap: Dict) -> None:
+        self.state.load_state_dict(snap["state"])
+        self.agg_count_host = list(snap["agg_count_host"])
+        random.setstate(snap["py_random"])
+        np.random.set_state(snap["np_random"])
+        torch.set_rng_state(snap["torch_random"])
