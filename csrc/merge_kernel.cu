@@ -1,0 +1,183 @@
+// T2 merge / election / T3 verification gate.
+//
+// Reference: election src/Trainer/client_trainer.py:262-285 (+ src/main.py:284-288); merge rules
+// :107-134; verification src/Trainer/model_verifier.py:29-99 and client_trainer.py:174-206.
+//
+// The merge kernel turns MSE scores into normalised weights and performs the weighted parameter
+// reduction in one launch.  Every selected model is read straight from its owner's parameter slab
+// through a table of peer-mapped base pointers: for models owned by another GPU these are plain
+// ld.global on NVLink-mapped addresses (P2P over NVSwitch), so no all-gather, staging buffer or
+// separate elementwise kernel exists on this path.  Each rank computes the full reduction for itself
+// (an all-reduce by pull), which also *is* the broadcast of the aggregated model.
+#include "common.cuh"
+#include "../include/fedmse_b200.h"
+
+namespace fm {
+
+__device__ __forceinline__ void owner_of(int g, int n_global, int world, int& rank, int& local) {
+    const int base = n_global / world, rem = n_global - base * world;
+    const int cut = rem * (base + 1);
+    if (g < cut) { rank = g / (base + 1); local = g - rank * (base + 1); }
+    else { const int q = (g - cut) / base; rank = rem + q; local = (g - cut) - q * base; }
+}
+
+__global__ void elect_kernel(const float* __restrict__ scores, const int* __restrict__ sel, int n_sel, int voter_pos,
+                             const int* __restrict__ agg_count, int max_agg, int* __restrict__ agg_pos) {
+    // single warp: lexicographic (score, position) argmin over eligible candidates
+    const int lane = threadIdx.x;
+    float best = __int_as_float(0x7f800000);
+    int bpos = 0x7fffffff;
+    if (voter_pos >= 0) {
+        for (int p = lane; p < n_sel; p += 32) {
+            if (p == voter_pos || agg_count[sel[p]] >= max_agg) continue;
+            float s = scores[p];
+            if (s != s) s = __int_as_float(0x7f800000);
+            if (s < best || (s == best && p < bpos)) { best = s; bpos = p; }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int op = __shfl_xor_sync(0xffffffffu, bpos, o);
+        if (ob < best || (ob == best && op < bpos)) { best = ob; bpos = op; }
+    }
+    if (lane == 0) {
+        const bool ok = bpos != 0x7fffffff;
+        agg_pos[0] = ok ? bpos : -1;
+        agg_pos[1] = ok ? sel[bpos] : -1;
+    }
+}
+
+constexpr int MNT = 256;
+
+__global__ void __launch_bounds__(MNT) merge_kernel(const FmMergeArgs a) {
+    extern __shared__ float wts[];            // [n_sel]
+    __shared__ double red[34];
+    const int ap = a.agg_pos[0];
+    if (ap < 0) return;
+    const int tid = threadIdx.x, n = a.n_sel;
+    // ---- weights (every CTA recomputes them: n_sel is small) ----
+    if (a.mode == 0) {
+        for (int k = tid; k < n; k += MNT) wts[k] = 1.f / (float)n;
+        __syncthreads();
+    } else {
+        double part = 0.0;
+        for (int k = tid; k < n; k += MNT) {
+            int src = k;
+            if (a.compat && n > 1 && k == ap && ap > 0) src = ap - 1;   // scored while holding model ap-1
+            const float s = 1.f / a.mse[src];
+            wts[k] = s;
+            part += (double)s;
+        }
+        const double tot = block_sum<double>(part, red);
+        for (int k = tid; k < n; k += MNT) wts[k] = (float)((double)wts[k] / tot);
+        __syncthreads();
+        if (a.compat && n > 1 && tid == 0) {                            // aggregator's slot aliases the last-loaded peer
+            const int last = (ap != n - 1) ? n - 1 : n - 2;
+            const float moved = wts[ap];
+            wts[ap] = 0.f;
+            wts[last] += moved;
+        }
+        __syncthreads();
+    }
+    if (a.weights_out && blockIdx.x == 0)
+        for (int k = tid; k < n; k += MNT) a.weights_out[k] = wts[k];
+    // ---- weighted reduction, one parameter per thread, models pulled from their owners ----
+    const int p = blockIdx.x * MNT + tid;
+    if (p < P_PAD) {
+        float acc = 0.f;
+        if (p < NP) {
+            for (int k = 0; k < n; ++k) {
+                const float wk = wts[k];
+                if (wk == 0.f) continue;
+                int r, l;
+                owner_of(a.sel[k], a.n_global, a.world, r, l);
+                const float* src = a.peer_slabs[r] + (size_t)l * P_PAD;
+                acc = fmaf(wk, src[p], acc);
+            }
+        }
+        a.theta[p] = acc;
+    }
+    if (blockIdx.x == 0 && tid == 0) a.agg_count[a.sel[ap]] += 1;
+}
+
+constexpr int VNT = 256;
+
+__device__ __forceinline__ void verify_decide_and_apply(float* params_c, float* anchor_c, float* hist_c, float* hist_perf,
+                                                         int* hist_valid, int* rejected, int c, const float* theta,
+                                                         float perf, float thr_change, float thr_perf, double* red,
+                                                         float* out_change, float* out_dperf) {
+    const int tid = threadIdx.x;
+    const bool first = hist_valid[c] == 0;
+    float change = 0.f, dperf = 0.f;
+    bool ok = true;
+    if (!first) {
+        float part[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int p = tid; p < NP; p += VNT) {
+            const float dl = hist_c[p] - theta[p];
+            part[tensor_of(p)] = fmaf(dl, dl, part[tensor_of(p)]);
+        }
+#pragma unroll
+        for (int t = 0; t < 8; ++t) change += sqrtf((float)block_sum<double>((double)part[t], red));
+        dperf = perf - hist_perf[c];
+        ok = (change <= thr_change) && (dperf >= -thr_perf);
+    }
+    __syncthreads();
+    for (int p = tid; p < P_PAD; p += VNT) {
+        const float t = theta[p];
+        hist_c[p] = t;
+        if (ok) { params_c[p] = t; anchor_c[p] = t; }
+    }
+    if (tid == 0) {
+        hist_perf[c] = perf;
+        hist_valid[c] = 1;
+        rejected[c] = ok ? 0 : rejected[c] + 1;
+        if (out_change) out_change[c] = change;
+        if (out_dperf) out_dperf[c] = dperf;
+    }
+}
+
+__global__ void __launch_bounds__(VNT) verify_kernel(const FmVerifyArgs a) {
+    __shared__ double red[34];
+    if (a.agg_pos[0] < 0) return;
+    const int c = blockIdx.x, tid = threadIdx.x;
+    const int g = a.first_client + c;
+    float* params_c = a.params + (size_t)c * P_PAD;
+    if (g == a.agg_pos[1]) {                       // the aggregator just adopts its own result (no gate, anchor kept)
+        for (int p = tid; p < P_PAD; p += VNT) params_c[p] = a.theta[p];
+        return;
+    }
+    const int seg = a.shared_segment ? 0 : c;
+    const int r0 = a.sse_off[seg], nr = a.sse_off[seg + 1] - r0;
+    double part = 0.0;
+    for (int r = tid; r < nr; r += VNT) part += (double)a.sse[r0 + r];
+    const double tot = block_sum<double>(part, red);
+    const float mse = (float)(tot / ((double)nr * (double)D));
+    const float perf = 1.f / (1.f + mse);
+    verify_decide_and_apply(params_c, a.anchor + (size_t)c * P_PAD, a.hist + (size_t)c * P_PAD, a.hist_perf,
+                            a.hist_valid, a.rejected, c, a.theta, perf, a.thr_change, a.thr_perf, red,
+                            a.out_change, a.out_dperf);
+}
+
+}  // namespace fm
+
+extern "C" int fm_elect(const float* scores, const int32_t* sel, int32_t n_sel, int32_t voter_pos,
+                        const int32_t* agg_count, int32_t max_agg, int32_t* agg_pos, void* stream) {
+    fm::elect_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(scores, sel, n_sel, voter_pos, agg_count, max_agg, agg_pos);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int fm_merge(const FmMergeArgs* args, void* stream) {
+    using namespace fm;
+    if (args->n_sel <= 0 || args->n_sel > FM_MAX_SEL) return (int)cudaErrorInvalidValue;
+    const int grid = (P_PAD + MNT - 1) / MNT;
+    merge_kernel<<<grid, MNT, args->n_sel * sizeof(float), (cudaStream_t)stream>>>(*args);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int fm_verify_update(const FmVerifyArgs* args, void* stream) {
+    using namespace fm;
+    if (args->n_local <= 0) return 0;
+    verify_kernel<<<args->n_local, VNT, 0, (cudaStream_t)stream>>>(*args);
+    return (int)cudaGetLastError();
+}

@@ -1,0 +1,457 @@
+// T1 -- persistent per-client local training (exact fp32, CUDA cores).
+//
+// One CTA owns one selected client for its whole ClientTrainer.run() call
+// (reference: src/Trainer/client_trainer.py:360-419): weights (27 KB), Adam moments (54 KB) and,
+// for FedProx, the anchor (27 KB) live in shared memory across all epochs and steps; the host is
+// not involved between steps.  Batches of <= BT rows are streamed global->shared by the TMA unit
+// (1-D bulk async copies completing on an mbarrier, double buffered) while the previous step
+// computes.  Per step: 4-layer forward, SAE/AE loss, backward, FedProx gradient and Adam, all
+// fused; weight gradients are consumed by the Adam update in registers and never stored.
+//
+// The batch is 12 rows and every step depends on the previous step's weights, so the
+// matrix products are [12 x K] x [K x N] with N <= 115: far below a tcgen05 tile (M >= 64).
+// The products therefore run as register-tiled FFMA out of shared memory; what this kernel
+// buys over the reference is persistence (no launches, no host syncs, no HBM round trips).
+#include "common.cuh"
+#include "../include/fedmse_b200.h"
+
+namespace fm {
+
+constexpr int NT = 512;  // threads per CTA
+
+// shared-memory weight layout: every matrix row padded to a multiple of 4 floats so rows can be
+// read with LDS.128, pitches chosen so 8 consecutive rows hit 8 distinct 16-B bank groups.
+constexpr int W1P = 116, W2P = 28, W3P = 8, W4P = 28;
+constexpr int S_W1 = 0;
+constexpr int S_B1 = S_W1 + H * W1P;
+constexpr int S_W2 = S_B1 + 28;
+constexpr int S_B2 = S_W2 + Z * W2P;
+constexpr int S_W3 = S_B2 + 8;
+constexpr int S_B3 = S_W3 + H * W3P;
+constexpr int S_W4 = S_B3 + 28;
+constexpr int S_B4 = S_W4 + D * W4P;
+constexpr int S_TOT = S_B4 + 116;  // 6944 floats
+static_assert(S_TOT % 4 == 0, "");
+
+__device__ __forceinline__ int sidx(int p) {
+    if (p < OFF_B1) { int j = p / D; return S_W1 + j * W1P + (p - j * D); }
+    if (p < OFF_W2) return S_B1 + (p - OFF_B1);
+    if (p < OFF_B2) { int q = p - OFF_W2, i = q / H; return S_W2 + i * W2P + (q - i * H); }
+    if (p < OFF_W3) return S_B2 + (p - OFF_B2);
+    if (p < OFF_B3) { int q = p - OFF_W3, j = q / Z; return S_W3 + j * W3P + (q - j * Z); }
+    if (p < OFF_W4) return S_B3 + (p - OFF_B3);
+    if (p < OFF_B4) { int q = p - OFF_W4, d = q / H; return S_W4 + d * W4P + (q - d * H); }
+    return S_B4 + (p - OFF_B4);
+}
+
+// C[b][n] = act(bias[n] + sum_k A[b][k] W[n][k]); K = 4*K4 (zero padded), rows b < BT.
+// item = (n, group of 4 rows); KS adjacent lanes split the K chunks and shuffle-reduce.
+template <int BT, int N, int K4, int KS, bool RELU>
+__device__ __forceinline__ void layer_nt(const float* __restrict__ A, int AP, const float* __restrict__ W,
+                                         int WP, const float* __restrict__ bias, float* __restrict__ C,
+                                         int CP) {
+    constexpr int ITEMS = N * (BT / 4);
+    constexpr int PER_PASS = NT / KS;
+    const int s = threadIdx.x % KS;
+    for (int base = 0; base < ITEMS; base += PER_PASS) {
+        const int it = base + threadIdx.x / KS;
+        const bool active = it < ITEMS;
+        const int n = active ? it % N : 0, bg = active ? it / N : 0;
+        float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
+        if (active) {
+            const float* wrow = W + n * WP;
+            const float* arow = A + (bg * 4) * AP;
+#pragma unroll 2
+            for (int c = s; c < K4; c += KS) {
+                const float4 w = *reinterpret_cast<const float4*>(wrow + 4 * c);
+                const float4 a0 = *reinterpret_cast<const float4*>(arow + 4 * c);
+                const float4 a1 = *reinterpret_cast<const float4*>(arow + AP + 4 * c);
+                const float4 a2 = *reinterpret_cast<const float4*>(arow + 2 * AP + 4 * c);
+                const float4 a3 = *reinterpret_cast<const float4*>(arow + 3 * AP + 4 * c);
+                acc0 = fmaf(a0.x, w.x, fmaf(a0.y, w.y, fmaf(a0.z, w.z, fmaf(a0.w, w.w, acc0))));
+                acc1 = fmaf(a1.x, w.x, fmaf(a1.y, w.y, fmaf(a1.z, w.z, fmaf(a1.w, w.w, acc1))));
+                acc2 = fmaf(a2.x, w.x, fmaf(a2.y, w.y, fmaf(a2.z, w.z, fmaf(a2.w, w.w, acc2))));
+                acc3 = fmaf(a3.x, w.x, fmaf(a3.y, w.y, fmaf(a3.z, w.z, fmaf(a3.w, w.w, acc3))));
+            }
+        }
+#pragma unroll
+        for (int o = 1; o < KS; o <<= 1) {
+            acc0 += __shfl_xor_sync(0xffffffffu, acc0, o);
+            acc1 += __shfl_xor_sync(0xffffffffu, acc1, o);
+            acc2 += __shfl_xor_sync(0xffffffffu, acc2, o);
+            acc3 += __shfl_xor_sync(0xffffffffu, acc3, o);
+        }
+        if (active && s == 0) {
+            const float bb = bias[n];
+            float r0 = acc0 + bb, r1 = acc1 + bb, r2 = acc2 + bb, r3 = acc3 + bb;
+            if (RELU) { r0 = fmaxf(r0, 0.f); r1 = fmaxf(r1, 0.f); r2 = fmaxf(r2, 0.f); r3 = fmaxf(r3, 0.f); }
+            float* c = C + (bg * 4) * CP + n;
+            c[0] = r0; c[CP] = r1; c[2 * CP] = r2; c[3 * CP] = r3;
+        }
+    }
+}
+
+// Data gradient: GinT[k][b] = mask * sum_n GoutT[n][b] * W[n][k]; gradients are stored transposed
+// ([feature][BT]) so four batch rows are one LDS.128.  mask = (Act[b][k] > 0) when RELU_MASK.
+template <int BT, int N, int K, int KS, bool RELU_MASK>
+__device__ __forceinline__ void layer_dgrad(const float* __restrict__ GoutT, const float* __restrict__ W, int WP,
+                                            const float* __restrict__ Act, int ActP, float* __restrict__ GinT) {
+    constexpr int ITEMS = K * (BT / 4);
+    constexpr int PER_PASS = NT / KS;
+    const int s = threadIdx.x % KS;
+    for (int base = 0; base < ITEMS; base += PER_PASS) {
+        const int it = base + threadIdx.x / KS;
+        const bool active = it < ITEMS;
+        const int k = active ? it % K : 0, bg = active ? it / K : 0;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (active) {
+#pragma unroll 4
+            for (int n = s; n < N; n += KS) {
+                const float w = W[n * WP + k];
+                const float4 g = *reinterpret_cast<const float4*>(GoutT + n * BT + bg * 4);
+                acc.x = fmaf(g.x, w, acc.x); acc.y = fmaf(g.y, w, acc.y);
+                acc.z = fmaf(g.z, w, acc.z); acc.w = fmaf(g.w, w, acc.w);
+            }
+        }
+#pragma unroll
+        for (int o = 1; o < KS; o <<= 1) {
+            acc.x += __shfl_xor_sync(0xffffffffu, acc.x, o);
+            acc.y += __shfl_xor_sync(0xffffffffu, acc.y, o);
+            acc.z += __shfl_xor_sync(0xffffffffu, acc.z, o);
+            acc.w += __shfl_xor_sync(0xffffffffu, acc.w, o);
+        }
+        if (active && s == 0) {
+            if (RELU_MASK) {
+                const float* a = Act + (bg * 4) * ActP + k;
+                acc.x = a[0] > 0.f ? acc.x : 0.f;
+                acc.y = a[ActP] > 0.f ? acc.y : 0.f;
+                acc.z = a[2 * ActP] > 0.f ? acc.z : 0.f;
+                acc.w = a[3 * ActP] > 0.f ? acc.w : 0.f;
+            }
+            *reinterpret_cast<float4*>(GinT + k * BT + bg * 4) = acc;
+        }
+    }
+}
+
+struct AdamStep {
+    float step_size;     // lr / (1 - b1^t)
+    float inv_sqrt_bc2;  // 1 / sqrt(1 - b2^t)
+    float mu;            // FedProx
+};
+
+__device__ __forceinline__ void adam_update(float* __restrict__ Ws, float* __restrict__ Ms, float* __restrict__ Vs,
+                                            const float* __restrict__ As, int idx, float g, const AdamStep& st,
+                                            float& prox_acc) {
+    float w = Ws[idx], m = Ms[idx], v = Vs[idx];
+    if (st.mu != 0.f) {
+        const float dl = w - As[idx];
+        prox_acc = fmaf(dl, dl, prox_acc);
+        g = fmaf(2.f * st.mu, dl, g);
+    }
+    m = fmaf(g - m, 0.1f, m);                     // exp_avg.lerp_(g, 1 - beta1)
+    v = fmaf(0.001f * g, g, v * 0.999f);          // exp_avg_sq.mul_(beta2).addcmul_(g, g, 1 - beta2)
+    const float denom = fmaf(sqrtf(v), st.inv_sqrt_bc2, 1e-8f);
+    w = fmaf(-st.step_size, m / denom, w);
+    Ws[idx] = w; Ms[idx] = m; Vs[idx] = v;
+}
+
+// Weight gradient + Adam for one linear layer: dW[n][k] = sum_b GT[n][b] * A[b][k], dbias[n] = sum_b GT[n][b].
+// item = (n, chunk of 4 consecutive k); the gradient never leaves registers.
+template <int BT, int N, int K, int K4>
+__device__ __forceinline__ void wgrad_adam(int item0, const float* __restrict__ GT, const float* __restrict__ A,
+                                           int AP, int sW, int WP, int sB, float* Ws, float* Ms, float* Vs,
+                                           const float* As, const AdamStep& st, float& prox_acc) {
+    constexpr int ITEMS = N * K4 + (N + 3) / 4;
+    for (int it = item0; it < ITEMS; it += NT) {
+        if (it < N * K4) {
+            const int n = it / K4, kc = it - n * K4;
+            float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+            const float* gt = GT + n * BT;
+            const float* a = A + 4 * kc;
+#pragma unroll
+            for (int b4 = 0; b4 < BT; b4 += 4) {
+                const float4 gg = *reinterpret_cast<const float4*>(gt + b4);
+                const float4 a0 = *reinterpret_cast<const float4*>(a + (b4 + 0) * AP);
+                const float4 a1 = *reinterpret_cast<const float4*>(a + (b4 + 1) * AP);
+                const float4 a2 = *reinterpret_cast<const float4*>(a + (b4 + 2) * AP);
+                const float4 a3 = *reinterpret_cast<const float4*>(a + (b4 + 3) * AP);
+                g.x = fmaf(gg.x, a0.x, fmaf(gg.y, a1.x, fmaf(gg.z, a2.x, fmaf(gg.w, a3.x, g.x))));
+                g.y = fmaf(gg.x, a0.y, fmaf(gg.y, a1.y, fmaf(gg.z, a2.y, fmaf(gg.w, a3.y, g.y))));
+                g.z = fmaf(gg.x, a0.z, fmaf(gg.y, a1.z, fmaf(gg.z, a2.z, fmaf(gg.w, a3.z, g.z))));
+                g.w = fmaf(gg.x, a0.w, fmaf(gg.y, a1.w, fmaf(gg.z, a2.w, fmaf(gg.w, a3.w, g.w))));
+            }
+            const int idx = sW + n * WP + 4 * kc, k0 = 4 * kc;
+            adam_update(Ws, Ms, Vs, As, idx, g.x, st, prox_acc);
+            if (k0 + 1 < K) adam_update(Ws, Ms, Vs, As, idx + 1, g.y, st, prox_acc);
+            if (k0 + 2 < K) adam_update(Ws, Ms, Vs, As, idx + 2, g.z, st, prox_acc);
+            if (k0 + 3 < K) adam_update(Ws, Ms, Vs, As, idx + 3, g.w, st, prox_acc);
+        } else {
+            const int n0 = (it - N * K4) * 4;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int n = n0 + q;
+                if (n < N) {
+                    float g = 0.f;
+#pragma unroll
+                    for (int b = 0; b < BT; ++b) g += GT[n * BT + b];
+                    adam_update(Ws, Ms, Vs, As, sB + n, g, st, prox_acc);
+                }
+            }
+        }
+    }
+}
+
+template <int BT>
+struct TrainSmem {
+    static constexpr int HP = 28, ZP = 8, XHP = 116;
+    float W[S_TOT];
+    float M[S_TOT];
+    float V[S_TOT];
+    alignas(16) float x[2][BT * XP];
+    alignas(16) float h1[BT * HP];
+    alignas(16) float z[BT * ZP];
+    alignas(16) float h2[BT * HP];
+    alignas(16) float dxT[D * BT];     // d(loss)/d(xhat), transposed [d][b]
+    alignas(16) float dp2T[H * BT];    // grad wrt pre-activation of decoder hidden
+    alignas(16) float dzT[Z * BT];
+    alignas(16) float dp1T[H * BT];
+    float znorm[BT];
+    double red[34];
+    float sc[8];                        // step scalars broadcast by thread 0
+    int flag[4];
+    alignas(8) uint64_t bar[2];
+    // FedProx anchor (S_TOT floats) follows only when mu != 0
+};
+
+template <int BT>
+__global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    using SM = TrainSmem<BT>;
+    SM& S = *reinterpret_cast<SM*>(smem_raw);
+    float* As = reinterpret_cast<float*>(smem_raw + ((sizeof(SM) + 15) / 16) * 16);  // valid iff mu != 0
+    const int tid = threadIdx.x;
+    const int c = a.sel_local[blockIdx.x];
+    const int g = a.first_client + c;
+    const int tr0 = a.train_off[c], n_tr = a.train_off[c + 1] - tr0;
+    const int va0 = a.valid_off[g], n_va = a.valid_off[g + 1] - va0;
+    const int B = a.batch;
+    const int nbt = (n_tr + B - 1) / B, nbv = (n_va + B - 1) / B;
+    const int steps_per_epoch = nbt + nbv;
+    const bool prox = a.fedprox_mu != 0.f;
+    float* gp = a.params + (size_t)c * P_PAD;
+    float* gm = a.adam_m + (size_t)c * P_PAD;
+    float* gv = a.adam_v + (size_t)c * P_PAD;
+
+    // ---- load state into shared memory -----------------------------------------------------
+    for (int i = tid; i < S_TOT; i += NT) { S.W[i] = 0.f; S.M[i] = 0.f; S.V[i] = 0.f; if (prox) As[i] = 0.f; }
+    for (int i = tid; i < 2 * BT * XP; i += NT) (&S.x[0][0])[i] = 0.f;
+    for (int i = tid; i < BT * SM::HP; i += NT) { S.h1[i] = 0.f; S.h2[i] = 0.f; }
+    for (int i = tid; i < BT * SM::ZP; i += NT) S.z[i] = 0.f;
+    for (int i = tid; i < D * BT; i += NT) S.dxT[i] = 0.f;
+    for (int i = tid; i < H * BT; i += NT) { S.dp2T[i] = 0.f; S.dp1T[i] = 0.f; }
+    for (int i = tid; i < Z * BT; i += NT) S.dzT[i] = 0.f;
+    if (tid == 0) { mbar_init(&S.bar[0], 1); mbar_init(&S.bar[1], 1); fence_mbar_init(); }
+    __syncthreads();
+    for (int p = tid; p < NP; p += NT) {
+        const int s = sidx(p);
+        S.W[s] = gp[p]; S.M[s] = gm[p]; S.V[s] = gv[p];
+        if (prox) As[s] = a.anchor[(size_t)c * P_PAD + p];
+    }
+    fence_proxy_async();
+    __syncthreads();
+
+    // batch stream: per epoch nbt train batches then nbv validation batches
+    auto issue = [&](int q_in_epoch, int buf) {   // thread 0 only
+        const float* src; int rows;
+        if (q_in_epoch < nbt) { const int r0 = q_in_epoch * B; rows = min(B, n_tr - r0); src = a.x_train + (size_t)(tr0 + r0) * XP; }
+        else { const int r0 = (q_in_epoch - nbt) * B; rows = min(B, n_va - r0); src = a.x_valid + (size_t)(va0 + r0) * XP; }
+        const uint32_t bytes = (uint32_t)rows * XP * 4u;
+        mbar_expect_tx(&S.bar[buf], bytes);
+        bulk_g2s(&S.x[buf][0], src, bytes, &S.bar[buf]);
+    };
+
+    int t_step = a.adam_t[c];    // tracked by thread 0 only
+    double b1t = 1.0, b2t = 1.0;
+    if (tid == 0) { b1t = pow(0.9, (double)t_step); b2t = pow(0.999, (double)t_step); }
+    float min_valid = __int_as_float(0x7f800000);
+    int worse = 0, epochs_done = 0;
+    uint32_t uses0 = 0, uses1 = 0;   // completed waits per buffer -> parity
+    long long q = 0;                  // global step index (selects the buffer)
+    bool outstanding = false;
+    if (tid == 0 && steps_per_epoch > 0 && a.epochs > 0 && n_tr > 0) issue(0, 0);
+    outstanding = (steps_per_epoch > 0 && a.epochs > 0 && n_tr > 0);
+    const int n_epochs = (n_tr > 0) ? a.epochs : 0;
+
+    for (int e = 0; e < n_epochs; ++e) {
+        float loss_acc = 0.f;   // this thread's share of sum over train batches of batch loss
+        float vloss_acc = 0.f;
+        for (int qe = 0; qe < steps_per_epoch; ++qe, ++q) {
+            const int buf = (int)(q & 1);
+            const bool is_train = qe < nbt;
+            const int r0 = is_train ? qe * B : (qe - nbt) * B;
+            const int rows = min(B, (is_train ? n_tr : n_va) - r0);
+            // S0: wait for this batch, prefetch the next one into the other buffer
+            mbar_wait(&S.bar[buf], (buf ? uses1 : uses0) & 1u);
+            if (buf) ++uses1; else ++uses0;
+            const bool has_next = (qe + 1 < steps_per_epoch) || (e + 1 < n_epochs);
+            if (tid == 0 && has_next) issue((qe + 1) % steps_per_epoch, buf ^ 1);
+            outstanding = has_next;
+            const float* X = &S.x[buf][0];
+            if (is_train && tid == 0) {     // bias corrections in double, broadcast through smem
+                ++t_step; b1t *= 0.9; b2t *= 0.999;
+                S.sc[0] = (float)((double)a.lr / (1.0 - b1t));
+                S.sc[1] = (float)(1.0 / sqrt(1.0 - b2t));
+            }
+            // ---- forward ----
+            layer_nt<BT, H, 29, 4, true>(X, XP, S.W + S_W1, W1P, S.W + S_B1, S.h1, SM::HP);
+            __syncthreads();
+            layer_nt<BT, Z, 7, 4, false>(S.h1, SM::HP, S.W + S_W2, W2P, S.W + S_B2, S.z, SM::ZP);
+            __syncthreads();
+            layer_nt<BT, H, 2, 1, true>(S.z, SM::ZP, S.W + S_W3, W3P, S.W + S_B3, S.h2, SM::HP);
+            if (tid < BT) {
+                float s2 = 0.f;
+#pragma unroll
+                for (int i = 0; i < Z; ++i) s2 = fmaf(S.z[tid * SM::ZP + i], S.z[tid * SM::ZP + i], s2);
+                const float nz = sqrtf(s2);
+                S.znorm[tid] = nz;
+                if (tid < rows && a.shrink_lambda != 0.f) {
+                    const float contrib = a.shrink_lambda * nz / (float)rows;
+                    if (is_train) loss_acc += contrib; else vloss_acc += contrib;
+                }
+            }
+            __syncthreads();
+            // output layer fused with the reconstruction loss and its gradient
+            {
+                constexpr int ITEMS = D * (BT / 4);
+                const float inv = 1.f / ((float)rows * (float)D);
+                float lsum = 0.f;
+                for (int it = tid; it < ITEMS; it += NT) {
+                    const int d = it % D, bg = it / D;
+                    const float* wrow = S.W + S_W4 + d * W4P;
+                    const float* arow = S.h2 + (bg * 4) * SM::HP;
+                    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
+#pragma unroll
+                    for (int cc = 0; cc < 7; ++cc) {
+                        const float4 w = *reinterpret_cast<const float4*>(wrow + 4 * cc);
+                        const float4 a0 = *reinterpret_cast<const float4*>(arow + 4 * cc);
+                        const float4 a1 = *reinterpret_cast<const float4*>(arow + SM::HP + 4 * cc);
+                        const float4 a2 = *reinterpret_cast<const float4*>(arow + 2 * SM::HP + 4 * cc);
+                        const float4 a3 = *reinterpret_cast<const float4*>(arow + 3 * SM::HP + 4 * cc);
+                        acc0 = fmaf(a0.x, w.x, fmaf(a0.y, w.y, fmaf(a0.z, w.z, fmaf(a0.w, w.w, acc0))));
+                        acc1 = fmaf(a1.x, w.x, fmaf(a1.y, w.y, fmaf(a1.z, w.z, fmaf(a1.w, w.w, acc1))));
+                        acc2 = fmaf(a2.x, w.x, fmaf(a2.y, w.y, fmaf(a2.z, w.z, fmaf(a2.w, w.w, acc2))));
+                        acc3 = fmaf(a3.x, w.x, fmaf(a3.y, w.y, fmaf(a3.z, w.z, fmaf(a3.w, w.w, acc3))));
+                    }
+                    const float bb = S.W[S_B4 + d];
+                    const int b0 = bg * 4;
+                    float e0 = (acc0 + bb) - X[(b0 + 0) * XP + d];
+                    float e1 = (acc1 + bb) - X[(b0 + 1) * XP + d];
+                    float e2 = (acc2 + bb) - X[(b0 + 2) * XP + d];
+                    float e3 = (acc3 + bb) - X[(b0 + 3) * XP + d];
+                    e0 = (b0 + 0 < rows) ? e0 : 0.f; e1 = (b0 + 1 < rows) ? e1 : 0.f;
+                    e2 = (b0 + 2 < rows) ? e2 : 0.f; e3 = (b0 + 3 < rows) ? e3 : 0.f;
+                    lsum = fmaf(e0, e0, fmaf(e1, e1, fmaf(e2, e2, fmaf(e3, e3, lsum))));
+                    if (is_train) {
+                        const float sc2 = 2.f * inv;
+                        *reinterpret_cast<float4*>(S.dxT + d * BT + b0) = make_float4(e0 * sc2, e1 * sc2, e2 * sc2, e3 * sc2);
+                    }
+                }
+                if (is_train) loss_acc = fmaf(lsum, inv, loss_acc); else vloss_acc = fmaf(lsum, inv, vloss_acc);
+            }
+            __syncthreads();
+            if (!is_train) continue;
+            // ---- backward ----
+            layer_dgrad<BT, D, H, 4, true>(S.dxT, S.W + S_W4, W4P, S.h2, SM::HP, S.dp2T);
+            __syncthreads();
+            float prox_acc = 0.f;
+            AdamStep st;
+            st.step_size = S.sc[0]; st.inv_sqrt_bc2 = S.sc[1]; st.mu = a.fedprox_mu;
+            // (update W4,b4) || (dz = dp2 W3 + shrink gradient)
+            wgrad_adam<BT, D, H, 7>(tid, S.dxT, S.h2, SM::HP, S_W4, W4P, S_B4, S.W, S.M, S.V, As, st, prox_acc);
+            layer_dgrad<BT, H, Z, 4, false>(S.dp2T, S.W + S_W3, W3P, nullptr, 0, S.dzT);
+            __syncthreads();
+            if (a.shrink_lambda != 0.f && tid < Z * BT) {
+                const int i = tid / BT, b = tid - i * BT;
+                if (b < rows) {
+                    const float nz = S.znorm[b];
+                    if (nz > 0.f) S.dzT[i * BT + b] += a.shrink_lambda / (float)rows * S.z[b * SM::ZP + i] / nz;
+                }
+            }
+            __syncthreads();
+            // (update W3,b3) || (dp1 = relu'(h1) * dz W2)
+            wgrad_adam<BT, H, Z, 2>(tid, S.dp2T, S.z, SM::ZP, S_W3, W3P, S_B3, S.W, S.M, S.V, As, st, prox_acc);
+            layer_dgrad<BT, Z, H, 1, true>(S.dzT, S.W + S_W2, W2P, S.h1, SM::HP, S.dp1T);
+            __syncthreads();
+            // update W2,b2 and W1,b1
+            wgrad_adam<BT, Z, H, 7>(tid, S.dzT, S.h1, SM::HP, S_W2, W2P, S_B2, S.W, S.M, S.V, As, st, prox_acc);
+            wgrad_adam<BT, H, D, 29>(tid, S.dp1T, X, XP, S_W1, W1P, S_B1, S.W, S.M, S.V, As, st, prox_acc);
+            if (prox) loss_acc = fmaf(a.fedprox_mu, prox_acc, loss_acc);
+            __syncthreads();
+        }
+        // ---- epoch bookkeeping (reference: client_trainer.py:385, :404-417) ----
+        float prox_val = 0.f;
+        if (prox) {
+            float pa = 0.f;
+            for (int p = tid; p < NP; p += NT) { const int s = sidx(p); const float dl = S.W[s] - As[s]; pa = fmaf(dl, dl, pa); }
+            prox_val = a.fedprox_mu * (float)block_sum<double>((double)pa, S.red);
+        }
+        const double tl = block_sum<double>((double)loss_acc, S.red);
+        const double vl = block_sum<double>((double)vloss_acc, S.red);
+        const float train_loss = (float)(tl / (double)max(nbt, 1));
+        const float valid_loss = nbv > 0 ? (float)(vl / (double)nbv) + prox_val : __int_as_float(0x7fc00000);
+        if (tid == 0 && e < a.log_stride) {
+            a.loss_log[((size_t)c * a.log_stride + e) * 2 + 0] = train_loss;
+            a.loss_log[((size_t)c * a.log_stride + e) * 2 + 1] = valid_loss;
+        }
+        epochs_done = e + 1;
+        bool stop = false;
+        if (valid_loss < min_valid) {      // uniform across the block: every thread holds the same value
+            min_valid = valid_loss; worse = 0;
+            float* gb = a.best + (size_t)c * P_PAD;
+            for (int p = tid; p < NP; p += NT) gb[p] = S.W[sidx(p)];
+        } else if (++worse >= a.patience) {
+            stop = true;
+        }
+        if (stop) break;
+    }
+    // drain a speculative prefetch so no async write lands after the CTA exits
+    if (outstanding) { const int buf = (int)(q & 1); mbar_wait(&S.bar[buf], (buf ? uses1 : uses0) & 1u); }
+    __syncthreads();
+    for (int p = tid; p < NP; p += NT) {
+        const int s = sidx(p);
+        gp[p] = S.W[s]; gm[p] = S.M[s]; gv[p] = S.V[s];
+    }
+    if (tid == 0) {
+        a.adam_t[c] = t_step;
+        a.epochs_run[c] = epochs_done;
+        a.trained_rounds[c] += 1;
+        for (int e = epochs_done; e < a.log_stride; ++e) {
+            a.loss_log[((size_t)c * a.log_stride + e) * 2 + 0] = 0.f;
+            a.loss_log[((size_t)c * a.log_stride + e) * 2 + 1] = 0.f;
+        }
+    }
+}
+
+}  // namespace fm
+
+// ---------------------------------------------------------------------------------------------
+extern "C" int fm_train_clients(const FmTrainArgs* args, void* stream) {
+    using namespace fm;
+    if (args->n_sel <= 0) return 0;
+    if (args->batch <= 0 || args->batch > 32) return (int)cudaErrorInvalidValue;
+    const bool prox = args->fedprox_mu != 0.f;
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t err;
+    if (args->batch <= 12) {
+        size_t smem = ((sizeof(TrainSmem<12>) + 15) / 16) * 16 + (prox ? S_TOT * sizeof(float) : 0);
+        err = cudaFuncSetAttribute(train_clients_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (err != cudaSuccess) return (int)err;
+        train_clients_kernel<12><<<args->n_sel, NT, smem, st>>>(*args);
+    } else {
+        size_t smem = ((sizeof(TrainSmem<32>) + 15) / 16) * 16 + (prox ? S_TOT * sizeof(float) : 0);
+        err = cudaFuncSetAttribute(train_clients_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (err != cudaSuccess) return (int)err;
+        train_clients_kernel<32><<<args->n_sel, NT, smem, st>>>(*args);
+    }
+    return (int)cudaGetLastError();
+}

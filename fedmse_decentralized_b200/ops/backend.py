@@ -15,12 +15,14 @@ owns and the engine sums them across ranks.
 from __future__ import annotations
 
 from dataclasses import dataclass, field
-from typing import Dict, List, Optional, Sequence, Tuple
+from typing import TYPE_CHECKING, Dict, List, Optional, Sequence, Tuple
 
 import torch
 
-from ..data.shards import ShardStore
-from ..trainer.state import FederationState
+if TYPE_CHECKING:  # avoid the ops <-> trainer import cycle
+    from ..data.shards import ShardStore
+    from ..trainer.state import FederationState
+
 from . import oracle
 from .oracle import TrainHP
 
@@ -89,7 +91,7 @@ class OracleBackend:
 
     def elect(self, st: FederationState, scores: torch.Tensor, ctl: RoundControl, spec: MergeSpec
               ) -> torch.Tensor:
-        """argmin over candidates with remaining quota; returns int32[1] position or -1."""
+        """argmin over candidates with remaining quota; returns int32[2] = (position, global id) or -1."""
         sel = torch.tensor(ctl.sel, dtype=torch.long, device=scores.device)
         ok = st.agg_count[sel] < spec.max_aggregations
         if ctl.voter_pos >= 0:
@@ -102,7 +104,7 @@ class OracleBackend:
         pos = int(torch.argmin(s)) if bool(ok.any()) else -1
         if pos >= 0 and not bool(ok[pos]):
             pos = int(torch.nonzero(ok)[0])
-        return torch.tensor([pos], dtype=torch.int32, device=scores.device)
+        return torch.tensor([pos, ctl.sel[pos] if pos >= 0 else -1], dtype=torch.int32, device=scores.device)
 
     # ------------------------------------------------------------------ T2: merge
     def merge_scores(self, st: FederationState, sh: ShardStore, ctl: RoundControl) -> torch.Tensor:
@@ -117,7 +119,7 @@ class OracleBackend:
               ) -> torch.Tensor:
         """Weighted parameter reduction. ``rows`` = the selected models ``[n_sel, PP]`` when some
         live on other ranks (gathered by the engine); ``None`` = all local."""
-        a = int(agg_pos)
+        a = int(agg_pos[0])
         theta = torch.zeros(self.layout.padded, dtype=torch.float32, device=st.device)
         if a < 0:
             return theta
@@ -135,7 +137,7 @@ class OracleBackend:
     # ------------------------------------------------------------------ T3
     def verify_update(self, st: FederationState, sh: ShardStore, ctl: RoundControl, spec: MergeSpec,
                       theta: torch.Tensor, agg_pos: torch.Tensor) -> None:
-        a = int(agg_pos)
+        a = int(agg_pos[0])
         if a < 0:
             return
         agg_g = ctl.sel[a]

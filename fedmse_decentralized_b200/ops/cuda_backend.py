@@ -1,0 +1,306 @@
+"""CUDA backend: maps each round-engine operation to the sm_100a kernels of ``csrc/``.
+
+Kernel launches per round (elected mode): 1 train + (1 normalise + 1 score + 1
+reduce + 1 elect) for the vote + (1 score + 1 reduce) for MSE weights + 1 merge +
+(1 score + 1 verify) + (1-2 score + 1 AUC) for evaluation; the host uploads one
+small control block and reads one small result block.  The reference issues
+O(clients x steps x 40) launches and a host sync per step for the same round
+(SURVEY.md §3.2, §7.1).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import TYPE_CHECKING, Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+if TYPE_CHECKING:  # avoid the ops <-> trainer import cycle
+    from ..data.shards import ShardStore
+    from ..trainer.state import FederationState
+
+from ..layout import D_PAD, ParamLayout
+from . import _lib
+from .backend import MergeSpec, RoundControl
+from .oracle import TrainHP
+
+TILE = 64
+
+
+def _ptr(t: Optional[torch.Tensor]) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+def make_tiles(segments: Sequence[Sequence[int]]) -> torch.Tensor:
+    """Tile table ``[n, 4] = {slot, row0, nrows, out0}`` covering ``(slot, row0, nrows, out0)`` segments."""
+    out = []
+    for slot, row0, nrows, out0 in segments:
+        for s in range(0, nrows, TILE):
+            out.append((slot, row0 + s, min(TILE, nrows - s), out0 + s))
+    return torch.tensor(out, dtype=torch.int32).reshape(-1, 4)
+
+
+class CudaBackend:
+    name = "cuda"
+    reads_peers = True   # merge / gossip kernels read other ranks' slabs themselves
+
+    def __init__(self, layout: ParamLayout, device):
+        if (layout.dim, layout.hidden, layout.latent) != (115, 27, 7):
+            raise ValueError("the sm_100a kernels are specialised for the 115-27-7 autoencoder; "
+                             "use backend='oracle' for other shapes")
+        self.layout = layout
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("CudaBackend needs a CUDA device")
+        self.lib = _lib.load()
+        self.launches = 0
+        self._slabs = []
+        self._tile_cache: Dict = {}
+
+    # ------------------------------------------------------------------ setup
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def alloc_param_slab(self, n_local: int, padded: int, comm) -> torch.Tensor:
+        from ..parallel.symmetric import SymmetricSlab
+        with torch.cuda.device(self.device):
+            n_max = n_local
+            if comm.is_dist:
+                n_max = int(max(comm.all_gather_object(n_local)))
+            self.param_slab = SymmetricSlab(n_local, padded, comm, rows_max=n_max)
+            self.snap_slab = None
+        self._slabs.append(self.param_slab)
+        return self.param_slab.tensor
+
+    def bind(self, st: FederationState, sh: ShardStore, comm, hp: TrainHP, spec: MergeSpec, model_type: str):
+        dev = self.device
+        self.st, self.sh, self.comm = st, sh, comm
+        f32 = dict(dtype=torch.float32, device=dev)
+        i32 = dict(dtype=torch.int32, device=dev)
+        n_sel_max = max(1, sh.n_global)
+        M = self._M = n_sel_max
+        # one control block per round: [sel | jitter (fp32 bits) | sel_local], uploaded in a single copy
+        # from a small ring of pinned staging buffers (a slot is reused only after its copy completed)
+        self.ctl_dev = torch.zeros(3 * M, **i32)
+        self.ctl_sel = self.ctl_dev[0:M]
+        self.ctl_jit = self.ctl_dev[M:2 * M].view(torch.float32)
+        self.ctl_sel_local = self.ctl_dev[2 * M:3 * M]
+        self._pin = [torch.zeros(3 * M, dtype=torch.int32).pin_memory() for _ in range(4)]
+        self._pin_ev = [None] * 4
+        self._pin_i = 0
+        self.n_sel_local = 0
+        self.agg_pos = torch.full((2,), -1, **i32)
+        self.scores = torch.zeros(n_sel_max, **f32)
+        self.mse = torch.zeros(n_sel_max, **f32)
+        self.weights = torch.zeros(n_sel_max, **f32)
+        self.theta = torch.zeros(self.layout.padded, **f32)
+        max_valid = sh.valid.max_count()
+        self.vote_norm = torch.zeros(max(1, max_valid), D_PAD, **f32)        # scratch: normalised vote matrix
+        self.vote_sse = torch.zeros(n_sel_max * max(1, max_valid), **f32)    # scratch
+        self.dev_rows = sh.dev.shape[0]
+        self.merge_sse = None                                                 # lazily [n_sel * dev_rows]
+        self.verify_sse = torch.zeros(max(1, sh.valid.x.shape[0]), **f32)
+        self.test_sse = torch.zeros(max(1, sh.test.x.shape[0]), **f32)
+        self.test_lat = torch.zeros(max(1, sh.test.x.shape[0]), 8, **f32)
+        self.train_lat = torch.zeros(max(1, sh.train.x.shape[0]), 8, **f32)
+        self.auc = torch.zeros(max(1, sh.n_clients), dtype=torch.float64, device=dev)
+        self.scores_out = torch.zeros(max(1, sh.test.x.shape[0]), **f32)
+        # static tile tables
+        C_ = sh.n_clients
+        self.tiles_test = make_tiles([(c, sh.test.off_host[c], sh.test.count(c), sh.test.off_host[c])
+                                      for c in range(C_)]).to(dev)
+        self.tiles_train = make_tiles([(c, sh.train.off_host[c], sh.train.count(c), sh.train.off_host[c])
+                                       for c in range(C_)]).to(dev)
+        f = sh.first_client
+        self.tiles_verify_own = make_tiles([(0, sh.valid.off_host[f + c], sh.valid.count(f + c),
+                                             sh.valid.off_host[f + c]) for c in range(C_)]).to(dev)
+        self.verify_off_own = torch.tensor([sh.valid.off_host[f + c] for c in range(C_ + 1)], **i32)
+        self.peer_table = self.param_slab.table
+
+    def begin_round(self, ctl: RoundControl) -> None:
+        """Upload the round's control block: selection (global + local ids) and jitter."""
+        n, M, sh = len(ctl.sel), self._M, self.sh
+        i = self._pin_i
+        self._pin_i = (i + 1) % len(self._pin)
+        if self._pin_ev[i] is not None:
+            self._pin_ev[i].synchronize()
+        pin = self._pin[i]
+        pin[0:n] = torch.tensor(ctl.sel, dtype=torch.int32)
+        pin[M:M + n].view(torch.float32)[:] = torch.tensor(ctl.jitter, dtype=torch.float32)
+        loc = [g - sh.first_client for g in ctl.sel if sh.first_client <= g < sh.first_client + sh.n_clients]
+        self.n_sel_local = len(loc)
+        if loc:
+            pin[2 * M:2 * M + len(loc)] = torch.tensor(loc, dtype=torch.int32)
+        self.ctl_dev.copy_(pin, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._pin_ev[i] = ev
+        self.agg_pos.fill_(-1)
+
+    def _tiles(self, key, builder) -> torch.Tensor:
+        t = self._tile_cache.get(key)
+        if t is None:
+            t = builder().to(self.device)
+            self._tile_cache[key] = t
+        return t
+
+    def _score(self, slab: torch.Tensor, n_local: int, first: int, slot_client: Optional[torch.Tensor],
+               X: torch.Tensor, tiles: torch.Tensor, out_sse: Optional[torch.Tensor],
+               out_lat: Optional[torch.Tensor]) -> None:
+        a = _lib.FmScoreArgs(_ptr(slab), _ptr(slot_client), first, n_local, _ptr(X), _ptr(tiles),
+                             tiles.shape[0], _ptr(out_sse), _ptr(out_lat))
+        _lib.check(self.lib.fm_score_rows(C.byref(a), self._stream()), "score_rows")
+        self.launches += 1
+
+    # ------------------------------------------------------------------ T1
+    def train(self, st: FederationState, sh: ShardStore, sel_local: Sequence[int], hp: TrainHP) -> None:
+        n = len(sel_local)
+        assert n == self.n_sel_local, "begin_round() must upload the control block before train()"
+        st.epochs_run.zero_()
+        if n == 0:
+            return
+        a = _lib.FmTrainArgs(
+            _ptr(st.params), _ptr(st.adam_m), _ptr(st.adam_v), _ptr(st.adam_t), _ptr(st.anchor), _ptr(st.best),
+            _ptr(st.loss_log), _ptr(st.epochs_run), _ptr(st.trained_rounds),
+            _ptr(sh.train.x), _ptr(sh.train.off), _ptr(sh.valid.x), _ptr(sh.valid.off),
+            _ptr(self.ctl_sel_local), n, sh.first_client, hp.epochs, hp.batch_size, hp.patience,
+            st.loss_log.shape[1], hp.lr, hp.shrink_lambda, hp.fedprox_mu)
+        _lib.check(self.lib.fm_train_clients(C.byref(a), self._stream()), "train_clients")
+        self.launches += 1
+
+    # ------------------------------------------------------------------ T2 vote
+    def vote_scores(self, st, sh, ctl: RoundControl, spec: MergeSpec) -> torch.Tensor:
+        n = len(ctl.sel)
+        v0, rows = sh.valid.off_host[ctl.vote_client], sh.valid.count(ctl.vote_client)
+        V = sh.valid.x[v0:v0 + rows]
+        _lib.check(self.lib.fm_vote_normalise(_ptr(V), rows, _ptr(self.vote_norm), self._stream()), "vote_normalise")
+        tiles = self._tiles(("vote", n, rows), lambda: make_tiles([(p, 0, rows, p * rows) for p in range(n)]))
+        self._score(st.params, st.n_clients, sh.first_client, self.ctl_sel, self.vote_norm, tiles,
+                    self.vote_sse, None)
+        _lib.check(self.lib.fm_chunk_mean(_ptr(self.vote_sse), n, rows, spec.vote_chunk, _ptr(self.ctl_jit),
+                                          _ptr(self.ctl_sel), sh.first_client, st.n_clients, ctl.voter_pos,
+                                          _ptr(self.scores), self._stream()), "chunk_mean")
+        self.launches += 2
+        return self.scores[:n]
+
+    def elect(self, st, scores: torch.Tensor, ctl: RoundControl, spec: MergeSpec) -> torch.Tensor:
+        _lib.check(self.lib.fm_elect(_ptr(scores), _ptr(self.ctl_sel), len(ctl.sel), ctl.voter_pos,
+                                     _ptr(st.agg_count), spec.max_aggregations, _ptr(self.agg_pos),
+                                     self._stream()), "elect")
+        self.launches += 1
+        return self.agg_pos
+
+    # ------------------------------------------------------------------ T2 merge
+    def merge_scores(self, st, sh, ctl: RoundControl) -> torch.Tensor:
+        n, R = len(ctl.sel), self.dev_rows
+        if self.merge_sse is None or self.merge_sse.numel() < n * R:
+            self.merge_sse = torch.zeros(n * R, dtype=torch.float32, device=self.device)
+        tiles = self._tiles(("dev", n, R), lambda: make_tiles([(p, 0, R, p * R) for p in range(n)]))
+        self._score(st.params, st.n_clients, sh.first_client, self.ctl_sel, sh.dev, tiles, self.merge_sse, None)
+        _lib.check(self.lib.fm_chunk_mean(_ptr(self.merge_sse), n, R, 0, 0, _ptr(self.ctl_sel), sh.first_client,
+                                          st.n_clients, -1, _ptr(self.mse), self._stream()), "chunk_mean")
+        self.launches += 1
+        return self.mse[:n]
+
+    def merge(self, st, sh, ctl: RoundControl, spec: MergeSpec, mse, agg_pos, rows=None) -> torch.Tensor:
+        n = len(ctl.sel)
+        a = _lib.FmMergeArgs(_ptr(self.peer_table), self.comm.world, self.comm.rank, sh.n_global,
+                             _ptr(self.ctl_sel), n, _ptr(mse), 1 if spec.update_type == "mse_avg" else 0,
+                             1 if spec.compat_alias else 0, _ptr(agg_pos), _ptr(st.agg_count), _ptr(self.theta),
+                             _ptr(self.weights))
+        _lib.check(self.lib.fm_merge(C.byref(a), self._stream()), "merge")
+        self.launches += 1
+        if self.comm.is_dist:
+            # every rank must have finished pulling peers' rows before anyone overwrites its slab
+            self.comm.sum_(self._barrier_token())
+        return self.theta
+
+    def _barrier_token(self) -> torch.Tensor:
+        if not hasattr(self, "_tok"):
+            self._tok = torch.zeros(1, dtype=torch.float32, device=self.device)
+        return self._tok
+
+    # ------------------------------------------------------------------ T3
+    def verify_update(self, st, sh, ctl: RoundControl, spec: MergeSpec, theta, agg_pos) -> None:
+        if spec.verification_method == "dev":
+            R = self.dev_rows
+            tiles = self._tiles(("vdev", R), lambda: make_tiles([(0, 0, R, 0)]))
+            X, off, shared = sh.dev, self._tiles(("voff", R), lambda: torch.tensor([0, R], dtype=torch.int32)), 1
+            if self.verify_sse.numel() < R:
+                self.verify_sse = torch.zeros(R, dtype=torch.float32, device=self.device)
+        elif ctl.verify_client >= 0:
+            g = ctl.verify_client
+            r0, R = sh.valid.off_host[g], sh.valid.count(g)
+            tiles = self._tiles(("vshared", g), lambda: make_tiles([(0, r0, R, 0)]))
+            X, off, shared = sh.valid.x, self._tiles(("voff", R), lambda: torch.tensor([0, R], dtype=torch.int32)), 1
+        else:
+            tiles, X, off, shared = self.tiles_verify_own, sh.valid.x, self.verify_off_own, 0
+        self._score(theta, 1, 0, None, X, tiles, self.verify_sse, None)
+        a = _lib.FmVerifyArgs(_ptr(st.params), _ptr(st.anchor), _ptr(st.hist), _ptr(st.hist_perf),
+                              _ptr(st.hist_valid), _ptr(st.rejected), st.n_clients, sh.first_client, _ptr(theta),
+                              _ptr(agg_pos), _ptr(self.verify_sse), _ptr(off), shared,
+                              spec.verification_threshold, spec.performance_threshold, 0, 0)
+        _lib.check(self.lib.fm_verify_update(C.byref(a), self._stream()), "verify_update")
+        self.launches += 1
+
+    # ------------------------------------------------------------------ T4
+    def evaluate(self, st, sh, model_type: str, want_latents: bool = False, metric: str = "AUC"):
+        hybrid = model_type == "hybrid"
+        if hybrid:
+            self._score(st.params, st.n_clients, sh.first_client, None, sh.train.x, self.tiles_train, None,
+                        self.train_lat)
+            self._score(st.params, st.n_clients, sh.first_client, None, sh.test.x, self.tiles_test, None,
+                        self.test_lat)
+        else:
+            self._score(st.params, st.n_clients, sh.first_client, None, sh.test.x, self.tiles_test,
+                        self.test_sse, self.test_lat if want_latents else None)
+        want_scores = metric != "AUC"
+        a = _lib.FmAucArgs(1 if hybrid else 0, st.n_clients, _ptr(self.test_sse), _ptr(self.test_lat),
+                           _ptr(sh.test.y), _ptr(sh.test.off), _ptr(self.train_lat), _ptr(sh.train.off),
+                           _ptr(self.scores_out) if want_scores else 0, _ptr(self.auc), sh.test.max_count())
+        _lib.check(self.lib.fm_auc(C.byref(a), self._stream()), "auc")
+        self.launches += 1
+        vals = None
+        if want_scores:
+            from . import oracle
+            vals = [oracle.classification_metrics(torch.nan_to_num(self.scores_out[sh.test.off_host[c]:
+                                                                                     sh.test.off_host[c + 1]]),
+                                                  sh.test.labels(c))[0] for c in range(st.n_clients)]
+        lat = None
+        if want_latents:
+            host = self.test_lat[:, :7].cpu().numpy().astype("float32")
+            lat = [host[sh.test.off_host[c]:sh.test.off_host[c + 1]].copy() for c in range(st.n_clients)]
+        return self.auc, vals, lat
+
+    # ------------------------------------------------------------------ gossip
+    def gossip(self, st, sh, ctl: RoundControl, spec: MergeSpec, neigh: List[List[int]], rows=None) -> None:
+        from ..parallel import topology
+        from ..parallel.symmetric import SymmetricSlab
+        if self.snap_slab is None:
+            with torch.cuda.device(self.device):
+                self.snap_slab = SymmetricSlab(st.n_clients, self.layout.padded, self.comm,
+                                               rows_max=self.param_slab.nbytes // (4 * self.layout.padded))
+            self._slabs.append(self.snap_slab)
+        if getattr(self, "_nbr_src", None) is not neigh:     # keep a reference: identity, not id()
+            off, idx = topology.to_csr(neigh, include_self=True)
+            self._nbr = (off.to(self.device), idx.to(self.device))
+            self._nbr_src = neigh
+        self.snap_slab.tensor.copy_(st.params)
+        if self.comm.is_dist:
+            self.comm.sum_(self._barrier_token())          # all snapshots complete before anyone reads
+        n = self.n_sel_local
+        if n:
+            a = _lib.FmGossipArgs(_ptr(self.snap_slab.table), self.comm.world, self.comm.rank, sh.n_global,
+                                  _ptr(st.params), _ptr(st.anchor), _ptr(st.hist), _ptr(st.hist_perf),
+                                  _ptr(st.hist_valid), _ptr(st.rejected), st.n_clients, sh.first_client,
+                                  _ptr(self.ctl_sel_local), n, _ptr(self._nbr[0]), _ptr(self._nbr[1]),
+                                  _ptr(sh.valid.x), _ptr(sh.valid.off),
+                                  1 if spec.update_type == "mse_avg" else 0, spec.verification_threshold,
+                                  spec.performance_threshold)
+            _lib.check(self.lib.fm_gossip(C.byref(a), self._stream()), "gossip")
+            self.launches += 1
+        if self.comm.is_dist:
+            self.comm.sum_(self._barrier_token())          # peers done reading before the next snapshot
+
+    def synchronize(self) -> None:
+        torch.cuda.synchronize(self.device)

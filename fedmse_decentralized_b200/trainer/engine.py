@@ -195,7 +195,7 @@ class FederationEngine:
             with tm.phase("evaluate"):
                 auc_dev, auc64, lat = be.evaluate(st, sh, self.model_type, want_latents, cfg.metric)
         # ---- single readback of the round's results --------------------------------
-        a = int(agg_pos.item()) if agg_pos is not None else -1
+        a = int(agg_pos[0]) if agg_pos is not None else -1
         aggregator = ctl.sel[a] if a >= 0 else -1
         if aggregator >= 0:
             self.agg_count_host[aggregator] += 1

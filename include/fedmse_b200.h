@@ -1,0 +1,194 @@
+/* fedmse_b200 -- C ABI of the sm_100a kernels and the device runtime.
+ *
+ * Every entry point takes raw device pointers plus the CUDA stream to launch on
+ * (as a void*; 0 = default stream), launches asynchronously and returns a
+ * cudaError_t value as int (0 = success).  No entry point synchronises the
+ * stream.  Unless stated otherwise an entry point allocates nothing: all
+ * buffers, including scratch, belong to the caller.  Python binds these with
+ * ctypes (fedmse_decentralized_b200/ops/_lib.py); any C/C++ host can link them.
+ *
+ * Data conventions: every data matrix is fp32 row-major with a row pitch of
+ * FM_XP (128) floats, zero padded beyond the 115 features.  A model is a packed
+ * fp32 row of FM_P_PAD floats (the 8 state_dict tensors back to back).  Rows of
+ * many clients are concatenated and addressed through int32 offset tables
+ * off[clients + 1].
+ */
+#ifndef FEDMSE_B200_H
+#define FEDMSE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FM_D 115
+#define FM_H 27
+#define FM_Z 7
+#define FM_XP 128
+#define FM_NP 6764
+#define FM_P_PAD 6784
+#define FM_MAX_WORLD 16
+#define FM_MAX_SEL 4096
+
+/* ---- T1: persistent per-client local training -----------------------------------------
+ * One CTA per selected client runs the whole `ClientTrainer.run` call on chip: forward,
+ * SAE/AE loss, backward, FedProx term, Adam, per-epoch validation, best-epoch snapshot and
+ * early stop (reference: src/Trainer/client_trainer.py:360-419,
+ * src/Model/Shrink_Autoencoder.py:152-163).  Weights and Adam moments stay in shared memory
+ * for all epochs; batches are streamed with bulk async copies. */
+typedef struct FmTrainArgs {
+    float* params;            /* [C][P_PAD] in/out */
+    float* adam_m;            /* [C][P_PAD] in/out */
+    float* adam_v;            /* [C][P_PAD] in/out */
+    int32_t* adam_t;          /* [C] in/out optimiser step count */
+    const float* anchor;      /* [C][P_PAD] FedProx anchor (read only when mu != 0) */
+    float* best;              /* [C][P_PAD] out: weights of the best-validation epoch */
+    float* loss_log;          /* [C][log_stride][2] out: (train, valid) loss per epoch */
+    int32_t* epochs_run;      /* [C] out */
+    int32_t* trained_rounds;  /* [C] in/out, incremented */
+    const float* x_train;     /* rows of local clients */
+    const int32_t* train_off; /* [C+1] */
+    const float* x_valid;     /* rows of all (global) clients */
+    const int32_t* valid_off; /* [N_global+1] */
+    const int32_t* sel_local; /* [n_sel] local client indices to train */
+    int32_t n_sel;
+    int32_t first_client;     /* global id of local client 0 */
+    int32_t epochs;
+    int32_t batch;            /* rows per step, <= 32 */
+    int32_t patience;
+    int32_t log_stride;
+    float lr;
+    float shrink_lambda;      /* 0 => plain AE loss */
+    float fedprox_mu;         /* 0 => no proximal term */
+} FmTrainArgs;
+int fm_train_clients(const FmTrainArgs* args, void* stream);
+
+/* ---- row scoring forward (shared by T2 vote/merge scoring, T3 verification, T4 evaluation) --
+ * For every tile {slot, row0, nrows<=64, out0}: run the model of `slot` over rows
+ * X[row0 .. row0+nrows) and write per-row sum of squared reconstruction error to
+ * out_sse[out0 + r] and/or the latent to out_lat[(out0 + r) * 8 + i].
+ * Model of a slot: slot_client ? slab[(slot_client[slot] - first_client)] : slab[slot];
+ * slots whose client is not in [first_client, first_client + n_local) are skipped.
+ * (reference: the forward passes of client_trainer.py:208-247, :115-130,
+ * model_verifier.py:86-99, evaluator.py:56-94). */
+typedef struct FmScoreArgs {
+    const float* slab;          /* [n_local][P_PAD] (or a single model row with n_local = 1) */
+    const int32_t* slot_client; /* [n_slots] global client id per slot, or NULL = identity (local) */
+    int32_t first_client;
+    int32_t n_local;
+    const float* X;             /* data rows, pitch FM_XP */
+    const int32_t* tiles;       /* [n_tiles][4] = {slot, row0, nrows, out0} */
+    int32_t n_tiles;
+    float* out_sse;             /* or NULL */
+    float* out_lat;             /* or NULL; 8 floats per row (7 latents + 0) */
+} FmScoreArgs;
+int fm_score_rows(const FmScoreArgs* args, void* stream);
+
+/* Column-normalise a vote matrix: out = (V - mean) / (unbiased std + 1e-8)
+ * (reference: client_trainer.py:221-223).  V and out are [rows][FM_XP]; out is caller scratch. */
+int fm_vote_normalise(const float* V, int32_t rows, float* out, void* stream);
+
+/* scores[slot] = jitter[slot] * mean over `chunk`-row blocks of (sum sse / (rows_in_block * D)).
+ * sse is laid out [n_slots][rows]; chunk <= 0 means one block.  Slots with skip[slot] != 0 or
+ * whose client is not local get 0 (the caller sums over ranks).
+ * (reference: client_trainer.py:226-247; with chunk = 0 the full-batch MSE of :123). */
+int fm_chunk_mean(const float* sse, int32_t n_slots, int32_t rows, int32_t chunk, const float* jitter,
+                  const int32_t* slot_client, int32_t first_client, int32_t n_local, int32_t skip_slot,
+                  float* scores, void* stream);
+
+/* ---- election (reference: client_trainer.py:262-285, main.py:284-288) --------------------
+ * agg_pos[0] = argmin over positions p != voter_pos with agg_count[sel[p]] < max_agg of
+ * scores[p] (NaN = +inf, ties: first); -1 if none.  agg_pos[1] = the elected global id or -1. */
+int fm_elect(const float* scores, const int32_t* sel, int32_t n_sel, int32_t voter_pos,
+             const int32_t* agg_count, int32_t max_agg, int32_t* agg_pos, void* stream);
+
+/* ---- T2 merge: weights + weighted parameter reduction with in-kernel peer loads ----------
+ * theta = sum_k w_k * model(sel[k]), where model(g) is read from the owner rank's slab through
+ * peer_slabs[owner] (P2P over NVLink for remote owners).  Weights: uniform (mode 0) or
+ * normalised 1/mse (mode 1), with the reference's aliasing quirk when compat != 0
+ * (client_trainer.py:107-130).  Also performs the aggregator's side effects:
+ * agg_count[aggregator]++ and, on the owning rank, params[aggregator] = theta.
+ * No-op when agg_pos[0] < 0. */
+typedef struct FmMergeArgs {
+    const float* const* peer_slabs; /* device array [world] of slab base pointers (own rank included) */
+    int32_t world;
+    int32_t rank;
+    int32_t n_global;
+    const int32_t* sel;             /* [n_sel] global ids */
+    int32_t n_sel;
+    const float* mse;               /* [n_sel] or NULL for mode 0 */
+    int32_t mode;                   /* 0 avg/fedprox, 1 mse_avg */
+    int32_t compat;
+    const int32_t* agg_pos;         /* device int[2] from fm_elect */
+    int32_t* agg_count;             /* [n_global] */
+    float* theta;                   /* [P_PAD] out */
+    float* weights_out;             /* [n_sel] out (diagnostics), or NULL */
+} FmMergeArgs;
+int fm_merge(const FmMergeArgs* args, void* stream);
+
+/* ---- T3 verification gate + model update (reference: model_verifier.py:29-99,
+ * client_trainer.py:174-206).  One CTA per local client c != aggregator:
+ *   perf = 1 / (1 + mean(sse rows of c) / D); first time: accept;
+ *   else accept iff sum_k ||hist_k - theta_k||_2 <= thr_change and perf - hist_perf >= -thr_perf;
+ *   history <- theta (always); on accept params <- theta, anchor <- theta, rejected = 0;
+ *   else rejected++.
+ * sse rows of client c are sse[sse_off[c] .. sse_off[c+1]) (sse_off may describe one shared
+ * segment for all clients). */
+typedef struct FmVerifyArgs {
+    float* params; float* anchor; float* hist; float* hist_perf; int32_t* hist_valid; int32_t* rejected;
+    int32_t n_local; int32_t first_client;
+    const float* theta; const int32_t* agg_pos;
+    const float* sse; const int32_t* sse_off; int32_t shared_segment; /* 1: every client uses segment 0 */
+    float thr_change; float thr_perf;
+    float* out_change; float* out_dperf; /* [n_local] diagnostics or NULL */
+} FmVerifyArgs;
+int fm_verify_update(const FmVerifyArgs* args, void* stream);
+
+/* ---- T4 anomaly score -> ROC-AUC (reference: evaluator.py:50-119, Centroid.py:15-35) ------
+ * One CTA per local client.  mode 0 (autoencoder): score = sse / D.  mode 1 (hybrid):
+ * score = || (z - mean(z_train)) / std(z_train) ||_2 with population std, 0 -> 1.
+ * Non-finite scores are mapped like numpy.nan_to_num.  AUC is the tie-aware Mann-Whitney
+ * statistic computed exactly in integers after an in-shared-memory bitonic sort. */
+typedef struct FmAucArgs {
+    int32_t mode; int32_t n_local;
+    const float* test_sse; const float* test_lat; const float* labels; const int32_t* test_off;
+    const float* train_lat; const int32_t* train_off;
+    float* scores_out;  /* [test rows] or NULL */
+    double* auc;        /* [n_local] */
+    int32_t max_rows;   /* max test rows of any client (sizes shared memory) */
+} FmAucArgs;
+int fm_auc(const FmAucArgs* args, void* stream);
+
+/* ---- gossip merge (per-client T2; reference API client_trainer.py:141-172) ---------------
+ * One CTA per selected local client i: candidates = nbr_idx[nbr_off[i] .. nbr_off[i+1]) (self
+ * first); weight_j = 1/MSE(model_j on client i's validation rows) normalised (mode 1) or
+ * uniform (mode 0); theta_i = sum w_j model_j read through peer_slabs; then the verification
+ * gate of fm_verify_update on client i's own validation rows.  Reads `src` slabs, writes
+ * `params` (must be distinct buffers: synchronous gossip). */
+typedef struct FmGossipArgs {
+    const float* const* peer_src;   /* [world] snapshot slabs to read */
+    int32_t world; int32_t rank; int32_t n_global;
+    float* params; float* anchor; float* hist; float* hist_perf; int32_t* hist_valid; int32_t* rejected;
+    int32_t n_local; int32_t first_client;
+    const int32_t* sel_local; int32_t n_sel;
+    const int32_t* nbr_off; const int32_t* nbr_idx;  /* CSR over global ids, indexed by global id */
+    const float* x_valid; const int32_t* valid_off;
+    int32_t mode; float thr_change; float thr_perf;
+} FmGossipArgs;
+int fm_gossip(const FmGossipArgs* args, void* stream);
+
+/* ---- runtime: peer-mapped slabs (cudaMalloc + CUDA IPC), used for the parameter slab ------ */
+int fm_slab_alloc(uint64_t bytes, void** ptr);                 /* cudaMalloc, zeroed */
+int fm_slab_free(void* ptr);
+int fm_ipc_get_handle(void* ptr, uint8_t handle[64]);
+int fm_ipc_open_handle(const uint8_t handle[64], void** ptr);
+int fm_ipc_close_handle(void* ptr);
+int fm_enable_peer_access(int32_t peer_device);
+const char* fm_error_string(int code);
+int fm_device_info(int32_t* sm_count, int32_t* max_smem_optin, int32_t* cc_major, int32_t* cc_minor);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FEDMSE_B200_H */

@@ -1,0 +1,171 @@
+"""GPU numerics: every sm_100a kernel against the plain-PyTorch fp32 oracle of the same op."""
+import copy
+import random
+
+import numpy as np
+import pytest
+import torch
+
+from fedmse_decentralized_b200.layout import DEFAULT_LAYOUT as L
+from fedmse_decentralized_b200.ops import oracle
+from fedmse_decentralized_b200.ops.backend import MergeSpec, OracleBackend, RoundControl
+from fedmse_decentralized_b200.ops.oracle import TrainHP
+
+from helpers import assert_close, make_cfg, make_engine, make_shards
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    return torch.device("cuda", 0)
+
+
+def _pair(tiny_clients, tmp_path, dev, model_type="hybrid", update_type="mse_avg", **kw):
+    cfg = make_cfg(tmp_path, **kw)
+    e_ref = make_engine(cfg, make_shards(tiny_clients, "cpu"), model_type, update_type, "oracle")
+    e_gpu = make_engine(cfg, make_shards(tiny_clients, dev), model_type, update_type, "cuda")
+    assert_close(e_gpu.state.params, e_ref.state.params, 0, 0, "init params")
+    return e_ref, e_gpu
+
+
+@pytest.mark.parametrize("model_type,update_type", [("hybrid", "avg"), ("autoencoder", "avg"),
+                                                    ("hybrid", "fedprox")])
+def test_train_kernel_matches_oracle(tiny_clients, tmp_path, dev, model_type, update_type):
+    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, model_type, update_type, epoch=3, local_patience=5)
+    if update_type == "fedprox":   # make the proximal term non-trivial
+        for e in (e_ref, e_gpu):
+            e.state.anchor.mul_(0.9)
+            e.hp.fedprox_mu = 0.05
+    sel = [0, 2, 3, 5]
+    ctl = RoundControl(0, sel, 0, [1.0] * 4, sel[0], -1)
+    e_gpu.backend.begin_round(ctl)
+    for e in (e_ref, e_gpu):
+        e.backend.train(e.state, e.sh, sel, e.hp)
+    torch.cuda.synchronize()
+    assert e_gpu.state.epochs_run.tolist() == e_ref.state.epochs_run.tolist()
+    assert e_gpu.state.adam_t.tolist() == e_ref.state.adam_t.tolist()
+    n = int(e_ref.state.epochs_run[0])
+    assert_close(e_gpu.state.loss_log[sel, :n], e_ref.state.loss_log[sel, :n], 2e-4, 1e-6, "loss log")
+    assert_close(e_gpu.state.params, e_ref.state.params, 2e-3, 2e-5, "params after training")
+    assert_close(e_gpu.state.best, e_ref.state.best, 2e-3, 2e-5, "best-epoch snapshot")
+    assert_close(e_gpu.state.adam_m, e_ref.state.adam_m, 5e-3, 1e-6, "adam m")
+    # untouched clients stay bit-identical
+    assert torch.equal(e_gpu.state.params[1].cpu(), e_ref.state.params[1])
+
+
+def test_train_early_stop_and_partial_batch(tiny_clients, tmp_path, dev):
+    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "hybrid", "avg", epoch=6, local_patience=1, lr_rate=0.05)
+    sel = [1, 4]
+    ctl = RoundControl(0, sel, 0, [1.0] * 2, sel[0], -1)
+    e_gpu.backend.begin_round(ctl)
+    for e in (e_ref, e_gpu):
+        e.backend.train(e.state, e.sh, sel, e.hp)
+    assert e_gpu.state.epochs_run.tolist() == e_ref.state.epochs_run.tolist()
+    assert_close(e_gpu.state.params[sel], e_ref.state.params[sel], 5e-3, 5e-5, "params")
+
+
+def test_score_rows_matches_oracle(tiny_clients, tmp_path, dev):
+    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev)
+    be, st, sh = e_gpu.backend, e_gpu.state, e_gpu.sh
+    be._score(st.params, st.n_clients, 0, None, sh.test.x, be.tiles_test, be.test_sse, be.test_lat)
+    torch.cuda.synchronize()
+    for c in range(st.n_clients):
+        x = e_ref.sh.test.rows(c)
+        z, _ = oracle.forward(e_ref.state.params[c], x[:, :L.dim], L)
+        sse = oracle.row_sse(e_ref.state.params[c], x, L)
+        lo, hi = sh.test.off_host[c], sh.test.off_host[c + 1]
+        assert_close(be.test_sse[lo:hi], sse, 1e-4, 1e-4, f"sse client {c}")
+        assert_close(be.test_lat[lo:hi, :7], z, 1e-4, 1e-5, f"latent client {c}")
+
+
+@pytest.mark.parametrize("model_type", ["hybrid", "autoencoder"])
+def test_auc_kernel_matches_sklearn(tiny_clients, tmp_path, dev, model_type):
+    from sklearn.metrics import auc, roc_curve
+    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, model_type, "avg")
+    a_gpu, _, lat = e_gpu.backend.evaluate(e_gpu.state, e_gpu.sh, model_type, True)
+    a_ref, a64, _ = e_ref.backend.evaluate(e_ref.state, e_ref.sh, model_type, False)
+    assert_close(a_gpu, torch.tensor(a64), 0, 2e-4, "auc vs oracle")
+    # exactness of the device rank statistic against sklearn on the device's own scores
+    be, sh = e_gpu.backend, e_gpu.sh
+    e_gpu.backend.evaluate(e_gpu.state, e_gpu.sh, model_type, False, metric="classification")
+    torch.cuda.synchronize()
+    for c in range(sh.n_clients):
+        lo, hi = sh.test.off_host[c], sh.test.off_host[c + 1]
+        s = be.scores_out[lo:hi].cpu().numpy()
+        y = sh.test.y[lo:hi].cpu().numpy()
+        fpr, tpr, _ = roc_curve(y, s)
+        assert abs(auc(fpr, tpr) - float(be.auc[c])) < 1e-12
+    assert lat[0].shape == (sh.test.count(0), 7)
+
+
+def test_auc_kernel_ties_and_nonfinite(dev):
+    import ctypes as C
+    from fedmse_decentralized_b200.ops import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(1)
+    n = 1000
+    sse = torch.randint(0, 20, (n,), generator=g).float() * 115.0      # heavy ties
+    sse[5] = float("nan"); sse[6] = float("inf"); sse[7] = -0.0
+    y = (torch.rand(n, generator=g) > 0.6).float()
+    want = oracle.auc_from_scores(sse / 115.0, y)
+    d = lambda t: t.to(dev)
+    off = d(torch.tensor([0, n], dtype=torch.int32))
+    out = torch.zeros(1, dtype=torch.float64, device=dev)
+    sse_d, y_d = d(sse), d(y)
+    a = _lib.FmAucArgs(0, 1, sse_d.data_ptr(), 0, y_d.data_ptr(), off.data_ptr(), 0, 0, 0, out.data_ptr(), n)
+    _lib.check(lib.fm_auc(C.byref(a), torch.cuda.current_stream().cuda_stream))
+    assert abs(float(out[0]) - want) < 1e-12
+
+
+@pytest.mark.parametrize("update_type,compat", [("avg", True), ("mse_avg", True), ("mse_avg", False),
+                                                ("fedprox", True)])
+def test_full_round_matches_oracle(tiny_clients, tmp_path, dev, update_type, compat):
+    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "hybrid", update_type, reference_compat=compat,
+                         num_participants=0.7)
+    for r in range(3):
+        random.seed(100 + r); torch.manual_seed(100 + r)
+        ctl = e_ref.make_control(r)
+        res_ref = e_ref.run_round(r, copy.deepcopy(ctl))
+        res_gpu = e_gpu.run_round(r, copy.deepcopy(ctl))
+        assert res_gpu.aggregator == res_ref.aggregator and res_ref.aggregator >= 0
+        assert res_gpu.epochs_run == res_ref.epochs_run
+        assert [v["is_verified"] for v in res_gpu.verification] == [v["is_verified"] for v in res_ref.verification]
+        assert_close(e_gpu.backend.theta, e_ref.state.params[res_ref.aggregator], 3e-3, 3e-5, f"theta r{r}")
+        assert_close(e_gpu.state.params, e_ref.state.params, 3e-3, 3e-5, f"params r{r}")
+        assert_close(e_gpu.state.hist_perf, e_ref.state.hist_perf, 1e-4, 1e-6, f"hist perf r{r}")
+        assert_close(torch.tensor(res_gpu.client_metrics), torch.tensor(res_ref.client_metrics), 0, 2e-3, "auc")
+    assert e_gpu.state.agg_count.tolist() == e_ref.state.agg_count.tolist()
+    assert e_gpu.backend.launches > 0
+
+
+def test_vote_scores_and_election(tiny_clients, tmp_path, dev):
+    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev)
+    sel = [4, 1, 3, 0]
+    ctl = RoundControl(0, sel, 0, [1.0, 1.00005, 0.99995, 1.00002], sel[0], 5)
+    e_gpu.backend.begin_round(ctl)
+    s_ref = e_ref.backend.vote_scores(e_ref.state, e_ref.sh, ctl, e_ref.spec)
+    s_gpu = e_gpu.backend.vote_scores(e_gpu.state, e_gpu.sh, ctl, e_gpu.spec)
+    assert_close(s_gpu, s_ref, 1e-4, 1e-6, "vote scores")
+    assert float(s_gpu[0]) == 0.0
+    # quota: exclude the best candidate
+    best = int(torch.argmin(torch.where(s_ref > 0, s_ref, torch.full_like(s_ref, 1e30))))
+    for e in (e_ref, e_gpu):
+        e.state.agg_count[sel[best]] = 3
+    a_ref = e_ref.backend.elect(e_ref.state, s_ref, ctl, e_ref.spec)
+    a_gpu = e_gpu.backend.elect(e_gpu.state, s_gpu, ctl, e_gpu.spec)
+    assert a_gpu.tolist() == a_ref.tolist() and a_ref[0] != best
+
+
+def test_gossip_matches_oracle(tiny_clients, tmp_path, dev):
+    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "hybrid", "mse_avg", aggregation="gossip",
+                         topology="ring", num_participants=1.0, epoch=1)
+    for r in range(2):
+        random.seed(7 + r)
+        sel = random.sample(range(6), 6)
+        ctl = RoundControl(r, sel, -1, [1.0] * 6, sel[0], -1)
+        res_ref = e_ref.run_round(r, copy.deepcopy(ctl))
+        res_gpu = e_gpu.run_round(r, copy.deepcopy(ctl))
+        assert_close(e_gpu.state.params, e_ref.state.params, 3e-3, 3e-5, f"gossip params r{r}")
+        assert e_gpu.state.rejected.tolist() == e_ref.state.rejected.tolist()
+        assert_close(torch.tensor(res_gpu.client_metrics), torch.tensor(res_ref.client_metrics), 0, 2e-3, "auc")
