@@ -1,0 +1,301 @@
+#!/usr/bin/env python
+"""Flagship benchmark: federated rounds of SAE-CEN + MSEAvg on synthetic N-BaIoT-shaped traffic.
+
+Config (BASELINE.json #4 shape, reference round semantics of src/main.py:267-340): 125 simulated
+clients per GPU (weak scaling: N GPUs -> 125*N clients), 50 % participation, 5 local epochs with
+local early stop (patience 1), batch 12, lr 1e-3, shrink_lambda 5 (the reference's checked-in
+hyper-parameters), hybrid model, mse_avg merge, verification gate, evaluation of every client each
+round.  A "step" is one full federated round.
+
+metric: local training samples per second = sum over selected clients of
+(train rows + validation rows) x epochs actually run, divided by the whole round time (vote, merge,
+verification and evaluation included), aggregated over all GPUs.  rounds_per_sec is reported next to it.
+
+  python bench.py --gpus 1 --steps 10 --warmup 3
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+         --master-port 29500 bench.py --gpus 8 --steps 10 --warmup 3
+  python bench.py --impl reference --gpus 1 --steps 3 --warmup 3
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import random
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+# reference as-is, local epoch ~6.1k rows/s (hybrid/avg, CPU box of the survey);
+# the only throughput number BASELINE.md has (it publishes none for any GPU).
+BASELINE_LOCAL_SAMPLES_PER_SEC = 6.1e3
+
+
+class ClockSampler:
+    """Samples nvidia-smi SM clocks / throttle reasons in the background during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) >= 9:
+                for nm, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def build_world(args):
+    import torch
+    from fedmse_decentralized_b200.parallel import block_partition, init_distributed
+    comm = init_distributed()
+    if comm.world != args.gpus:
+        if comm.rank == 0:
+            print(f"[bench] WORLD_SIZE={comm.world} but --gpus {args.gpus}: launch with torchrun "
+                  f"--nproc-per-node {args.gpus}", file=sys.stderr)
+        if comm.world == 1 and args.gpus > 1:
+            sys.exit(2)
+    n_global = args.clients_per_gpu * comm.world
+    first, cnt = block_partition(n_global, comm.world, comm.rank)
+    return comm, n_global, first, cnt
+
+
+def synth(n_global, owned, seed):
+    from fedmse_decentralized_b200.data import NBAIOT_SPEC, make_clients
+    return make_clients(n_global, NBAIOT_SPEC, seed=seed, full=owned)
+
+
+def seed_all(seed):
+    import numpy as np
+    import torch
+    random.seed(seed); np.random.seed(seed); torch.manual_seed(seed)
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    from fedmse_decentralized_b200 import ExperimentConfig
+    from fedmse_decentralized_b200.data import ShardStore, prepare_client, pool_dev_set
+    from fedmse_decentralized_b200.data.shards import Segmented
+    from fedmse_decentralized_b200.trainer import FederationEngine
+
+    comm, n_global, first, cnt = build_world(args)
+    dev = comm.device
+    owned = range(first, first + cnt)
+    t0 = time.time()
+    raw = synth(n_global, owned, args.seed)
+    seed_all(args.seed)
+    rng = np.random.default_rng(args.seed)
+    prepared = []
+    for i, cl in enumerate(raw):
+        normal = cl.normal[rng.permutation(len(cl.normal))]
+        abn = cl.abnormal[rng.permutation(len(cl.abnormal))] if i in owned else cl.abnormal
+        prepared.append(prepare_client(cl.name, normal, abn, cl.test_normal if i in owned else None, True))
+    devset = pool_dev_set(prepared, sampler=lambda a, n: a[rng.permutation(len(a))[:n]])
+    local = prepared[first:first + cnt]
+    sh_host = ShardStore.build(local, devset, first_client=first, n_global=n_global)
+    sh_host.valid = Segmented.from_list([c.valid for c in prepared])
+    sh = sh_host.to(dev)
+    # pinned host copies of what an IoT gateway would deliver fresh every round (local training data)
+    pin_train = sh_host.train.x.pin_memory()
+    v0, v1 = sh_host.valid.off_host[first], sh_host.valid.off_host[first + cnt]
+    pin_valid = sh_host.valid.x[v0:v1].pin_memory()
+    cfg = ExperimentConfig(num_participants=args.participation, epoch=args.epochs, lr_rate=1e-3, shrink_lambda=5,
+                           network_size=n_global, batch_size=12, backend="cuda", write_latents=False,
+                           save_client_models=False, reference_compat=True)
+    eng = FederationEngine(cfg, sh, args.model, args.update, comm=comm, names_global=[c.name for c in prepared])
+    setup_s = time.time() - t0
+    result_bytes = 8 * cnt + 4 * cnt * 2 + 8   # AUC (f64) + epochs_run + rejected (i32) + aggregator
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        comm.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(n_rounds, r0, with_h2d):
+        """Returns (device ms over n_rounds [max over ranks], wall s, samples, launches)."""
+        launches0 = eng.backend.launches
+        samples = 0
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0 = time.perf_counter()
+        e0.record()
+        for r in range(r0, r0 + n_rounds):
+            if with_h2d:    # this round's inputs: fresh local traffic from pinned host memory
+                sh.train.x.copy_(pin_train, non_blocking=True)
+                sh.valid.x[v0:v1].copy_(pin_valid, non_blocking=True)
+            res = eng.run_round(r)              # includes the device->host read of the round's results
+            samples += res.samples
+        e1.record()
+        sync_all()
+        wall = time.perf_counter() - w0
+        ms = torch.tensor([e0.elapsed_time(e1), wall * 1e3, float(samples)], dtype=torch.float64, device=dev)
+        mx = comm.max_(ms.clone())
+        tot = comm.sum_(ms.clone())
+        return float(mx[0]), float(mx[1]) / 1e3, int(tot[2]), eng.backend.launches - launches0, res
+
+    timed(args.warmup, 0, False)
+    sampler = ClockSampler(torch.cuda.current_device())
+    if comm.rank == 0:
+        sampler.start()
+    ms, wall, samples, launches, res = timed(args.steps, args.warmup, False)
+    ms_e, wall_e, samples_e, _, res_e = timed(args.steps, args.warmup + args.steps, True)
+    clocks = sampler.stop() if comm.rank == 0 else None
+    phases = {k: round(v["mean_ms"], 4) for k, v in eng.timer.summary().items()}
+    if comm.rank == 0:
+        value = samples / (ms / 1e3)
+        e2e = samples_e / wall_e
+        h2d = (pin_train.numel() + pin_valid.numel()) * 4 + eng.backend.ctl_dev.numel() * 4
+        out = {
+            "metric": "local_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": comm.world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": value / BASELINE_LOCAL_SAMPLES_PER_SEC, "dtype": "fp32", "data": "synthetic",
+            "impl": "ours",
+            "rounds_per_sec": args.steps / (ms / 1e3),
+            "config": {"model": f"SAE-CEN 115-27-7 ({args.model}) + {args.update}",
+                       "scenario": "N-BaIoT-shaped synthetic, reference round loop (elect/merge/broadcast/verify/evaluate)",
+                       "clients": n_global, "clients_per_gpu": args.clients_per_gpu,
+                       "global_batch": 12, "seq_len": 115, "epochs": args.epochs, "local_patience": 1,
+                       "participation": args.participation, "lr": 1e-3, "shrink_lambda": 5,
+                       "parallelism": f"client-parallel dp{comm.world} (one CTA per client, clients block-partitioned over GPUs)",
+                       "l2": f"inputs larger than L2: {sh.nbytes() / 2**20:.0f} MiB of shards per GPU streamed every round",
+                       "baseline_ref": "BASELINE.md sec.3: reference local epoch 6.1k rows/s on the survey's CPU (no GPU number is published)"},
+            "e2e": {"value": e2e, "unit": "samples/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": result_bytes, "ms_per_step": wall_e * 1e3 / args.steps,
+                    "rounds_per_sec": args.steps / wall_e,
+                    "what": "engine.run_round() per step incl. pinned-host upload of the local train+valid shards "
+                            "and the control block, and the host read-back of AUC / epochs / verdicts"},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "samples_per_step": samples / args.steps,
+            "wall_ms_per_step": wall * 1e3 / args.steps,
+            "phases_ms": phases,
+            "auc_mean_last_round": sum(res_e.client_metrics) / len(res_e.client_metrics),
+            "setup_s": round(setup_s, 1),
+        }
+        print(json.dumps(out))
+    comm.barrier()
+
+
+def run_reference(args):
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))
+    import ref_harness
+    why = ref_harness.available()
+    if why:
+        print(json.dumps({"impl": "reference", "unavailable": why}))
+        return
+    import torch
+    import torch.distributed as dist
+    comm, n_global, first, cnt = build_world(args)
+    dev = comm.device
+    owned = range(first, first + cnt)
+    raw = synth(n_global, owned, args.seed)
+    seed_all(args.seed)
+    cfg = {"model_type": args.model, "update_type": args.update, "epoch": args.epochs, "batch_size": 12,
+           "lr_rate": 1e-3, "shrink_lambda": 5, "patience": 1, "num_participants": args.participation}
+    fed = ref_harness.ReferenceFederation(raw, owned, cfg, comm.world, comm.rank, dev)
+
+    def sync_all():
+        if dev.type == "cuda":
+            torch.cuda.synchronize(dev)
+        comm.barrier()
+
+    for r in range(args.warmup):
+        fed.run_round(r)
+    sampler = ClockSampler(torch.cuda.current_device() if dev.type == "cuda" else 0)
+    if comm.rank == 0:
+        sampler.start()
+    fed.samples = 0
+    sync_all()
+    if dev.type == "cuda":
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+    w0 = time.perf_counter()
+    for r in range(args.warmup, args.warmup + args.steps):
+        metrics = fed.run_round(r)
+    if dev.type == "cuda":
+        e1.record()
+    sync_all()
+    wall = time.perf_counter() - w0
+    ms_dev = e0.elapsed_time(e1) if dev.type == "cuda" else wall * 1e3
+    t = torch.tensor([ms_dev, wall * 1e3, float(fed.samples)], dtype=torch.float64, device=dev)
+    mx = comm.max_(t.clone()); tot = comm.sum_(t.clone())
+    clocks = sampler.stop() if comm.rank == 0 else None
+    fed.close()
+    if comm.rank == 0:
+        ms, samples = float(mx[0]), float(tot[2])
+        value = samples / (ms / 1e3)
+        print(json.dumps({
+            "impl": "reference", "metric": "local_samples_per_sec", "value": value, "unit": "samples/s",
+            "n_gpus": comm.world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": value / BASELINE_LOCAL_SAMPLES_PER_SEC,
+            "dtype": "fp32", "data": "synthetic", "rounds_per_sec": args.steps / (ms / 1e3),
+            "config": {"model": f"SAE-CEN 115-27-7 ({args.model}) + {args.update}", "clients": n_global,
+                       "clients_per_gpu": args.clients_per_gpu, "global_batch": 12, "seq_len": 115,
+                       "epochs": args.epochs, "local_patience": 1, "participation": args.participation,
+                       "parallelism": f"reference loop, clients block-partitioned, NCCL all_gather of models, dp{comm.world}"},
+            "e2e": {"value": samples / (float(mx[1]) / 1e3), "unit": "samples/s",
+                    "what": "the reference's loop is end to end by construction (per-batch H2D from pinned "
+                            "DataLoaders, .item() every step)"},
+            "clocks": clocks, "samples_per_step": samples / args.steps,
+            "auc_mean_last_round": sum(metrics) / len(metrics)}))
+    comm.barrier()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--clients-per-gpu", type=int, default=125)
+    ap.add_argument("--epochs", type=int, default=5)
+    ap.add_argument("--participation", type=float, default=0.5)
+    ap.add_argument("--model", default="hybrid", choices=["hybrid", "autoencoder"])
+    ap.add_argument("--update", default="mse_avg", choices=["avg", "fedprox", "mse_avg"])
+    ap.add_argument("--seed", type=int, default=1234)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)   # timing rule: at least 3 warm-up steps, both arms
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+    from fedmse_decentralized_b200.parallel import shutdown
+    shutdown()
+
+
+if __name__ == "__main__":
+    main()

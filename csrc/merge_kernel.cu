@@ -51,11 +51,18 @@ __global__ void elect_kernel(const float* __restrict__ scores, const int* __rest
 constexpr int MNT = 256;
 
 __global__ void __launch_bounds__(MNT) merge_kernel(const FmMergeArgs a) {
-    extern __shared__ float wts[];            // [n_sel]
+    extern __shared__ __align__(16) unsigned char msm[];
+    const float** srcs = reinterpret_cast<const float**>(msm);                       // [n_sel] source rows
+    float* wts = reinterpret_cast<float*>(msm + (size_t)a.n_sel * sizeof(float*));   // [n_sel]
     __shared__ double red[34];
     const int ap = a.agg_pos[0];
     if (ap < 0) return;
     const int tid = threadIdx.x, n = a.n_sel;
+    for (int k = tid; k < n; k += MNT) {
+        int r, l;
+        owner_of(a.sel[k], a.n_global, a.world, r, l);
+        srcs[k] = a.peer_slabs[r] + (size_t)l * P_PAD;
+    }
     // ---- weights (every CTA recomputes them: n_sel is small) ----
     if (a.mode == 0) {
         for (int k = tid; k < n; k += MNT) wts[k] = 1.f / (float)n;
@@ -87,14 +94,15 @@ __global__ void __launch_bounds__(MNT) merge_kernel(const FmMergeArgs a) {
     if (p < P_PAD) {
         float acc = 0.f;
         if (p < NP) {
-            for (int k = 0; k < n; ++k) {
-                const float wk = wts[k];
-                if (wk == 0.f) continue;
-                int r, l;
-                owner_of(a.sel[k], a.n_global, a.world, r, l);
-                const float* src = a.peer_slabs[r] + (size_t)l * P_PAD;
-                acc = fmaf(wk, src[p], acc);
+            int k = 0;
+            for (; k + 8 <= n; k += 8) {            // 8 independent (possibly peer) loads in flight per thread
+                float v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = srcs[k + u][p];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) acc = fmaf(wts[k + u], v[u], acc);
             }
+            for (; k < n; ++k) acc = fmaf(wts[k], srcs[k][p], acc);
         }
         a.theta[p] = acc;
     }
@@ -171,7 +179,7 @@ extern "C" int fm_merge(const FmMergeArgs* args, void* stream) {
     using namespace fm;
     if (args->n_sel <= 0 || args->n_sel > FM_MAX_SEL) return (int)cudaErrorInvalidValue;
     const int grid = (P_PAD + MNT - 1) / MNT;
-    merge_kernel<<<grid, MNT, args->n_sel * sizeof(float), (cudaStream_t)stream>>>(*args);
+    merge_kernel<<<grid, MNT, args->n_sel * (sizeof(float) + sizeof(float*)), (cudaStream_t)stream>>>(*args);
     return (int)cudaGetLastError();
 }
 

@@ -69,42 +69,54 @@ __global__ void __launch_bounds__(SNT, 2) score_rows_kernel(const FmScoreArgs a,
     }
 }
 
-// ---- vote matrix normalisation -------------------------------------------------------------------
+// ---- vote matrix normalisation: block = 32 columns x 8 row lanes -----------------------------
 __global__ void vote_normalise_kernel(const float* __restrict__ V, int rows, float* __restrict__ out) {
-    const int col = blockIdx.x * blockDim.x + threadIdx.x;
-    if (col >= XP) return;
-    if (col >= D) { for (int r = 0; r < rows; ++r) out[(size_t)r * XP + col] = 0.f; return; }
+    __shared__ double red[8][33];
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int col = blockIdx.x * 32 + tx;
+    const bool live = col < D;
     double s = 0.0;
-    for (int r = 0; r < rows; ++r) s += (double)V[(size_t)r * XP + col];
-    const double mean = s / rows;
+    if (live) for (int r = ty; r < rows; r += 8) s += (double)V[(size_t)r * XP + col];
+    red[ty][tx] = s;
+    __syncthreads();
+    double mean = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) mean += red[i][tx];
+    mean /= rows;
+    __syncthreads();
     double q = 0.0;
-    for (int r = 0; r < rows; ++r) { const double dlt = (double)V[(size_t)r * XP + col] - mean; q += dlt * dlt; }
+    if (live) for (int r = ty; r < rows; r += 8) { const double dl = (double)V[(size_t)r * XP + col] - mean; q += dl * dl; }
+    red[ty][tx] = q;
+    __syncthreads();
+    double var = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) var += red[i][tx];
     const float meanf = (float)mean;
-    const float stdf = (float)sqrt(q / (double)(rows - 1)) + 1e-8f;   // unbiased, as torch.std
-    for (int r = 0; r < rows; ++r) out[(size_t)r * XP + col] = (V[(size_t)r * XP + col] - meanf) / stdf;
+    const float stdf = (float)sqrt(var / (double)(rows - 1)) + 1e-8f;   // unbiased, as torch.std
+    for (int r = ty; r < rows; r += 8)
+        out[(size_t)r * XP + col] = live ? (V[(size_t)r * XP + col] - meanf) / stdf : 0.f;
 }
 
-// ---- chunked mean of per-row SSE: one warp per slot ---------------------------------------------
-__global__ void chunk_mean_kernel(const float* __restrict__ sse, int n_slots, int rows, int chunk,
+// ---- chunked mean of per-row SSE: one block per slot ---------------------------------------------
+__global__ void __launch_bounds__(256) chunk_mean_kernel(const float* __restrict__ sse, int n_slots, int rows, int chunk,
                                   const float* __restrict__ jitter, const int* __restrict__ slot_client,
                                   int first_client, int n_local, int skip_slot, float* __restrict__ scores) {
-    const int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const int lane = threadIdx.x & 31;
-    if (slot >= n_slots) return;
+    __shared__ double red[34];
+    const int slot = blockIdx.x, tid = threadIdx.x;
     const int g = slot_client ? slot_client[slot] : first_client + slot;
     const int c = g - first_client;
-    if (slot == skip_slot || c < 0 || c >= n_local) { if (lane == 0) scores[slot] = 0.f; return; }
+    if (slot == skip_slot || c < 0 || c >= n_local) { if (tid == 0) scores[slot] = 0.f; return; }
     if (chunk <= 0 || chunk > rows) chunk = rows;
     const float* s = sse + (size_t)slot * rows;
     float acc = 0.f; int nchunks = 0;
     for (int r0 = 0; r0 < rows; r0 += chunk, ++nchunks) {
         const int n = min(chunk, rows - r0);
-        float part = 0.f;
-        for (int r = lane; r < n; r += 32) part += s[r0 + r];
-        part = warp_sum(part);
-        acc += part / ((float)n * (float)D);
+        double part = 0.0;
+        for (int r = tid; r < n; r += 256) part += (double)s[r0 + r];
+        const double tot = block_sum<double>(part, red);
+        acc += (float)(tot / ((double)n * (double)D));
     }
-    if (lane == 0) scores[slot] = (acc / (float)nchunks) * (jitter ? jitter[slot] : 1.f);
+    if (tid == 0) scores[slot] = (acc / (float)nchunks) * (jitter ? jitter[slot] : 1.f);
 }
 
 }  // namespace fm
@@ -126,7 +138,7 @@ extern "C" int fm_score_rows(const FmScoreArgs* args, void* stream) {
 
 extern "C" int fm_vote_normalise(const float* V, int32_t rows, float* out, void* stream) {
     if (rows <= 0) return 0;
-    fm::vote_normalise_kernel<<<4, 32, 0, (cudaStream_t)stream>>>(V, rows, out);
+    fm::vote_normalise_kernel<<<4, dim3(32, 8), 0, (cudaStream_t)stream>>>(V, rows, out);
     return (int)cudaGetLastError();
 }
 
@@ -134,8 +146,7 @@ extern "C" int fm_chunk_mean(const float* sse, int32_t n_slots, int32_t rows, in
                              const int32_t* slot_client, int32_t first_client, int32_t n_local, int32_t skip_slot,
                              float* scores, void* stream) {
     if (n_slots <= 0) return 0;
-    const int wpb = 4;
-    fm::chunk_mean_kernel<<<(n_slots + wpb - 1) / wpb, wpb * 32, 0, (cudaStream_t)stream>>>(
+    fm::chunk_mean_kernel<<<n_slots, 256, 0, (cudaStream_t)stream>>>(
         sse, n_slots, rows, chunk, jitter, slot_client, first_client, n_local, skip_slot, scores);
     return (int)cudaGetLastError();
 }

@@ -139,20 +139,44 @@ struct AdamStep {
     float mu;            // FedProx
 };
 
-__device__ __forceinline__ void adam_update(float* __restrict__ Ws, float* __restrict__ Ms, float* __restrict__ Vs,
-                                            const float* __restrict__ As, int idx, float g, const AdamStep& st,
-                                            float& prox_acc) {
-    float w = Ws[idx], m = Ms[idx], v = Vs[idx];
+__device__ __forceinline__ void adam1(float& w, float& m, float& v, float anchor, float g, const AdamStep& st,
+                                      float& prox_acc) {
     if (st.mu != 0.f) {
-        const float dl = w - As[idx];
+        const float dl = w - anchor;
         prox_acc = fmaf(dl, dl, prox_acc);
         g = fmaf(2.f * st.mu, dl, g);
     }
     m = fmaf(g - m, 0.1f, m);                     // exp_avg.lerp_(g, 1 - beta1)
     v = fmaf(0.001f * g, g, v * 0.999f);          // exp_avg_sq.mul_(beta2).addcmul_(g, g, 1 - beta2)
     const float denom = fmaf(sqrtf(v), st.inv_sqrt_bc2, 1e-8f);
-    w = fmaf(-st.step_size, m / denom, w);
+    w = fmaf(-st.step_size, __fdividef(m, denom), w);
+}
+
+__device__ __forceinline__ void adam_update(float* __restrict__ Ws, float* __restrict__ Ms, float* __restrict__ Vs,
+                                            const float* __restrict__ As, int idx, float g, const AdamStep& st,
+                                            float& prox_acc) {
+    float w = Ws[idx], m = Ms[idx], v = Vs[idx];
+    adam1(w, m, v, st.mu != 0.f ? As[idx] : 0.f, g, st, prox_acc);
     Ws[idx] = w; Ms[idx] = m; Vs[idx] = v;
+}
+
+// four consecutive parameters at a 16-B aligned index: vector LDS/STS, conflict-free across lanes.
+// Padding slots need no mask: their gradient is exactly 0 (zero-padded activations), so w, m, v stay 0.
+__device__ __forceinline__ void adam_update4(float* __restrict__ Ws, float* __restrict__ Ms, float* __restrict__ Vs,
+                                             const float* __restrict__ As, int idx, float4 g, const AdamStep& st,
+                                             float& prox_acc) {
+    float4 w = *reinterpret_cast<float4*>(Ws + idx);
+    float4 m = *reinterpret_cast<float4*>(Ms + idx);
+    float4 v = *reinterpret_cast<float4*>(Vs + idx);
+    float4 an = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (st.mu != 0.f) an = *reinterpret_cast<const float4*>(As + idx);
+    adam1(w.x, m.x, v.x, an.x, g.x, st, prox_acc);
+    adam1(w.y, m.y, v.y, an.y, g.y, st, prox_acc);
+    adam1(w.z, m.z, v.z, an.z, g.z, st, prox_acc);
+    adam1(w.w, m.w, v.w, an.w, g.w, st, prox_acc);
+    *reinterpret_cast<float4*>(Ws + idx) = w;
+    *reinterpret_cast<float4*>(Ms + idx) = m;
+    *reinterpret_cast<float4*>(Vs + idx) = v;
 }
 
 // Weight gradient + Adam for one linear layer: dW[n][k] = sum_b GT[n][b] * A[b][k], dbias[n] = sum_b GT[n][b].
@@ -180,11 +204,7 @@ __device__ __forceinline__ void wgrad_adam(int item0, const float* __restrict__ 
                 g.z = fmaf(gg.x, a0.z, fmaf(gg.y, a1.z, fmaf(gg.z, a2.z, fmaf(gg.w, a3.z, g.z))));
                 g.w = fmaf(gg.x, a0.w, fmaf(gg.y, a1.w, fmaf(gg.z, a2.w, fmaf(gg.w, a3.w, g.w))));
             }
-            const int idx = sW + n * WP + 4 * kc, k0 = 4 * kc;
-            adam_update(Ws, Ms, Vs, As, idx, g.x, st, prox_acc);
-            if (k0 + 1 < K) adam_update(Ws, Ms, Vs, As, idx + 1, g.y, st, prox_acc);
-            if (k0 + 2 < K) adam_update(Ws, Ms, Vs, As, idx + 2, g.z, st, prox_acc);
-            if (k0 + 3 < K) adam_update(Ws, Ms, Vs, As, idx + 3, g.w, st, prox_acc);
+            adam_update4(Ws, Ms, Vs, As, sW + n * WP + 4 * kc, g, st, prox_acc);
         } else {
             const int n0 = (it - N * K4) * 4;
 #pragma unroll
@@ -204,9 +224,9 @@ __device__ __forceinline__ void wgrad_adam(int item0, const float* __restrict__ 
 template <int BT>
 struct TrainSmem {
     static constexpr int HP = 28, ZP = 8, XHP = 116;
-    float W[S_TOT];
-    float M[S_TOT];
-    float V[S_TOT];
+    alignas(16) float W[S_TOT];
+    alignas(16) float M[S_TOT];
+    alignas(16) float V[S_TOT];
     alignas(16) float x[2][BT * XP];
     alignas(16) float h1[BT * HP];
     alignas(16) float z[BT * ZP];

@@ -52,14 +52,22 @@ def _mixing(rng: np.random.Generator, spec: SyntheticSpec):
 
 
 def make_clients(n_clients: int, spec: SyntheticSpec = NBAIOT_SPEC, seed: int = 0,
-                 names: Optional[List[str]] = None) -> List[ClientRaw]:
-    """Generate ``n_clients`` clients of raw float64 traffic."""
+                 names: Optional[List[str]] = None, full: Optional[range] = None) -> List[ClientRaw]:
+    """Generate ``n_clients`` clients of raw float64 traffic.
+
+    ``full`` restricts the clients for which the abnormal / new-device rows are generated (a
+    multi-GPU rank needs every client's normal rows for the replicated validation shards and the
+    pooled dev set, but test data only for the clients it owns); the others get empty matrices.
+    Every client draws from its own generator keyed by ``(seed, index)``, so the rows of a client
+    do not depend on which other clients are generated.
+    """
     g = np.random.default_rng(seed)
     A, scale, offset, const = _mixing(g, spec)
     A_att = A + 0.8 * g.normal(size=A.shape) / np.sqrt(spec.rank)
     att_shift = g.normal(0.0, 1.5, size=spec.rank)
     out: List[ClientRaw] = []
     for c in range(n_clients):
+        want_full = full is None or c in full
         r = np.random.default_rng([seed, c + 1])
         shift = spec.noniid * r.normal(size=spec.rank)
         j = spec.jitter_rows
@@ -81,11 +89,13 @@ def make_clients(n_clients: int, spec: SyntheticSpec = NBAIOT_SPEC, seed: int = 
             x[:, const] = offset[const]
             return x
 
+        empty = np.zeros((0, spec.dim))
+        nor = finish(normal(n_nor))
         out.append(ClientRaw(
             name=(names[c] if names else f"Syn-Client-{c + 1}"),
-            normal=finish(normal(n_nor)),
-            abnormal=finish(attack(n_abn)),
-            test_normal=finish(normal(spec.n_test_normal)),
+            normal=nor,
+            abnormal=finish(attack(n_abn)) if want_full else empty,
+            test_normal=finish(normal(spec.n_test_normal)) if want_full else empty,
         ))
     return out
 

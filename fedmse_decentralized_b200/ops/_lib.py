@@ -39,6 +39,13 @@ class FmScoreArgs(C.Structure):
                 ("X", c_vp), ("tiles", c_vp), ("n_tiles", C.c_int32), ("out_sse", c_vp), ("out_lat", c_vp)]
 
 
+class FmVoteArgs(C.Structure):
+    _fields_ = [("slab", c_vp), ("sel", c_vp), ("n_sel", C.c_int32), ("first_client", C.c_int32),
+                ("n_local", C.c_int32), ("V", c_vp), ("rows", C.c_int32), ("chunk", C.c_int32),
+                ("jitter", c_vp), ("voter_pos", C.c_int32), ("tiles", c_vp), ("n_tiles", C.c_int32),
+                ("scratch_norm", c_vp), ("scratch_sse", c_vp), ("scores", c_vp)]
+
+
 class FmMergeArgs(C.Structure):
     _fields_ = [("peer_slabs", c_vp), ("world", C.c_int32), ("rank", C.c_int32), ("n_global", C.c_int32),
                 ("sel", c_vp), ("n_sel", C.c_int32), ("mse", c_vp), ("mode", C.c_int32), ("compat", C.c_int32),
@@ -117,6 +124,7 @@ def load() -> C.CDLL:
         ("fm_vote_normalise", [c_vp, C.c_int32, c_vp, c_vp]),
         ("fm_chunk_mean", [c_vp, C.c_int32, C.c_int32, C.c_int32, c_vp, c_vp, C.c_int32, C.c_int32,
                            C.c_int32, c_vp, c_vp]),
+        ("fm_vote_scores", [C.POINTER(FmVoteArgs), c_vp]),
         ("fm_elect", [c_vp, c_vp, C.c_int32, C.c_int32, c_vp, C.c_int32, c_vp, c_vp]),
         ("fm_merge", [C.POINTER(FmMergeArgs), c_vp]),
         ("fm_verify_update", [C.POINTER(FmVerifyArgs), c_vp]),

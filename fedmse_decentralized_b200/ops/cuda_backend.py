@@ -173,14 +173,12 @@ class CudaBackend:
         n = len(ctl.sel)
         v0, rows = sh.valid.off_host[ctl.vote_client], sh.valid.count(ctl.vote_client)
         V = sh.valid.x[v0:v0 + rows]
-        _lib.check(self.lib.fm_vote_normalise(_ptr(V), rows, _ptr(self.vote_norm), self._stream()), "vote_normalise")
         tiles = self._tiles(("vote", n, rows), lambda: make_tiles([(p, 0, rows, p * rows) for p in range(n)]))
-        self._score(st.params, st.n_clients, sh.first_client, self.ctl_sel, self.vote_norm, tiles,
-                    self.vote_sse, None)
-        _lib.check(self.lib.fm_chunk_mean(_ptr(self.vote_sse), n, rows, spec.vote_chunk, _ptr(self.ctl_jit),
-                                          _ptr(self.ctl_sel), sh.first_client, st.n_clients, ctl.voter_pos,
-                                          _ptr(self.scores), self._stream()), "chunk_mean")
-        self.launches += 2
+        a = _lib.FmVoteArgs(_ptr(st.params), _ptr(self.ctl_sel), n, sh.first_client, st.n_clients, _ptr(V), rows,
+                            spec.vote_chunk, _ptr(self.ctl_jit), ctl.voter_pos, _ptr(tiles), tiles.shape[0],
+                            _ptr(self.vote_norm), _ptr(self.vote_sse), _ptr(self.scores))
+        _lib.check(self.lib.fm_vote_scores(C.byref(a), self._stream()), "vote_scores")
+        self.launches += 3
         return self.scores[:n]
 
     def elect(self, st, scores: torch.Tensor, ctl: RoundControl, spec: MergeSpec) -> torch.Tensor:

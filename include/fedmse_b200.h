@@ -97,6 +97,20 @@ int fm_chunk_mean(const float* sse, int32_t n_slots, int32_t rows, int32_t chunk
                   const int32_t* slot_client, int32_t first_client, int32_t n_local, int32_t skip_slot,
                   float* scores, void* stream);
 
+/* ---- T2 vote scoring in one call: fm_vote_normalise + fm_score_rows + fm_chunk_mean ----------
+ * (reference: client_trainer.py:208-247 applied to every candidate, main.py:284-288).
+ * scores[p] = jitter[p] * chunked MSE of model sel[p] on the normalised V; 0 for the voter's own
+ * position and for models owned by other ranks.  tiles must cover, for every position p, rows
+ * [0, rows) of the normalised matrix with out0 = p * rows.  scratch_norm holds rows * FM_XP floats,
+ * scratch_sse holds n_sel * rows floats; both are caller-allocated and may be reused afterwards. */
+typedef struct FmVoteArgs {
+    const float* slab; const int32_t* sel; int32_t n_sel; int32_t first_client; int32_t n_local;
+    const float* V; int32_t rows; int32_t chunk; const float* jitter; int32_t voter_pos;
+    const int32_t* tiles; int32_t n_tiles;
+    float* scratch_norm; float* scratch_sse; float* scores;
+} FmVoteArgs;
+int fm_vote_scores(const FmVoteArgs* args, void* stream);
+
 /* ---- election (reference: client_trainer.py:262-285, main.py:284-288) --------------------
  * agg_pos[0] = argmin over positions p != voter_pos with agg_count[sel[p]] < max_agg of
  * scores[p] (NaN = +inf, ties: first); -1 if none.  agg_pos[1] = the elected global id or -1. */
@@ -107,9 +121,9 @@ int fm_elect(const float* scores, const int32_t* sel, int32_t n_sel, int32_t vot
  * theta = sum_k w_k * model(sel[k]), where model(g) is read from the owner rank's slab through
  * peer_slabs[owner] (P2P over NVLink for remote owners).  Weights: uniform (mode 0) or
  * normalised 1/mse (mode 1), with the reference's aliasing quirk when compat != 0
- * (client_trainer.py:107-130).  Also performs the aggregator's side effects:
- * agg_count[aggregator]++ and, on the owning rank, params[aggregator] = theta.
- * No-op when agg_pos[0] < 0. */
+ * (client_trainer.py:107-130).  Also bumps agg_count[aggregator] (the quota of
+ * client_trainer.py:329).  The aggregator's own parameters are replaced by fm_verify_update, after
+ * every rank has finished reading the selected rows.  No-op when agg_pos[0] < 0. */
 typedef struct FmMergeArgs {
     const float* const* peer_slabs; /* device array [world] of slab base pointers (own rank included) */
     int32_t world;

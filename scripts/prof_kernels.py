@@ -1,0 +1,54 @@
+"""Stand-alone driver for ncu captures: runs one kernel family a few times on bench-shaped data.
+
+  python scripts/prof_kernels.py train|score|round [--clients 125] [--iters 3]
+"""
+import argparse
+import os
+import random
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+
+from fedmse_decentralized_b200 import ExperimentConfig
+from fedmse_decentralized_b200.data import NBAIOT_SPEC, ShardStore, make_clients, prepare_from_raw
+from fedmse_decentralized_b200.ops.backend import RoundControl
+from fedmse_decentralized_b200.trainer import FederationEngine
+
+ap = argparse.ArgumentParser()
+ap.add_argument("what", choices=["train", "score", "round"])
+ap.add_argument("--clients", type=int, default=125)
+ap.add_argument("--iters", type=int, default=3)
+ap.add_argument("--epochs", type=int, default=5)
+ap.add_argument("--patience", type=int, default=1)
+ap.add_argument("--score-precision", default="fp32")
+a = ap.parse_args()
+dev = torch.device("cuda", 0)
+random.seed(0); np.random.seed(0); torch.manual_seed(0)
+clients, devset = prepare_from_raw(make_clients(a.clients, NBAIOT_SPEC, seed=1234), True, seed=1)
+sh = ShardStore.build(clients, devset).to(dev)
+cfg = ExperimentConfig(epoch=a.epochs, network_size=a.clients, backend="cuda", write_latents=False,
+                       save_client_models=False, local_patience=a.patience, score_precision=a.score_precision)
+eng = FederationEngine(cfg, sh, "hybrid", "mse_avg")
+be, st = eng.backend, eng.state
+ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+for it in range(a.iters):
+    ctl = eng.make_control(it)
+    be.begin_round(ctl)
+    torch.cuda.synchronize()
+    ev[0].record()
+    if a.what == "train":
+        be.train(st, sh, eng._sel_local(ctl.sel), eng.hp)
+    elif a.what == "score":
+        be.merge_scores(st, sh, ctl)
+    else:
+        eng.run_round(it, ctl)
+    ev[1].record()
+    torch.cuda.synchronize()
+    extra = ""
+    if a.what == "train":
+        ep = st.epochs_run[st.epochs_run > 0]
+        extra = f" epochs max {int(ep.max())} mean {float(ep.float().mean()):.2f}"
+    print(f"{a.what} iter {it}: {ev[0].elapsed_time(ev[1]):.3f} ms{extra}")
