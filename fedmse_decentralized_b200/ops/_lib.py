@@ -46,6 +46,17 @@ class FmVoteArgs(C.Structure):
                 ("scratch_norm", c_vp), ("scratch_sse", c_vp), ("scores", c_vp)]
 
 
+class FmVoteStaticArgs(C.Structure):
+    _fields_ = [("slab", c_vp), ("sel", c_vp), ("n_sel", C.c_int32), ("first_client", C.c_int32),
+                ("n_local", C.c_int32), ("V", c_vp), ("rows", C.c_int32), ("chunk", C.c_int32),
+                ("jitter", c_vp), ("voter_pos", C.c_int32), ("tiles", c_vp), ("n_tiles", C.c_int32),
+                ("scores", c_vp)]
+
+
+STATIC_VOTE_MAX_ROWS = 1024
+STATIC_VOTE_MAX_SEL = 64
+
+
 class FmMergeArgs(C.Structure):
     _fields_ = [("peer_slabs", c_vp), ("world", C.c_int32), ("rank", C.c_int32), ("n_global", C.c_int32),
                 ("sel", c_vp), ("n_sel", C.c_int32), ("mse", c_vp), ("mode", C.c_int32), ("compat", C.c_int32),
@@ -125,6 +136,7 @@ def load() -> C.CDLL:
         ("fm_chunk_mean", [c_vp, C.c_int32, C.c_int32, C.c_int32, c_vp, c_vp, C.c_int32, C.c_int32,
                            C.c_int32, c_vp, c_vp]),
         ("fm_vote_scores", [C.POINTER(FmVoteArgs), c_vp]),
+        ("fm_vote_scores_static", [C.POINTER(FmVoteStaticArgs), c_vp]),
         ("fm_elect", [c_vp, c_vp, C.c_int32, C.c_int32, c_vp, C.c_int32, c_vp, c_vp]),
         ("fm_merge", [C.POINTER(FmMergeArgs), c_vp]),
         ("fm_verify_update", [C.POINTER(FmVerifyArgs), c_vp]),
@@ -141,6 +153,8 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)
         fn.argtypes = argt
         fn.restype = C.c_int
+    lib.fm_vote_scores_static_error.argtypes = []
+    lib.fm_vote_scores_static_error.restype = C.c_char_p
     lib.fm_error_string.argtypes = [C.c_int]
     lib.fm_error_string.restype = C.c_char_p
     _lib = lib

@@ -111,6 +111,32 @@ typedef struct FmVoteArgs {
 } FmVoteArgs;
 int fm_vote_scores(const FmVoteArgs* args, void* stream);
 
+/* ---- vote scoring without caller scratch --------------------------------------------------
+ * No counterpart in the reference (which allocates freely through PyTorch).  Same inputs, outputs
+ * and results as fm_vote_scores, for hosts that cannot supply scratch because they cannot allocate
+ * device memory at the point of the call: loops that must never hit cudaMalloc's device-wide
+ * serialisation after start-up, processes whose GPU memory is already owned by another framework's
+ * pool, or plain C hosts without an allocator.  The scratch is a device array built into the
+ * library, limited to FM_STATIC_VOTE_MAX_ROWS validation rows and FM_STATIC_VOTE_MAX_SEL selected
+ * models (768 KiB, resident on every GPU that loads the library until the process exits).  Larger
+ * requests return cudaErrorInvalidValue and leave a message in fm_vote_scores_static_error().
+ * The call performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ *  - The first call on each device looks up the array's device address; make that first call
+ *    outside any stream capture.
+ *  - All calls share the one array, which keeps the previous call's contents; the entry point
+ *    clears what must start from zero itself.  Two calls whose GPU work can overlap (different
+ *    streams, or threads) race on the array: serialise them. */
+#define FM_STATIC_VOTE_MAX_ROWS 1024
+#define FM_STATIC_VOTE_MAX_SEL 64
+typedef struct FmVoteStaticArgs {
+    const float* slab; const int32_t* sel; int32_t n_sel; int32_t first_client; int32_t n_local;
+    const float* V; int32_t rows; int32_t chunk; const float* jitter; int32_t voter_pos;
+    const int32_t* tiles; int32_t n_tiles;
+    float* scores;
+} FmVoteStaticArgs;
+int fm_vote_scores_static(const FmVoteStaticArgs* args, void* stream);
+const char* fm_vote_scores_static_error(void);
+
 /* ---- election (reference: client_trainer.py:262-285, main.py:284-288) --------------------
  * agg_pos[0] = argmin over positions p != voter_pos with agg_count[sel[p]] < max_agg of
  * scores[p] (NaN = +inf, ties: first); -1 if none.  agg_pos[1] = the elected global id or -1. */
