@@ -76,7 +76,10 @@ class IoTDataProccessor:
         return self.transform(dataframe, type="normal")
 
     def transform(self, dataframe, type: str = "normal") -> Tuple[np.ndarray, np.ndarray]:
-        data = self.scaler.transform(dataframe)
+        if len(dataframe) == 0:      # e.g. test data of a client owned by another rank
+            data = np.zeros((0, np.shape(dataframe)[1] if np.ndim(dataframe) == 2 else 0))
+        else:
+            data = self.scaler.transform(dataframe)
         label = np.zeros(len(dataframe), dtype=np.int64) if type == "normal" \
             else np.ones(len(dataframe), dtype=np.int64)
         return data, label

@@ -28,7 +28,17 @@ from .synthetic import ClientRaw
 log = logging.getLogger(__name__)
 
 
+def _find_config(path: str) -> str:
+    """Accept the reference's ``Configuration/<name>.json`` spelling: fall back to ``configs/<name>.json``."""
+    if os.path.exists(path):
+        return path
+    repo = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    cand = os.path.join(repo, "configs", os.path.basename(path))
+    return cand if os.path.exists(cand) else path
+
+
 def load_scenario(path: str) -> Dict:
+    path = _find_config(path)
     with open(path, "r") as fh:
         cfg = json.load(fh)
     if "devices_list" not in cfg or "data_path" not in cfg:

@@ -1,0 +1,3 @@
+from .evaluator import Evaluator
+
+__all__ = ["Evaluator"]

@@ -1,0 +1,67 @@
+"""Multi-GPU (NCCL + peer-mapped slabs): N ranks on N GPUs must reproduce the single-GPU run.
+Needs >= 2 visible GPUs; run on the B200 box with `gpurun --gpus 2`."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r'''
+import json, os, random, sys
+import numpy as np, torch
+sys.path.insert(0, os.environ["FM_ROOT"])
+from fedmse_decentralized_b200 import ExperimentConfig
+from fedmse_decentralized_b200.data import SyntheticSpec, make_clients, prepare_from_raw
+from fedmse_decentralized_b200.parallel import init_distributed, shutdown
+from fedmse_decentralized_b200.trainer import FederationEngine, build_shards
+comm = init_distributed()
+assert comm.device.type == "cuda"
+spec = SyntheticSpec(n_normal=300, n_abnormal=220, n_test_normal=50, jitter_rows=8)
+clients, dev = prepare_from_raw(make_clients(9, spec, seed=4), True, seed=2)
+sh, names = build_shards(clients, dev, comm, comm.device)
+random.seed(1); np.random.seed(1); torch.manual_seed(1)
+cfg = ExperimentConfig(epoch=2, num_rounds=3, network_size=9, backend="cuda", output_root=os.environ["FM_OUT"],
+                       aggregation=os.environ.get("FM_AGG", "elected"), topology="ring", num_participants=0.7,
+                       write_latents=False, save_client_models=False)
+eng = FederationEngine(cfg, sh, "hybrid", os.environ.get("FM_UPD", "mse_avg"), comm=comm, names_global=names)
+out = [eng.run_round(r) for r in range(3)]
+torch.cuda.synchronize()
+if comm.rank == 0:
+    print("RESULT " + json.dumps({"metrics": [r.client_metrics for r in out], "agg": [r.aggregator for r in out],
+                                  "ver": [[v["is_verified"] for v in r.verification] for r in out],
+                                  "epochs": [sorted(r.epochs_run.items()) for r in out]}))
+shutdown()
+'''
+
+
+def _run(world, tmp_path, agg, upd="mse_avg"):
+    env = dict(os.environ, FM_ROOT=ROOT, FM_OUT=str(tmp_path), FM_AGG=agg, FM_UPD=upd, MASTER_ADDR="127.0.0.1")
+    script = tmp_path / "worker_gpu.py"
+    script.write_text(WORKER)
+    if world == 1:
+        cmd = [sys.executable, str(script)]
+    else:
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+               "--master-addr", "127.0.0.1", "--master-port", "29631", str(script)]
+    p = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=900)
+    assert p.returncode == 0, (p.stdout[-1500:], p.stderr[-3000:])
+    line = [l for l in p.stdout.splitlines() if l.startswith("RESULT ")][-1]
+    return json.loads(line[7:])
+
+
+@pytest.mark.parametrize("agg,upd", [("elected", "mse_avg"), ("elected", "avg"), ("gossip", "mse_avg")])
+def test_n_gpus_match_one_gpu(tmp_path, agg, upd):
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = 2 if n < 4 else (4 if n < 8 else 8)
+    one = _run(1, tmp_path, agg, upd)
+    many = _run(world, tmp_path, agg, upd)
+    assert one["agg"] == many["agg"] and one["ver"] == many["ver"] and one["epochs"] == many["epochs"]
+    for a, b in zip(one["metrics"], many["metrics"]):
+        assert len(a) == 9 and max(abs(x - y) for x, y in zip(a, b)) < 1e-6
