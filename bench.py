@@ -134,7 +134,8 @@ def run_ours(args):
     pin_valid = sh_host.valid.x[v0:v1].pin_memory()
     cfg = ExperimentConfig(num_participants=args.participation, epoch=args.epochs, lr_rate=1e-3, shrink_lambda=5,
                            network_size=n_global, batch_size=12, backend="cuda", write_latents=False,
-                           save_client_models=False, reference_compat=True)
+                           save_client_models=False, reference_compat=True,
+                           score_precision=args.score_precision)
     eng = FederationEngine(cfg, sh, args.model, args.update, comm=comm, names_global=[c.name for c in prepared])
     setup_s = time.time() - t0
     result_bytes = 8 * cnt + 4 * cnt * 2 + 8   # AUC (f64) + epochs_run + rejected (i32) + aggregator
@@ -182,8 +183,11 @@ def run_ours(args):
             "metric": "local_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": comm.world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": value / BASELINE_LOCAL_SAMPLES_PER_SEC, "dtype": "fp32", "data": "synthetic",
-            "impl": "ours",
+            "vs_baseline": value / BASELINE_LOCAL_SAMPLES_PER_SEC,
+            "dtype": {"fp32": "fp32", "tf32": "fp32 training + tf32 scoring forwards",
+                      "tf32x3": "fp32 (training: fp32 FFMA; scoring forwards: error-compensated 3xTF32 on tcgen05, "
+                                "fp32 accumulate, ~1e-6 relative to fp32)"}[args.score_precision],
+            "data": "synthetic", "impl": "ours",
             "rounds_per_sec": args.steps / (ms / 1e3),
             "config": {"model": f"SAE-CEN 115-27-7 ({args.model}) + {args.update}",
                        "scenario": "N-BaIoT-shaped synthetic, reference round loop (elect/merge/broadcast/verify/evaluate)",
@@ -287,6 +291,8 @@ def main():
     ap.add_argument("--model", default="hybrid", choices=["hybrid", "autoencoder"])
     ap.add_argument("--update", default="mse_avg", choices=["avg", "fedprox", "mse_avg"])
     ap.add_argument("--seed", type=int, default=1234)
+    ap.add_argument("--score-precision", default="tf32x3", choices=["fp32", "tf32", "tf32x3"],
+                    help="scoring forwards: exact FFMA kernel, single-pass TF32 or error-compensated 3xTF32 on tcgen05")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)   # timing rule: at least 3 warm-up steps, both arms
     if args.impl == "reference":

@@ -1,0 +1,415 @@
+// Row-scoring forward on the 5th-generation tensor cores (tcgen05 + TMEM + TMA), TF32 inputs,
+// fp32 accumulation.  Same contract as score_rows_kernel (score_kernel.cu) with 128-row tiles.
+//
+// This is the GEMM-shaped work of the framework: one model applied to 10^4..10^6 rows (MSE-weight
+// scoring on the pooled dev set, client_trainer.py:115-130; evaluation, evaluator.py:56-94; vote and
+// verification forwards).  Per 128-row tile:
+//
+//   TMA   : X tile [128 x 128] fp32 -> smem, four 128-B-swizzled K-blocks (cp.async.bulk.tensor.2d)
+//   MMA 1 : D1[128 x 32]  = X[128 x 128] . W1^T            16 x tcgen05.mma kind::tf32 (SS), M=128 N=32 K=8
+//   epi 1 : one thread per row: tcgen05.ld D1 -> +b1, ReLU -> 27->7->27 bottleneck in registers (FFMA,
+//           weights broadcast from smem) -> latent out; h2 -> tcgen05.st into TMEM as the next A operand
+//   MMA 2 : D2[128 x 128] = H2[128 x 32] . W4^T            4 x tcgen05.mma kind::tf32 (TS: A from TMEM)
+//   epi 2 : tcgen05.ld D2 -> +b4, minus x (swizzled smem reads, conflict-free), squared error -> out
+//
+// Warp roles: warps 0-3 own TMEM lanes 32w..32w+31 (= tile rows) and run both epilogues; one elected
+// lane of warp 4 issues TMA and MMA; completion travels through mbarriers (tcgen05.commit).  Two CTAs
+// per SM (256 TMEM columns each) overlap one tile's epilogue with the other's copy and MMAs.
+#include <cuda.h>
+#include "common.cuh"
+#include "../include/fedmse_b200.h"
+
+namespace fm {
+namespace tc {
+
+constexpr int TROWS = 128;                 // rows per tile = MMA M
+constexpr int NT_TC = 160;                 // 4 epilogue warps + 1 producer/MMA warp
+constexpr int XBLK = TROWS * 128;          // bytes of one K-block of X: 128 rows x 128 B
+constexpr int W1BLK = 32 * 128;            // one K-block of the W1 operand: 32 rows (N) x 128 B
+constexpr int TMEM_COLS = 256;
+constexpr int COL_D1 = 0, COL_A2 = 32, COL_A2LO = 64, COL_D2 = 128;
+
+// PREC = 1: single TF32 pass.  PREC = 3: error-compensated 3xTF32 -- every operand is split into
+// hi = value truncated to TF32 and lo = value - hi (exact in fp32), and each product is formed as
+// hi*hi + hi*lo + lo*hi with fp32 accumulation, which recovers ~22 mantissa bits (fp32-grade results).
+template <int PREC>
+struct TcSmem {
+    static constexpr int LO = PREC == 3 ? 1 : 0;
+    alignas(1024) unsigned char x[4 * XBLK];      // 64 KB, 4 K-blocks, SWIZZLE_128B (PREC 3: hi part, in place)
+    alignas(1024) unsigned char w1[4 * W1BLK];    // 16 KB, B operand of MMA 1: [N=32][K=128] K-major
+    alignas(1024) unsigned char w4[128 * 128];    // 16 KB, B operand of MMA 2: [N=128][K=32] K-major
+    alignas(1024) unsigned char xlo[LO ? 4 * XBLK : 1024];
+    alignas(1024) unsigned char w1lo[LO ? 4 * W1BLK : 1024];
+    alignas(1024) unsigned char w4lo[LO ? 128 * 128 : 1024];
+    alignas(16) float w2[Z * 28];                 // [i][j]
+    alignas(16) float w3[H * 8];                  // [j][i]
+    alignas(16) float b1[32], b2[8], b3[32], b4[128];
+    alignas(8) uint64_t bar_x, bar_split, bar_d1, bar_h2, bar_d2, bar_free;
+    uint32_t tmem_base;
+};
+
+// ---- PTX wrappers ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cvt_tf32(float f) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(f));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// K-major, 128-byte swizzle shared-memory matrix descriptor (sm_100 format, version 1):
+// rows are 128 B apart inside an 8-row swizzle atom, atoms are SBO = 1024 B apart; LBO is unused.
+__device__ __forceinline__ uint64_t smem_desc_sw128(const void* p) {
+    const uint32_t a = smem_u32(p);
+    uint64_t d = 0;
+    d |= (uint64_t)((a & 0x3FFFFu) >> 4);          // start address  [0,14)
+    d |= (uint64_t)1 << 16;                         // leading byte offset (ignored for swizzled K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;               // stride byte offset [32,46)
+    d |= (uint64_t)1 << 46;                         // descriptor version (Blackwell)
+    d |= (uint64_t)2 << 61;                         // layout type: SWIZZLE_128B
+    return d;
+}
+// instruction descriptor: D=F32, A=B=TF32, both K-major, dense
+__host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}\n"
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum), "r"(0u) : "memory");
+}
+__device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, {%5, %5, %5, %5}, p;\n\t}\n"
+                 ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accum), "r"(0u) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                   "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                   "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+                 "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+                 "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};\n"
+                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+                   "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+                   "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+                 : "memory");
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
+// byte offset of element (row, k) inside a [rows x 32 floats] K-block with the 128-B swizzle
+__device__ __forceinline__ int sw128(int row, int k) {
+    return row * 128 + ((((k >> 2) ^ (row & 7)) << 4) | ((k & 3) << 2));
+}
+
+// stage one model into the UMMA operand layouts (TF32, round-to-nearest) and plain fp32 tables
+__device__ __forceinline__ uint32_t trunc_tf32(float f) { return __float_as_uint(f) & 0xFFFFE000u; }
+
+template <int PREC>
+__device__ __forceinline__ void stage_model(TcSmem<PREC>& S, const float* __restrict__ row) {
+    const int tid = threadIdx.x;
+    for (int i = tid; i < (4 * W1BLK) / 16; i += NT_TC) reinterpret_cast<uint4*>(S.w1)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < (128 * 128) / 16; i += NT_TC) reinterpret_cast<uint4*>(S.w4)[i] = make_uint4(0, 0, 0, 0);
+    if (PREC == 3) {
+        for (int i = tid; i < (4 * W1BLK) / 16; i += NT_TC) reinterpret_cast<uint4*>(S.w1lo)[i] = make_uint4(0, 0, 0, 0);
+        for (int i = tid; i < (128 * 128) / 16; i += NT_TC) reinterpret_cast<uint4*>(S.w4lo)[i] = make_uint4(0, 0, 0, 0);
+    }
+    for (int i = tid; i < Z * 28; i += NT_TC) S.w2[i] = 0.f;
+    for (int i = tid; i < H * 8; i += NT_TC) S.w3[i] = 0.f;
+    if (tid < 32) { S.b1[tid] = 0.f; S.b3[tid] = 0.f; }
+    if (tid < 8) S.b2[tid] = 0.f;
+    if (tid < 128) S.b4[tid] = 0.f;
+    __syncthreads();
+    for (int p = tid; p < NP; p += NT_TC) {
+        const float v = row[p];
+        if (p < OFF_B1) {
+            const int n = p / D, k = p - n * D;
+            const int off = (k >> 5) * W1BLK + sw128(n, k & 31);
+            if (PREC == 3) {
+                const uint32_t hi = trunc_tf32(v);
+                *reinterpret_cast<uint32_t*>(S.w1 + off) = hi;
+                *reinterpret_cast<float*>(S.w1lo + off) = v - __uint_as_float(hi);
+            } else *reinterpret_cast<uint32_t*>(S.w1 + off) = cvt_tf32(v);
+        } else if (p < OFF_W2) S.b1[p - OFF_B1] = v;
+        else if (p < OFF_B2) { const int q = p - OFF_W2, i = q / H, j = q - i * H; S.w2[i * 28 + j] = v; }
+        else if (p < OFF_W3) S.b2[p - OFF_B2] = v;
+        else if (p < OFF_B3) { const int q = p - OFF_W3, j = q / Z, i = q - j * Z; S.w3[j * 8 + i] = v; }
+        else if (p < OFF_W4) S.b3[p - OFF_B3] = v;
+        else if (p < OFF_B4) {
+            const int q = p - OFF_W4, d = q / H, j = q - d * H;
+            const int off = sw128(d, j);
+            if (PREC == 3) {
+                const uint32_t hi = trunc_tf32(v);
+                *reinterpret_cast<uint32_t*>(S.w4 + off) = hi;
+                *reinterpret_cast<float*>(S.w4lo + off) = v - __uint_as_float(hi);
+            } else *reinterpret_cast<uint32_t*>(S.w4 + off) = cvt_tf32(v);
+        } else S.b4[p - OFF_B4] = v;
+    }
+    fence_proxy_async();          // generic-proxy writes -> visible to the tensor core (async proxy)
+    __syncthreads();
+}
+
+template <int PREC>
+__global__ void __launch_bounds__(NT_TC, PREC == 3 ? 1 : 2)
+score_rows_tc_kernel(const FmScoreArgs a, const __grid_constant__ CUtensorMap xmap, int tiles_per_cta) {
+    extern __shared__ unsigned char smem_dyn[];
+    using SM = TcSmem<PREC>;
+    SM& S = *reinterpret_cast<SM*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int t_begin = blockIdx.x * tiles_per_cta;
+    const int t_end = min(a.n_tiles, t_begin + tiles_per_cta);
+    if (t_begin >= t_end) return;
+    const bool need_sse = a.out_sse != nullptr;
+
+    if (tid == 0) {
+        mbar_init(&S.bar_x, 1); mbar_init(&S.bar_d1, 1); mbar_init(&S.bar_d2, 1);
+        mbar_init(&S.bar_h2, 128); mbar_init(&S.bar_free, 128); mbar_init(&S.bar_split, 128);
+        fence_mbar_init();
+    }
+    if (warp == 4) {      // one warp allocates the CTA's tensor memory
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)), "r"(TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = S.tmem_base;
+
+    auto local_of = [&](int slot) -> int {
+        const int g = a.slot_client ? a.slot_client[slot] : a.first_client + slot;
+        const int c = g - a.first_client;
+        return (c >= 0 && c < a.n_local) ? c : -1;
+    };
+    constexpr uint32_t IDESC1 = idesc_tf32(128, 32), IDESC2 = idesc_tf32(128, 128);
+    int cur_model = -1;
+    uint32_t n_done = 0;          // tiles processed by this CTA -> barrier phase parity
+    for (int t = t_begin; t < t_end; ++t) {
+        const int4 tl = reinterpret_cast<const int4*>(a.tiles)[t];   // {slot, row0, nrows, out0}
+        const int c = local_of(tl.x);
+        if (c < 0) continue;
+        if (c != cur_model) {       // previous tile's MMAs are complete (its epilogue waited on them)
+            __syncthreads();
+            stage_model<PREC>(S, a.slab + (size_t)c * P_PAD);
+            cur_model = c;
+        }
+        const uint32_t ph = n_done & 1u;
+        if (warp == 4) {
+            if (lane == 0) {
+                if (n_done > 0) mbar_wait(&S.bar_free, ph ^ 1u);      // x tile and TMEM free again
+                mbar_expect_tx(&S.bar_x, 4 * XBLK);
+#pragma unroll
+                for (int kb = 0; kb < 4; ++kb) tma_load_2d(S.x + kb * XBLK, &xmap, kb * 32, tl.y, &S.bar_x);
+                mbar_wait(PREC == 3 ? &S.bar_split : &S.bar_x, ph);   // PREC 3: wait for the hi/lo split of the tile
+                tc_fence_after();
+#pragma unroll
+                for (int kb = 0; kb < 4; ++kb) {
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        const uint64_t ad = smem_desc_sw128(S.x + kb * XBLK + ks * 32);
+                        const uint64_t bd = smem_desc_sw128(S.w1 + kb * W1BLK + ks * 32);
+                        mma_ss(tmem + COL_D1, ad, bd, IDESC1, (kb | ks) ? 1u : 0u);
+                        if (PREC == 3) {
+                            mma_ss(tmem + COL_D1, ad, smem_desc_sw128(S.w1lo + kb * W1BLK + ks * 32), IDESC1, 1u);
+                            mma_ss(tmem + COL_D1, smem_desc_sw128(S.xlo + kb * XBLK + ks * 32), bd, IDESC1, 1u);
+                        }
+                    }
+                }
+                tc_commit(&S.bar_d1);
+                if (need_sse) {
+                    mbar_wait(&S.bar_h2, ph);
+                    tc_fence_after();
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        const uint64_t bd = smem_desc_sw128(S.w4 + ks * 32);
+                        mma_ts(tmem + COL_D2, tmem + COL_A2 + ks * 8, bd, IDESC2, ks ? 1u : 0u);
+                        if (PREC == 3) {
+                            mma_ts(tmem + COL_D2, tmem + COL_A2 + ks * 8, smem_desc_sw128(S.w4lo + ks * 32), IDESC2, 1u);
+                            mma_ts(tmem + COL_D2, tmem + COL_A2LO + ks * 8, bd, IDESC2, 1u);
+                        }
+                    }
+                    tc_commit(&S.bar_d2);
+                }
+            }
+            __syncwarp();
+        } else {
+            const int r = warp * 32 + lane;                      // tile row = TMEM lane
+            const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+            if (PREC == 3) {
+                // split the raw tile into hi (in place) and lo; elementwise, so the swizzled layout is kept
+                mbar_wait(&S.bar_x, ph);
+                uint4* xh = reinterpret_cast<uint4*>(S.x);
+                float4* xl = reinterpret_cast<float4*>(S.xlo);
+#pragma unroll 4
+                for (int i = tid; i < (4 * XBLK) / 16; i += 128) {
+                    const uint4 raw = xh[i];
+                    const uint4 hi = make_uint4(raw.x & 0xFFFFE000u, raw.y & 0xFFFFE000u, raw.z & 0xFFFFE000u, raw.w & 0xFFFFE000u);
+                    xh[i] = hi;
+                    xl[i] = make_float4(__uint_as_float(raw.x) - __uint_as_float(hi.x), __uint_as_float(raw.y) - __uint_as_float(hi.y),
+                                        __uint_as_float(raw.z) - __uint_as_float(hi.z), __uint_as_float(raw.w) - __uint_as_float(hi.w));
+                }
+                fence_proxy_async();
+                mbar_arrive(&S.bar_split);
+            }
+            // ---- epilogue 1 ----
+            mbar_wait(&S.bar_d1, ph);
+            tc_fence_after();
+            uint32_t v[32];
+            tmem_ld32(lane_base + COL_D1, v);
+            float h1[28];
+#pragma unroll
+            for (int j = 0; j < H; ++j) h1[j] = fmaxf(__uint_as_float(v[j]) + S.b1[j], 0.f);
+            h1[27] = 0.f;
+            float z[8];
+#pragma unroll
+            for (int i = 0; i < Z; ++i) {
+                float acc = S.b2[i];
+#pragma unroll
+                for (int j4 = 0; j4 < 28; j4 += 4) {
+                    const float4 w = *reinterpret_cast<const float4*>(&S.w2[i * 28 + j4]);
+                    acc = fmaf(h1[j4], w.x, fmaf(h1[j4 + 1], w.y, fmaf(h1[j4 + 2], w.z, fmaf(h1[j4 + 3], w.w, acc))));
+                }
+                z[i] = acc;
+            }
+            z[7] = 0.f;
+            if (a.out_lat && r < tl.z) {
+                float4* o = reinterpret_cast<float4*>(a.out_lat + (size_t)(tl.w + r) * 8);
+                o[0] = make_float4(z[0], z[1], z[2], z[3]);
+                o[1] = make_float4(z[4], z[5], z[6], 0.f);
+            }
+            if (need_sse) {
+#pragma unroll
+                for (int j = 0; j < H; ++j) {
+                    const float4 wa = *reinterpret_cast<const float4*>(&S.w3[j * 8]);
+                    const float4 wb = *reinterpret_cast<const float4*>(&S.w3[j * 8 + 4]);
+                    float acc = S.b3[j];
+                    acc = fmaf(z[0], wa.x, fmaf(z[1], wa.y, fmaf(z[2], wa.z, fmaf(z[3], wa.w, acc))));
+                    acc = fmaf(z[4], wb.x, fmaf(z[5], wb.y, fmaf(z[6], wb.z, acc)));
+                    const float hv = fmaxf(acc, 0.f);
+                    if (PREC == 3) { v[j] = trunc_tf32(hv); h1[j] = hv - __uint_as_float(v[j]); }   // h1[] reused for the lo part
+                    else v[j] = cvt_tf32(hv);
+                }
+#pragma unroll
+                for (int j = H; j < 32; ++j) v[j] = 0u;
+                tmem_st32(lane_base + COL_A2, v);
+                if (PREC == 3) {
+#pragma unroll
+                    for (int j = 0; j < H; ++j) v[j] = __float_as_uint(h1[j]);
+                    tmem_st32(lane_base + COL_A2LO, v);
+                }
+                tc_fence_before();
+                mbar_arrive(&S.bar_h2);
+                // ---- epilogue 2 ----
+                mbar_wait(&S.bar_x, ph);            // acquire the TMA-written x tile for generic loads
+                mbar_wait(&S.bar_d2, ph);
+                tc_fence_after();
+                float sse = 0.f;
+#pragma unroll 1
+                for (int cb = 0; cb < 4; ++cb) {
+                    tmem_ld32(lane_base + COL_D2 + cb * 32, v);
+                    const unsigned char* xb = S.x + cb * XBLK + r * 128;
+#pragma unroll
+                    for (int q4 = 0; q4 < 8; ++q4) {
+                        float4 xv = *reinterpret_cast<const float4*>(xb + ((q4 ^ (r & 7)) << 4));
+                        if (PREC == 3) {      // x = hi + lo exactly
+                            const float4 xl = *reinterpret_cast<const float4*>(S.xlo + cb * XBLK + r * 128 + ((q4 ^ (r & 7)) << 4));
+                            xv.x += xl.x; xv.y += xl.y; xv.z += xl.z; xv.w += xl.w;
+                        }
+                        const float4 bb = *reinterpret_cast<const float4*>(&S.b4[cb * 32 + q4 * 4]);
+                        const int d0 = cb * 32 + q4 * 4;
+                        const float e0 = (__uint_as_float(v[q4 * 4 + 0]) + bb.x) - xv.x;
+                        const float e1 = (__uint_as_float(v[q4 * 4 + 1]) + bb.y) - xv.y;
+                        const float e2 = (__uint_as_float(v[q4 * 4 + 2]) + bb.z) - xv.z;
+                        const float e3 = (__uint_as_float(v[q4 * 4 + 3]) + bb.w) - xv.w;
+                        if (d0 + 0 < D) sse = fmaf(e0, e0, sse);
+                        if (d0 + 1 < D) sse = fmaf(e1, e1, sse);
+                        if (d0 + 2 < D) sse = fmaf(e2, e2, sse);
+                        if (d0 + 3 < D) sse = fmaf(e3, e3, sse);
+                    }
+                }
+                if (r < tl.z) a.out_sse[tl.w + r] = sse;
+            }
+            tc_fence_before();
+            mbar_arrive(&S.bar_free);
+        }
+        ++n_done;
+    }
+    // teardown: everyone done with tensor memory, then the allocating warp frees it
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) {
+        if (lane == 0 && n_done > 0) mbar_wait(&S.bar_free, (n_done - 1) & 1u);
+        __syncwarp();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS));
+    }
+}
+
+}  // namespace tc
+}  // namespace fm
+
+// ---- host side: tensor map + launch ---------------------------------------------------------
+namespace {
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+}  // namespace
+
+// x_rows = number of valid rows behind args->X (rows past it are zero-filled by the TMA unit).
+extern "C" int fm_score_rows_tc(const FmScoreArgs* args, int64_t x_rows, int32_t precision, void* stream) {
+    if (precision != 1 && precision != 3) return (int)cudaErrorInvalidValue;
+    using namespace fm;
+    using namespace fm::tc;
+    if (args->n_tiles <= 0) return 0;
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return (int)cudaErrorNotSupported;
+    CUtensorMap map;
+    const cuuint64_t gdim[2] = {(cuuint64_t)XP, (cuuint64_t)x_rows};
+    const cuuint64_t gstride[1] = {(cuuint64_t)XP * sizeof(float)};
+    const cuuint32_t box[2] = {32u, (cuuint32_t)TROWS};
+    const cuuint32_t estride[2] = {1u, 1u};
+    CUresult r = enc(&map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(args->X), gdim, gstride, box, estride,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return (int)cudaErrorInvalidValue;
+    static int sms = 0;
+    if (!sms) { int dev; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    const bool x3 = precision == 3;
+    const size_t smem = (x3 ? sizeof(TcSmem<3>) : sizeof(TcSmem<1>)) + 1024;
+    cudaError_t err = x3 ? cudaFuncSetAttribute(score_rows_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                         : cudaFuncSetAttribute(score_rows_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return (int)err;
+    int grid = min(args->n_tiles, (x3 ? 1 : 2) * sms);
+    const int per = (args->n_tiles + grid - 1) / grid;
+    grid = (args->n_tiles + per - 1) / per;
+    if (x3) score_rows_tc_kernel<3><<<grid, NT_TC, smem, (cudaStream_t)stream>>>(*args, map, per);
+    else score_rows_tc_kernel<1><<<grid, NT_TC, smem, (cudaStream_t)stream>>>(*args, map, per);
+    return (int)cudaGetLastError();
+}

@@ -31,12 +31,12 @@ def _ptr(t: Optional[torch.Tensor]) -> int:
     return 0 if t is None else t.data_ptr()
 
 
-def make_tiles(segments: Sequence[Sequence[int]]) -> torch.Tensor:
+def make_tiles(segments: Sequence[Sequence[int]], tile: int = TILE) -> torch.Tensor:
     """Tile table ``[n, 4] = {slot, row0, nrows, out0}`` covering ``(slot, row0, nrows, out0)`` segments."""
     out = []
     for slot, row0, nrows, out0 in segments:
-        for s in range(0, nrows, TILE):
-            out.append((slot, row0 + s, min(TILE, nrows - s), out0 + s))
+        for s in range(0, nrows, tile):
+            out.append((slot, row0 + s, min(tile, nrows - s), out0 + s))
     return torch.tensor(out, dtype=torch.int32).reshape(-1, 4)
 
 
@@ -44,7 +44,15 @@ class CudaBackend:
     name = "cuda"
     reads_peers = True   # merge / gossip kernels read other ranks' slabs themselves
 
-    def __init__(self, layout: ParamLayout, device):
+    def __init__(self, layout: ParamLayout, device, score_precision: str = "fp32"):
+        if score_precision not in ("fp32", "tf32", "tf32x3"):
+            raise ValueError("score_precision must be 'fp32', 'tf32' or 'tf32x3'")
+        # scoring forwards of merge / verify / evaluate: exact FFMA kernel, or the tcgen05 kernel (single
+        # TF32 pass or error-compensated 3xTF32).  Vote scoring always uses the exact kernel: the election
+        # is an argmin over nearly equal scores.
+        self.score_precision = score_precision
+        self.tc = {"fp32": 0, "tf32": 1, "tf32x3": 3}[score_precision]
+        self.tile = 128 if self.tc else TILE
         if (layout.dim, layout.hidden, layout.latent) != (115, 27, 7):
             raise ValueError("the sm_100a kernels are specialised for the 115-27-7 autoencoder; "
                              "use backend='oracle' for other shapes")
@@ -108,12 +116,12 @@ class CudaBackend:
         # static tile tables
         C_ = sh.n_clients
         self.tiles_test = make_tiles([(c, sh.test.off_host[c], sh.test.count(c), sh.test.off_host[c])
-                                      for c in range(C_)]).to(dev)
+                                      for c in range(C_)], self.tile).to(dev)
         self.tiles_train = make_tiles([(c, sh.train.off_host[c], sh.train.count(c), sh.train.off_host[c])
-                                       for c in range(C_)]).to(dev)
+                                       for c in range(C_)], self.tile).to(dev)
         f = sh.first_client
         self.tiles_verify_own = make_tiles([(0, sh.valid.off_host[f + c], sh.valid.count(f + c),
-                                             sh.valid.off_host[f + c]) for c in range(C_)]).to(dev)
+                                             sh.valid.off_host[f + c]) for c in range(C_)], self.tile).to(dev)
         self.verify_off_own = torch.tensor([sh.valid.off_host[f + c] for c in range(C_ + 1)], **i32)
         self.peer_table = self.param_slab.table
 
@@ -149,7 +157,10 @@ class CudaBackend:
                out_lat: Optional[torch.Tensor]) -> None:
         a = _lib.FmScoreArgs(_ptr(slab), _ptr(slot_client), first, n_local, _ptr(X), _ptr(tiles),
                              tiles.shape[0], _ptr(out_sse), _ptr(out_lat))
-        _lib.check(self.lib.fm_score_rows(C.byref(a), self._stream()), "score_rows")
+        if self.tc:
+            _lib.check(self.lib.fm_score_rows_tc(C.byref(a), X.shape[0], self.tc, self._stream()), "score_rows_tc")
+        else:
+            _lib.check(self.lib.fm_score_rows(C.byref(a), self._stream()), "score_rows")
         self.launches += 1
 
     # ------------------------------------------------------------------ T1
@@ -193,7 +204,7 @@ class CudaBackend:
         n, R = len(ctl.sel), self.dev_rows
         if self.merge_sse is None or self.merge_sse.numel() < n * R:
             self.merge_sse = torch.zeros(n * R, dtype=torch.float32, device=self.device)
-        tiles = self._tiles(("dev", n, R), lambda: make_tiles([(p, 0, R, p * R) for p in range(n)]))
+        tiles = self._tiles(("dev", n, R), lambda: make_tiles([(p, 0, R, p * R) for p in range(n)], self.tile))
         self._score(st.params, st.n_clients, sh.first_client, self.ctl_sel, sh.dev, tiles, self.merge_sse, None)
         _lib.check(self.lib.fm_chunk_mean(_ptr(self.merge_sse), n, R, 0, 0, _ptr(self.ctl_sel), sh.first_client,
                                           st.n_clients, -1, _ptr(self.mse), self._stream()), "chunk_mean")
@@ -222,14 +233,14 @@ class CudaBackend:
     def verify_update(self, st, sh, ctl: RoundControl, spec: MergeSpec, theta, agg_pos) -> None:
         if spec.verification_method == "dev":
             R = self.dev_rows
-            tiles = self._tiles(("vdev", R), lambda: make_tiles([(0, 0, R, 0)]))
+            tiles = self._tiles(("vdev", R), lambda: make_tiles([(0, 0, R, 0)], self.tile))
             X, off, shared = sh.dev, self._tiles(("voff", R), lambda: torch.tensor([0, R], dtype=torch.int32)), 1
             if self.verify_sse.numel() < R:
                 self.verify_sse = torch.zeros(R, dtype=torch.float32, device=self.device)
         elif ctl.verify_client >= 0:
             g = ctl.verify_client
             r0, R = sh.valid.off_host[g], sh.valid.count(g)
-            tiles = self._tiles(("vshared", g), lambda: make_tiles([(0, r0, R, 0)]))
+            tiles = self._tiles(("vshared", g), lambda: make_tiles([(0, r0, R, 0)], self.tile))
             X, off, shared = sh.valid.x, self._tiles(("voff", R), lambda: torch.tensor([0, R], dtype=torch.int32)), 1
         else:
             tiles, X, off, shared = self.tiles_verify_own, sh.valid.x, self.verify_off_own, 0

@@ -78,14 +78,14 @@ class GlobalStop:
         return self.worse > self.patience
 
 
-def make_backend(name: str, layout: ParamLayout, device: torch.device):
+def make_backend(name: str, layout: ParamLayout, device: torch.device, score_precision: str = "fp32"):
     if name == "auto":
         name = "cuda" if device.type == "cuda" else "oracle"
     if name == "oracle":
         return OracleBackend(layout, device)
     if name == "cuda":
         from ..ops.cuda_backend import CudaBackend
-        return CudaBackend(layout, device)
+        return CudaBackend(layout, device, score_precision)
     raise ValueError(f"unknown backend {name!r}")
 
 
@@ -104,7 +104,7 @@ class FederationEngine:
             # same RNG order as the reference: one module per client on the global torch generator
             init_params = init_packed_models(self.N, model_type, self.layout, cfg.shrink_lambda)
         self.backend = backend if backend is not None and not isinstance(backend, str) else \
-            make_backend(backend or cfg.backend, self.layout, dev)
+            make_backend(backend or cfg.backend, self.layout, dev, cfg.score_precision)
         storage = None
         if hasattr(self.backend, "alloc_param_slab"):
             storage = self.backend.alloc_param_slab(self.n_local, self.layout.padded, self.comm)

@@ -85,6 +85,12 @@ typedef struct FmScoreArgs {
 } FmScoreArgs;
 int fm_score_rows(const FmScoreArgs* args, void* stream);
 
+/* Same contract on the tensor cores (tcgen05.mma kind::tf32, accumulators in TMEM, tiles by TMA):
+ * tiles hold up to 128 rows; x_rows = number of rows behind X (rows past it read as zero).
+ * precision 1: single TF32 pass (inputs truncated to 10-bit mantissa, fp32 accumulate);
+ * precision 3: error-compensated 3xTF32 (hi/lo split of both operands, ~fp32 accuracy). */
+int fm_score_rows_tc(const FmScoreArgs* args, int64_t x_rows, int32_t precision, void* stream);
+
 /* Column-normalise a vote matrix: out = (V - mean) / (unbiased std + 1e-8)
  * (reference: client_trainer.py:221-223).  V and out are [rows][FM_XP]; out is caller scratch. */
 int fm_vote_normalise(const float* V, int32_t rows, float* out, void* stream);

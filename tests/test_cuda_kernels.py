@@ -169,3 +169,40 @@ def test_gossip_matches_oracle(tiny_clients, tmp_path, dev):
         assert_close(e_gpu.state.params, e_ref.state.params, 3e-3, 3e-5, f"gossip params r{r}")
         assert e_gpu.state.rejected.tolist() == e_ref.state.rejected.tolist()
         assert_close(torch.tensor(res_gpu.client_metrics), torch.tensor(res_ref.client_metrics), 0, 2e-3, "auc")
+
+
+@pytest.mark.parametrize("precision,rtol", [("tf32", 2e-2), ("tf32x3", 2e-4)])
+def test_tensor_core_scoring_matches_oracle(tiny_clients, tmp_path, dev, precision, rtol):
+    """tcgen05 scoring forward (TMA tiles, TMEM accumulators) against the fp32 oracle."""
+    cfg = make_cfg(tmp_path, score_precision=precision)
+    e_ref = make_engine(cfg, make_shards(tiny_clients, "cpu"), "hybrid", "avg", "oracle")
+    e_gpu = make_engine(cfg, make_shards(tiny_clients, dev), "hybrid", "avg", "cuda")
+    be, st, sh = e_gpu.backend, e_gpu.state, e_gpu.sh
+    assert be.tc in (1, 3) and be.tile == 128
+    be.test_sse.fill_(-1.0); be.test_lat.fill_(-1.0)
+    be._score(st.params, st.n_clients, 0, None, sh.test.x, be.tiles_test, be.test_sse, be.test_lat)
+    torch.cuda.synchronize()
+    for c in range(st.n_clients):
+        x = e_ref.sh.test.rows(c)
+        z, _ = oracle.forward(e_ref.state.params[c], x[:, :L.dim], L)
+        sse = oracle.row_sse(e_ref.state.params[c], x, L)
+        lo, hi = sh.test.off_host[c], sh.test.off_host[c + 1]
+        assert_close(be.test_sse[lo:hi], sse, rtol, rtol * 10, f"sse client {c}")
+        assert_close(be.test_lat[lo:hi, :7], z, rtol, rtol, f"latent client {c}")
+    # latents-only mode (hybrid evaluation) and the AUC on top of it
+    a_gpu, _, _ = be.evaluate(st, sh, "hybrid", False)
+    _, a64, _ = e_ref.backend.evaluate(e_ref.state, e_ref.sh, "hybrid", False)
+    assert_close(a_gpu, torch.tensor(a64), 0, 3e-3, "auc")
+
+
+def test_full_round_with_tensor_core_scoring(tiny_clients, tmp_path, dev):
+    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "autoencoder", "mse_avg", score_precision="tf32x3",
+                         num_participants=0.7)
+    for r in range(2):
+        random.seed(50 + r); torch.manual_seed(50 + r)
+        ctl = e_ref.make_control(r)
+        res_ref = e_ref.run_round(r, copy.deepcopy(ctl))
+        res_gpu = e_gpu.run_round(r, copy.deepcopy(ctl))
+        assert res_gpu.aggregator == res_ref.aggregator
+        assert_close(e_gpu.state.params, e_ref.state.params, 3e-3, 3e-5, f"params r{r}")
+        assert_close(torch.tensor(res_gpu.client_metrics), torch.tensor(res_ref.client_metrics), 0, 2e-3, "auc")
