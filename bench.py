@@ -155,8 +155,7 @@ def run_ours(args):
         e0.record()
         for r in range(r0, r0 + n_rounds):
             if with_h2d:    # this round's inputs: fresh local traffic from pinned host memory
-                sh.train.x.copy_(pin_train, non_blocking=True)
-                sh.valid.x[v0:v1].copy_(pin_valid, non_blocking=True)
+                eng.update_local_data(pin_train, pin_valid)
             res = eng.run_round(r)              # includes the device->host read of the round's results
             samples += res.samples
         e1.record()

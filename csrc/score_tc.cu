@@ -27,7 +27,7 @@ constexpr int NT_TC = 160;                 // 4 epilogue warps + 1 producer/MMA 
 constexpr int XBLK = TROWS * 128;          // bytes of one K-block of X: 128 rows x 128 B
 constexpr int W1BLK = 32 * 128;            // one K-block of the W1 operand: 32 rows (N) x 128 B
 constexpr int TMEM_COLS = 256;
-constexpr int COL_D1 = 0, COL_A2 = 32, COL_A2LO = 64, COL_D2 = 128;
+constexpr int COL_D1A = 0, COL_D1B = 32, COL_A2 = 64, COL_A2LO = 96, COL_D2 = 128;
 
 // PREC = 1: single TF32 pass.  PREC = 3: error-compensated 3xTF32 -- every operand is split into
 // hi = value truncated to TF32 and lo = value - hi (exact in fp32), and each product is formed as
@@ -43,8 +43,8 @@ struct TcSmem {
     alignas(1024) unsigned char w4lo[LO ? 128 * 128 : 1024];
     alignas(16) float w2[Z * 28];                 // [i][j]
     alignas(16) float w3[H * 8];                  // [j][i]
-    alignas(16) float b1[32], b2[8], b3[32], b4[128];
-    alignas(8) uint64_t bar_x, bar_split, bar_d1, bar_h2, bar_d2, bar_free;
+    alignas(16) float b1[32], b2[8], b3[32];
+    alignas(8) uint64_t bar_x, bar_d1[2], bar_h2, bar_d2;
     uint32_t tmem_base;
 };
 
@@ -136,7 +136,6 @@ __device__ __forceinline__ void stage_model(TcSmem<PREC>& S, const float* __rest
     for (int i = tid; i < H * 8; i += NT_TC) S.w3[i] = 0.f;
     if (tid < 32) { S.b1[tid] = 0.f; S.b3[tid] = 0.f; }
     if (tid < 8) S.b2[tid] = 0.f;
-    if (tid < 128) S.b4[tid] = 0.f;
     __syncthreads();
     for (int p = tid; p < NP; p += NT_TC) {
         const float v = row[p];
@@ -161,15 +160,32 @@ __device__ __forceinline__ void stage_model(TcSmem<PREC>& S, const float* __rest
                 *reinterpret_cast<uint32_t*>(S.w4 + off) = hi;
                 *reinterpret_cast<float*>(S.w4lo + off) = v - __uint_as_float(hi);
             } else *reinterpret_cast<uint32_t*>(S.w4 + off) = cvt_tf32(v);
-        } else S.b4[p - OFF_B4] = v;
+        } else {                                    // b4[d] rides in column 27 of the W4 operand (h2[27] == 1)
+            const int off = sw128(p - OFF_B4, 27);
+            if (PREC == 3) {
+                const uint32_t hi = trunc_tf32(v);
+                *reinterpret_cast<uint32_t*>(S.w4 + off) = hi;
+                *reinterpret_cast<float*>(S.w4lo + off) = v - __uint_as_float(hi);
+            } else *reinterpret_cast<uint32_t*>(S.w4 + off) = cvt_tf32(v);
+        }
     }
     fence_proxy_async();          // generic-proxy writes -> visible to the tensor core (async proxy)
     __syncthreads();
 }
 
+// residual shard: xlo = x - trunc_tf32(x), so that x == hi + lo exactly with hi = what the tensor core reads
+__global__ void split_residual_kernel(const float4* __restrict__ x, float4* __restrict__ lo, size_t n4) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 v = x[i];
+        lo[i] = make_float4(v.x - __uint_as_float(trunc_tf32(v.x)), v.y - __uint_as_float(trunc_tf32(v.y)),
+                            v.z - __uint_as_float(trunc_tf32(v.z)), v.w - __uint_as_float(trunc_tf32(v.w)));
+    }
+}
+
 template <int PREC>
 __global__ void __launch_bounds__(NT_TC, PREC == 3 ? 1 : 2)
-score_rows_tc_kernel(const FmScoreArgs a, const __grid_constant__ CUtensorMap xmap, int tiles_per_cta) {
+score_rows_tc_kernel(const FmScoreArgs a, const __grid_constant__ CUtensorMap xmap,
+                     const __grid_constant__ CUtensorMap xlomap, long long x_rows, int tiles_per_cta) {
     extern __shared__ unsigned char smem_dyn[];
     using SM = TcSmem<PREC>;
     SM& S = *reinterpret_cast<SM*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
@@ -180,8 +196,8 @@ score_rows_tc_kernel(const FmScoreArgs a, const __grid_constant__ CUtensorMap xm
     const bool need_sse = a.out_sse != nullptr;
 
     if (tid == 0) {
-        mbar_init(&S.bar_x, 1); mbar_init(&S.bar_d1, 1); mbar_init(&S.bar_d2, 1);
-        mbar_init(&S.bar_h2, 128); mbar_init(&S.bar_free, 128); mbar_init(&S.bar_split, 128);
+        mbar_init(&S.bar_x, 1); mbar_init(&S.bar_d1[0], 1); mbar_init(&S.bar_d1[1], 1); mbar_init(&S.bar_d2, 1);
+        mbar_init(&S.bar_h2, 128);
         fence_mbar_init();
     }
     if (warp == 4) {      // one warp allocates the CTA's tensor memory
@@ -192,6 +208,7 @@ score_rows_tc_kernel(const FmScoreArgs a, const __grid_constant__ CUtensorMap xm
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = S.tmem_base;
+    const int4* tiles = reinterpret_cast<const int4*>(a.tiles);
 
     auto local_of = [&](int slot) -> int {
         const int g = a.slot_client ? a.slot_client[slot] : a.first_client + slot;
@@ -199,102 +216,116 @@ score_rows_tc_kernel(const FmScoreArgs a, const __grid_constant__ CUtensorMap xm
         return (c >= 0 && c < a.n_local) ? c : -1;
     };
     constexpr uint32_t IDESC1 = idesc_tf32(128, 32), IDESC2 = idesc_tf32(128, 128);
-    int cur_model = -1;
-    uint32_t n_done = 0;          // tiles processed by this CTA -> barrier phase parity
-    for (int t = t_begin; t < t_end; ++t) {
-        const int4 tl = reinterpret_cast<const int4*>(a.tiles)[t];   // {slot, row0, nrows, out0}
-        const int c = local_of(tl.x);
-        if (c < 0) continue;
-        if (c != cur_model) {       // previous tile's MMAs are complete (its epilogue waited on them)
-            __syncthreads();
-            stage_model<PREC>(S, a.slab + (size_t)c * P_PAD);
-            cur_model = c;
+    constexpr uint32_t XBYTES = (PREC == 3 ? 2u : 1u) * 4u * XBLK;
+    uint32_t g = 0;               // tiles processed so far by this CTA: selects D1 buffer and barrier parities
+
+    int t = t_begin;
+    while (t < t_end) {
+        // ---- a run = consecutive tiles of one slot (= one model) ----
+        const int slot = tiles[t].x;
+        int te = t + 1;
+        for (;;) {                // warp-parallel scan for the end of the run (same result in every warp)
+            const int q = te + lane;
+            const bool same = q < t_end && tiles[q].x == slot;
+            const unsigned m = __ballot_sync(0xffffffffu, same);
+            if (m == 0xffffffffu) { te += 32; continue; }
+            te += __ffs(~m) - 1;
+            break;
         }
-        const uint32_t ph = n_done & 1u;
+        const int c = local_of(slot);
+        if (c < 0) { t = te; continue; }             // model lives on another rank: its owner scores it
+        __syncthreads();                             // previous run fully drained (its epilogues waited on every MMA)
+        stage_model<PREC>(S, a.slab + (size_t)c * P_PAD);
+
         if (warp == 4) {
             if (lane == 0) {
-                if (n_done > 0) mbar_wait(&S.bar_free, ph ^ 1u);      // x tile and TMEM free again
-                mbar_expect_tx(&S.bar_x, 4 * XBLK);
+                auto load_tile = [&](int ti) {
+                    const int row0 = tiles[ti].y;
+                    mbar_expect_tx(&S.bar_x, XBYTES);
 #pragma unroll
-                for (int kb = 0; kb < 4; ++kb) tma_load_2d(S.x + kb * XBLK, &xmap, kb * 32, tl.y, &S.bar_x);
-                mbar_wait(PREC == 3 ? &S.bar_split : &S.bar_x, ph);   // PREC 3: wait for the hi/lo split of the tile
-                tc_fence_after();
-#pragma unroll
-                for (int kb = 0; kb < 4; ++kb) {
-#pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) {
-                        const uint64_t ad = smem_desc_sw128(S.x + kb * XBLK + ks * 32);
-                        const uint64_t bd = smem_desc_sw128(S.w1 + kb * W1BLK + ks * 32);
-                        mma_ss(tmem + COL_D1, ad, bd, IDESC1, (kb | ks) ? 1u : 0u);
-                        if (PREC == 3) {
-                            mma_ss(tmem + COL_D1, ad, smem_desc_sw128(S.w1lo + kb * W1BLK + ks * 32), IDESC1, 1u);
-                            mma_ss(tmem + COL_D1, smem_desc_sw128(S.xlo + kb * XBLK + ks * 32), bd, IDESC1, 1u);
-                        }
+                    for (int kb = 0; kb < 4; ++kb) {
+                        tma_load_2d(S.x + kb * XBLK, &xmap, kb * 32, row0, &S.bar_x);
+                        if (PREC == 3) tma_load_2d(S.xlo + kb * XBLK, &xlomap, kb * 32, row0, &S.bar_x);
                     }
-                }
-                tc_commit(&S.bar_d1);
-                if (need_sse) {
-                    mbar_wait(&S.bar_h2, ph);
+                };
+                load_tile(t);
+                uint32_t gg = g;
+                for (int ti = t; ti < te; ++ti, ++gg) {
+                    const uint32_t b = gg & 1u, ph = gg & 1u, ph1 = (gg >> 1) & 1u;
+                    mbar_wait(&S.bar_x, ph);
                     tc_fence_after();
+                    const uint32_t d1 = tmem + (b ? COL_D1B : COL_D1A);
 #pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) {
-                        const uint64_t bd = smem_desc_sw128(S.w4 + ks * 32);
-                        mma_ts(tmem + COL_D2, tmem + COL_A2 + ks * 8, bd, IDESC2, ks ? 1u : 0u);
-                        if (PREC == 3) {
-                            mma_ts(tmem + COL_D2, tmem + COL_A2 + ks * 8, smem_desc_sw128(S.w4lo + ks * 32), IDESC2, 1u);
-                            mma_ts(tmem + COL_D2, tmem + COL_A2LO + ks * 8, bd, IDESC2, 1u);
+                    for (int kb = 0; kb < 4; ++kb) {
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks) {
+                            const uint64_t ad = smem_desc_sw128(S.x + kb * XBLK + ks * 32);
+                            const uint64_t bd = smem_desc_sw128(S.w1 + kb * W1BLK + ks * 32);
+                            mma_ss(d1, ad, bd, IDESC1, (kb | ks) ? 1u : 0u);
+                            if (PREC == 3) {
+                                mma_ss(d1, ad, smem_desc_sw128(S.w1lo + kb * W1BLK + ks * 32), IDESC1, 1u);
+                                mma_ss(d1, smem_desc_sw128(S.xlo + kb * XBLK + ks * 32), bd, IDESC1, 1u);
+                            }
                         }
                     }
-                    tc_commit(&S.bar_d2);
+                    tc_commit(&S.bar_d1[b]);
+                    mbar_wait(&S.bar_d1[b], ph1);           // MMA 1 has consumed the x tile: refill it now
+                    if (ti + 1 < te) load_tile(ti + 1);
+                    mbar_wait(&S.bar_h2, ph);               // epilogue 1 done with D1 (and h2 is in TMEM)
+                    if (need_sse) {
+                        tc_fence_after();
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks) {
+                            const uint64_t bd = smem_desc_sw128(S.w4 + ks * 32);
+                            mma_ts(tmem + COL_D2, tmem + COL_A2 + ks * 8, bd, IDESC2, ks ? 1u : 0u);
+                            if (PREC == 3) {
+                                mma_ts(tmem + COL_D2, tmem + COL_A2 + ks * 8, smem_desc_sw128(S.w4lo + ks * 32), IDESC2, 1u);
+                                mma_ts(tmem + COL_D2, tmem + COL_A2LO + ks * 8, bd, IDESC2, 1u);
+                            }
+                        }
+                        tc_commit(&S.bar_d2);
+                    }
                 }
             }
             __syncwarp();
         } else {
             const int r = warp * 32 + lane;                      // tile row = TMEM lane
             const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
-            if (PREC == 3) {
-                // split the raw tile into hi (in place) and lo; elementwise, so the swizzled layout is kept
-                mbar_wait(&S.bar_x, ph);
-                uint4* xh = reinterpret_cast<uint4*>(S.x);
-                float4* xl = reinterpret_cast<float4*>(S.xlo);
-#pragma unroll 4
-                for (int i = tid; i < (4 * XBLK) / 16; i += 128) {
-                    const uint4 raw = xh[i];
-                    const uint4 hi = make_uint4(raw.x & 0xFFFFE000u, raw.y & 0xFFFFE000u, raw.z & 0xFFFFE000u, raw.w & 0xFFFFE000u);
-                    xh[i] = hi;
-                    xl[i] = make_float4(__uint_as_float(raw.x) - __uint_as_float(hi.x), __uint_as_float(raw.y) - __uint_as_float(hi.y),
-                                        __uint_as_float(raw.z) - __uint_as_float(hi.z), __uint_as_float(raw.w) - __uint_as_float(hi.w));
+            uint32_t gg = g;
+            for (int ti = t; ti < te; ++ti, ++gg) {
+                const int4 tl = tiles[ti];                        // {slot, row0, nrows, out0}
+                const uint32_t b = gg & 1u, ph = gg & 1u, ph1 = (gg >> 1) & 1u;
+                // ---- epilogue 1: one thread per row ----
+                mbar_wait(&S.bar_d1[b], ph1);
+                tc_fence_after();
+                uint32_t v[32];
+                tmem_ld32(lane_base + (b ? COL_D1B : COL_D1A), v);
+                float h1[28];
+#pragma unroll
+                for (int j = 0; j < H; ++j) h1[j] = fmaxf(__uint_as_float(v[j]) + S.b1[j], 0.f);
+                h1[27] = 0.f;
+                float z[8];
+#pragma unroll
+                for (int i = 0; i < Z; ++i) {
+                    float acc = S.b2[i];
+#pragma unroll
+                    for (int j4 = 0; j4 < 28; j4 += 4) {
+                        const float4 w = *reinterpret_cast<const float4*>(&S.w2[i * 28 + j4]);
+                        acc = fmaf(h1[j4], w.x, fmaf(h1[j4 + 1], w.y, fmaf(h1[j4 + 2], w.z, fmaf(h1[j4 + 3], w.w, acc))));
+                    }
+                    z[i] = acc;
                 }
-                fence_proxy_async();
-                mbar_arrive(&S.bar_split);
-            }
-            // ---- epilogue 1 ----
-            mbar_wait(&S.bar_d1, ph);
-            tc_fence_after();
-            uint32_t v[32];
-            tmem_ld32(lane_base + COL_D1, v);
-            float h1[28];
-#pragma unroll
-            for (int j = 0; j < H; ++j) h1[j] = fmaxf(__uint_as_float(v[j]) + S.b1[j], 0.f);
-            h1[27] = 0.f;
-            float z[8];
-#pragma unroll
-            for (int i = 0; i < Z; ++i) {
-                float acc = S.b2[i];
-#pragma unroll
-                for (int j4 = 0; j4 < 28; j4 += 4) {
-                    const float4 w = *reinterpret_cast<const float4*>(&S.w2[i * 28 + j4]);
-                    acc = fmaf(h1[j4], w.x, fmaf(h1[j4 + 1], w.y, fmaf(h1[j4 + 2], w.z, fmaf(h1[j4 + 3], w.w, acc))));
+                z[7] = 0.f;
+                if (a.out_lat && r < tl.z) {
+                    float4* o = reinterpret_cast<float4*>(a.out_lat + (size_t)(tl.w + r) * 8);
+                    o[0] = make_float4(z[0], z[1], z[2], z[3]);
+                    o[1] = make_float4(z[4], z[5], z[6], 0.f);
                 }
-                z[i] = acc;
-            }
-            z[7] = 0.f;
-            if (a.out_lat && r < tl.z) {
-                float4* o = reinterpret_cast<float4*>(a.out_lat + (size_t)(tl.w + r) * 8);
-                o[0] = make_float4(z[0], z[1], z[2], z[3]);
-                o[1] = make_float4(z[4], z[5], z[6], 0.f);
-            }
-            if (need_sse) {
+                if (!need_sse) {
+                    tc_fence_before();
+                    mbar_arrive(&S.bar_h2);                      // D1 buffer may be reused
+                    continue;
+                }
 #pragma unroll
                 for (int j = 0; j < H; ++j) {
                     const float4 wa = *reinterpret_cast<const float4*>(&S.w3[j * 8]);
@@ -303,62 +334,64 @@ score_rows_tc_kernel(const FmScoreArgs a, const __grid_constant__ CUtensorMap xm
                     acc = fmaf(z[0], wa.x, fmaf(z[1], wa.y, fmaf(z[2], wa.z, fmaf(z[3], wa.w, acc))));
                     acc = fmaf(z[4], wb.x, fmaf(z[5], wb.y, fmaf(z[6], wb.z, acc)));
                     const float hv = fmaxf(acc, 0.f);
-                    if (PREC == 3) { v[j] = trunc_tf32(hv); h1[j] = hv - __uint_as_float(v[j]); }   // h1[] reused for the lo part
+                    if (PREC == 3) { v[j] = trunc_tf32(hv); h1[j] = hv - __uint_as_float(v[j]); }   // h1[] reused: lo part
                     else v[j] = cvt_tf32(hv);
                 }
+                v[27] = __float_as_uint(1.0f);                   // constant-one column: folds b4 into MMA 2
 #pragma unroll
-                for (int j = H; j < 32; ++j) v[j] = 0u;
+                for (int j = H + 1; j < 32; ++j) v[j] = 0u;
                 tmem_st32(lane_base + COL_A2, v);
                 if (PREC == 3) {
 #pragma unroll
                     for (int j = 0; j < H; ++j) v[j] = __float_as_uint(h1[j]);
+                    v[27] = 0u;
                     tmem_st32(lane_base + COL_A2LO, v);
                 }
                 tc_fence_before();
                 mbar_arrive(&S.bar_h2);
-                // ---- epilogue 2 ----
-                mbar_wait(&S.bar_x, ph);            // acquire the TMA-written x tile for generic loads
+                // ---- epilogue 2: squared reconstruction error; x comes straight from global/L2 ----
+                const long long grow = (long long)tl.y + r;
+                const bool live = r < tl.z && grow < x_rows;
+                const float4* xg = reinterpret_cast<const float4*>(a.X + (size_t)(live ? grow : 0) * XP);
+                float4 xa[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) xa[q] = live ? __ldg(xg + q) : make_float4(0.f, 0.f, 0.f, 0.f);
                 mbar_wait(&S.bar_d2, ph);
                 tc_fence_after();
                 float sse = 0.f;
-#pragma unroll 1
-                for (int cb = 0; cb < 4; ++cb) {
-                    tmem_ld32(lane_base + COL_D2 + cb * 32, v);
-                    const unsigned char* xb = S.x + cb * XBLK + r * 128;
 #pragma unroll
-                    for (int q4 = 0; q4 < 8; ++q4) {
-                        float4 xv = *reinterpret_cast<const float4*>(xb + ((q4 ^ (r & 7)) << 4));
-                        if (PREC == 3) {      // x = hi + lo exactly
-                            const float4 xl = *reinterpret_cast<const float4*>(S.xlo + cb * XBLK + r * 128 + ((q4 ^ (r & 7)) << 4));
-                            xv.x += xl.x; xv.y += xl.y; xv.z += xl.z; xv.w += xl.w;
-                        }
-                        const float4 bb = *reinterpret_cast<const float4*>(&S.b4[cb * 32 + q4 * 4]);
-                        const int d0 = cb * 32 + q4 * 4;
-                        const float e0 = (__uint_as_float(v[q4 * 4 + 0]) + bb.x) - xv.x;
-                        const float e1 = (__uint_as_float(v[q4 * 4 + 1]) + bb.y) - xv.y;
-                        const float e2 = (__uint_as_float(v[q4 * 4 + 2]) + bb.z) - xv.z;
-                        const float e3 = (__uint_as_float(v[q4 * 4 + 3]) + bb.w) - xv.w;
+                for (int cb = 0; cb < 4; ++cb) {
+                    float4 xn[8];
+                    if (cb < 3) {
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) xn[q] = live ? __ldg(xg + (cb + 1) * 8 + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                    tmem_ld32(lane_base + COL_D2 + cb * 32, v);
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const int d0 = cb * 32 + q * 4;
+                        const float e0 = __uint_as_float(v[q * 4 + 0]) - xa[q].x, e1 = __uint_as_float(v[q * 4 + 1]) - xa[q].y;
+                        const float e2 = __uint_as_float(v[q * 4 + 2]) - xa[q].z, e3 = __uint_as_float(v[q * 4 + 3]) - xa[q].w;
                         if (d0 + 0 < D) sse = fmaf(e0, e0, sse);
                         if (d0 + 1 < D) sse = fmaf(e1, e1, sse);
                         if (d0 + 2 < D) sse = fmaf(e2, e2, sse);
                         if (d0 + 3 < D) sse = fmaf(e3, e3, sse);
                     }
+                    if (cb < 3) {
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) xa[q] = xn[q];
+                    }
                 }
                 if (r < tl.z) a.out_sse[tl.w + r] = sse;
             }
-            tc_fence_before();
-            mbar_arrive(&S.bar_free);
         }
-        ++n_done;
+        g += (uint32_t)(te - t);
+        t = te;
     }
     // teardown: everyone done with tensor memory, then the allocating warp frees it
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) {
-        if (lane == 0 && n_done > 0) mbar_wait(&S.bar_free, (n_done - 1) & 1u);
-        __syncwarp();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS));
-    }
+    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS));
 }
 
 }  // namespace tc
@@ -382,26 +415,44 @@ EncodeTiledFn get_encode() {
 }
 }  // namespace
 
+static int encode_map(EncodeTiledFn enc, CUtensorMap* map, const float* base, int64_t rows) {
+    const cuuint64_t gdim[2] = {(cuuint64_t)fm::XP, (cuuint64_t)rows};
+    const cuuint64_t gstride[1] = {(cuuint64_t)fm::XP * sizeof(float)};
+    const cuuint32_t box[2] = {32u, (cuuint32_t)fm::tc::TROWS};
+    const cuuint32_t estride[2] = {1u, 1u};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box, estride,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+}
+
+extern "C" int fm_split_residual(const float* x, float* x_lo, int64_t rows, void* stream) {
+    if (rows <= 0) return 0;
+    const size_t n4 = (size_t)rows * fm::XP / 4;
+    const int grid = (int)((n4 + 255) / 256 < 1184 ? (n4 + 255) / 256 : 1184);
+    fm::tc::split_residual_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(x),
+                                                                          reinterpret_cast<float4*>(x_lo), n4);
+    return (int)cudaGetLastError();
+}
+
 // x_rows = number of valid rows behind args->X (rows past it are zero-filled by the TMA unit).
-extern "C" int fm_score_rows_tc(const FmScoreArgs* args, int64_t x_rows, int32_t precision, void* stream) {
-    if (precision != 1 && precision != 3) return (int)cudaErrorInvalidValue;
+// precision 3 needs x_lo = the residual shard of X produced by fm_split_residual (same shape as X).
+extern "C" int fm_score_rows_tc(const FmScoreArgs* args, int64_t x_rows, int32_t precision, const float* x_lo, void* stream) {
     using namespace fm;
     using namespace fm::tc;
     if (args->n_tiles <= 0) return 0;
+    if (precision != 1 && precision != 3) return (int)cudaErrorInvalidValue;
+    const bool x3 = precision == 3;
+    if (x3 && !x_lo) return (int)cudaErrorInvalidValue;
     EncodeTiledFn enc = get_encode();
     if (!enc) return (int)cudaErrorNotSupported;
-    CUtensorMap map;
-    const cuuint64_t gdim[2] = {(cuuint64_t)XP, (cuuint64_t)x_rows};
-    const cuuint64_t gstride[1] = {(cuuint64_t)XP * sizeof(float)};
-    const cuuint32_t box[2] = {32u, (cuuint32_t)TROWS};
-    const cuuint32_t estride[2] = {1u, 1u};
-    CUresult r = enc(&map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(args->X), gdim, gstride, box, estride,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return (int)cudaErrorInvalidValue;
+    CUtensorMap map, lomap;
+    int rc = encode_map(enc, &map, args->X, x_rows);
+    if (rc) return rc;
+    rc = encode_map(enc, &lomap, x3 ? x_lo : args->X, x_rows);
+    if (rc) return rc;
     static int sms = 0;
     if (!sms) { int dev; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
-    const bool x3 = precision == 3;
     const size_t smem = (x3 ? sizeof(TcSmem<3>) : sizeof(TcSmem<1>)) + 1024;
     cudaError_t err = x3 ? cudaFuncSetAttribute(score_rows_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
                          : cudaFuncSetAttribute(score_rows_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -409,7 +460,7 @@ extern "C" int fm_score_rows_tc(const FmScoreArgs* args, int64_t x_rows, int32_t
     int grid = min(args->n_tiles, (x3 ? 1 : 2) * sms);
     const int per = (args->n_tiles + grid - 1) / grid;
     grid = (args->n_tiles + per - 1) / per;
-    if (x3) score_rows_tc_kernel<3><<<grid, NT_TC, smem, (cudaStream_t)stream>>>(*args, map, per);
-    else score_rows_tc_kernel<1><<<grid, NT_TC, smem, (cudaStream_t)stream>>>(*args, map, per);
+    if (x3) score_rows_tc_kernel<3><<<grid, NT_TC, smem, (cudaStream_t)stream>>>(*args, map, lomap, (long long)x_rows, per);
+    else score_rows_tc_kernel<1><<<grid, NT_TC, smem, (cudaStream_t)stream>>>(*args, map, lomap, (long long)x_rows, per);
     return (int)cudaGetLastError();
 }

@@ -148,7 +148,9 @@ __device__ __forceinline__ void adam1(float& w, float& m, float& v, float anchor
     }
     m = fmaf(g - m, 0.1f, m);                     // exp_avg.lerp_(g, 1 - beta1)
     v = fmaf(0.001f * g, g, v * 0.999f);          // exp_avg_sq.mul_(beta2).addcmul_(g, g, 1 - beta2)
-    const float denom = fmaf(sqrtf(v), st.inv_sqrt_bc2, 1e-8f);
+    float sq;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(v));
+    const float denom = fmaf(sq, st.inv_sqrt_bc2, 1e-8f);
     w = fmaf(-st.step_size, __fdividef(m, denom), w);
 }
 
@@ -181,12 +183,12 @@ __device__ __forceinline__ void adam_update4(float* __restrict__ Ws, float* __re
 
 // Weight gradient + Adam for one linear layer: dW[n][k] = sum_b GT[n][b] * A[b][k], dbias[n] = sum_b GT[n][b].
 // item = (n, chunk of 4 consecutive k); the gradient never leaves registers.
-template <int BT, int N, int K, int K4>
+template <int BT, int N, int K, int K4, int STRIDE>
 __device__ __forceinline__ void wgrad_adam(int item0, const float* __restrict__ GT, const float* __restrict__ A,
                                            int AP, int sW, int WP, int sB, float* Ws, float* Ms, float* Vs,
                                            const float* As, const AdamStep& st, float& prox_acc) {
     constexpr int ITEMS = N * K4 + (N + 3) / 4;
-    for (int it = item0; it < ITEMS; it += NT) {
+    for (int it = item0; it < ITEMS; it += STRIDE) {
         if (it < N * K4) {
             const int n = it / K4, kc = it - n * K4;
             float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -221,6 +223,75 @@ __device__ __forceinline__ void wgrad_adam(int item0, const float* __restrict__ 
     }
 }
 
+
+// Weight gradient + Adam for a 4(n) x 4(k) register tile of one big matrix (W1 or W4).  The thread owns
+// these 16 parameters for the whole kernel: their Adam moments stay in registers (m, v), the activations
+// are read once per tile instead of once per output feature, and the weights are touched once per step.
+template <int BT, int N, int K4>
+__device__ __forceinline__ void wgrad_adam_tile(int item, const float* __restrict__ GT, const float* __restrict__ A,
+                                                int AP, int sW, int WP, float* Ws, const float* As, const AdamStep& st,
+                                                float (&m)[16], float (&v)[16], float& prox_acc) {
+    const int nt = item / K4, kc = item - nt * K4;
+    const int n0 = nt * 4, nvalid = min(4, N - n0);
+    float g[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) g[i] = 0.f;
+    const float* a = A + 4 * kc;
+#pragma unroll
+    for (int b4 = 0; b4 < BT; b4 += 4) {
+        const float4 a0 = *reinterpret_cast<const float4*>(a + (b4 + 0) * AP);
+        const float4 a1 = *reinterpret_cast<const float4*>(a + (b4 + 1) * AP);
+        const float4 a2 = *reinterpret_cast<const float4*>(a + (b4 + 2) * AP);
+        const float4 a3 = *reinterpret_cast<const float4*>(a + (b4 + 3) * AP);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            if (q < nvalid) {
+                const float4 gg = *reinterpret_cast<const float4*>(GT + (n0 + q) * BT + b4);
+                g[q * 4 + 0] = fmaf(gg.x, a0.x, fmaf(gg.y, a1.x, fmaf(gg.z, a2.x, fmaf(gg.w, a3.x, g[q * 4 + 0]))));
+                g[q * 4 + 1] = fmaf(gg.x, a0.y, fmaf(gg.y, a1.y, fmaf(gg.z, a2.y, fmaf(gg.w, a3.y, g[q * 4 + 1]))));
+                g[q * 4 + 2] = fmaf(gg.x, a0.z, fmaf(gg.y, a1.z, fmaf(gg.z, a2.z, fmaf(gg.w, a3.z, g[q * 4 + 2]))));
+                g[q * 4 + 3] = fmaf(gg.x, a0.w, fmaf(gg.y, a1.w, fmaf(gg.z, a2.w, fmaf(gg.w, a3.w, g[q * 4 + 3]))));
+            }
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        if (q < nvalid) {
+            const int idx = sW + (n0 + q) * WP + 4 * kc;
+            float4 w = *reinterpret_cast<float4*>(Ws + idx);
+            float4 an = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (st.mu != 0.f) an = *reinterpret_cast<const float4*>(As + idx);
+            adam1(w.x, m[q * 4 + 0], v[q * 4 + 0], an.x, g[q * 4 + 0], st, prox_acc);
+            adam1(w.y, m[q * 4 + 1], v[q * 4 + 1], an.y, g[q * 4 + 1], st, prox_acc);
+            adam1(w.z, m[q * 4 + 2], v[q * 4 + 2], an.z, g[q * 4 + 2], st, prox_acc);
+            adam1(w.w, m[q * 4 + 3], v[q * 4 + 3], an.w, g[q * 4 + 3], st, prox_acc);
+            *reinterpret_cast<float4*>(Ws + idx) = w;
+        }
+    }
+}
+
+// moments of a register tile <-> packed global rows (p = off + n * K + k)
+template <int N, int K, int K4>
+__device__ __forceinline__ void tile_moments_io(int item, int off, float* gm, float* gv, float (&m)[16], float (&v)[16],
+                                                bool store) {
+    const int nt = item / K4, kc = item - nt * K4;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+#pragma unroll
+        for (int cix = 0; cix < 4; ++cix) {
+            const int n = nt * 4 + q, k = kc * 4 + cix;
+            const bool ok = n < N && k < K;
+            if (store) { if (ok) { gm[off + n * K + k] = m[q * 4 + cix]; gv[off + n * K + k] = v[q * 4 + cix]; } }
+            else { m[q * 4 + cix] = ok ? gm[off + n * K + k] : 0.f; v[q * 4 + cix] = ok ? gv[off + n * K + k] : 0.f; }
+        }
+    }
+}
+
+constexpr int W1_TILES = ((H + 3) / 4) * 29;    // 7 x 29 = 203 register tiles
+constexpr int W4_TILES = ((D + 3) / 4) * 7;     // 29 x 7 = 203
+constexpr int ROLE_W1 = 0, ROLE_W4 = 224, ROLE_SMALL = 448;   // first thread of each role (warp aligned)
+static_assert(W1_TILES <= ROLE_W4 - ROLE_W1 && W4_TILES <= ROLE_SMALL - ROLE_W4, "role ranges too small");
+
 template <int BT>
 struct TrainSmem {
     static constexpr int HP = 28, ZP = 8, XHP = 116;
@@ -249,7 +320,7 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
     using SM = TrainSmem<BT>;
     SM& S = *reinterpret_cast<SM*>(smem_raw);
     float* As = reinterpret_cast<float*>(smem_raw + ((sizeof(SM) + 15) / 16) * 16);  // valid iff mu != 0
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int c = a.sel_local[blockIdx.x];
     const int g = a.first_client + c;
     const int tr0 = a.train_off[c], n_tr = a.train_off[c + 1] - tr0;
@@ -277,6 +348,11 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
         S.W[s] = gp[p]; S.M[s] = gm[p]; S.V[s] = gv[p];
         if (prox) As[s] = a.anchor[(size_t)c * P_PAD + p];
     }
+    float tm[16], tv[16];          // Adam moments of this thread's register tile (roles W1 / W4)
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { tm[i] = 0.f; tv[i] = 0.f; }
+    if (tid < ROLE_W4) { if (tid < W1_TILES) tile_moments_io<H, D, 29>(tid, OFF_W1, gm, gv, tm, tv, false); }
+    else if (tid < ROLE_SMALL) { if (tid - ROLE_W4 < W4_TILES) tile_moments_io<D, H, 7>(tid - ROLE_W4, OFF_W4, gm, gv, tm, tv, false); }
     fence_proxy_async();
     __syncthreads();
 
@@ -325,18 +401,38 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
             // ---- forward ----
             layer_nt<BT, H, 29, 4, true>(X, XP, S.W + S_W1, W1P, S.W + S_B1, S.h1, SM::HP);
             __syncthreads();
-            layer_nt<BT, Z, 7, 4, false>(S.h1, SM::HP, S.W + S_W2, W2P, S.W + S_B2, S.z, SM::ZP);
-            __syncthreads();
-            layer_nt<BT, H, 2, 1, true>(S.z, SM::ZP, S.W + S_W3, W3P, S.W + S_B3, S.h2, SM::HP);
-            if (tid < BT) {
+            // bottleneck 27 -> 7 -> 27: one warp per batch row, no block barrier between the two layers
+            for (int b = warp; b < BT; b += NT / 32) {
+                const int i = lane >> 2, sK = lane & 3;
+                float zp = 0.f;
+                if (i < Z) {
+#pragma unroll
+                    for (int j = sK; j < H; j += 4) zp = fmaf(S.h1[b * SM::HP + j], S.W[S_W2 + i * W2P + j], zp);
+                }
+                zp += __shfl_xor_sync(0xffffffffu, zp, 1);
+                zp += __shfl_xor_sync(0xffffffffu, zp, 2);
+                if (i < Z) zp += S.W[S_B2 + i];
+                float zz[Z];
                 float s2 = 0.f;
 #pragma unroll
-                for (int i = 0; i < Z; ++i) s2 = fmaf(S.z[tid * SM::ZP + i], S.z[tid * SM::ZP + i], s2);
+                for (int k = 0; k < Z; ++k) { zz[k] = __shfl_sync(0xffffffffu, zp, k * 4); s2 = fmaf(zz[k], zz[k], s2); }
                 const float nz = sqrtf(s2);
-                S.znorm[tid] = nz;
-                if (tid < rows && a.shrink_lambda != 0.f) {
-                    const float contrib = a.shrink_lambda * nz / (float)rows;
-                    if (is_train) loss_acc += contrib; else vloss_acc += contrib;
+                if (lane < H) {
+                    const float4 wa = *reinterpret_cast<const float4*>(S.W + S_W3 + lane * W3P);
+                    const float4 wb = *reinterpret_cast<const float4*>(S.W + S_W3 + lane * W3P + 4);
+                    float acc = S.W[S_B3 + lane];
+                    acc = fmaf(zz[0], wa.x, fmaf(zz[1], wa.y, fmaf(zz[2], wa.z, fmaf(zz[3], wa.w, acc))));
+                    acc = fmaf(zz[4], wb.x, fmaf(zz[5], wb.y, fmaf(zz[6], wb.z, acc)));
+                    S.h2[b * SM::HP + lane] = fmaxf(acc, 0.f);
+                }
+                const float zmine = __shfl_sync(0xffffffffu, zp, (lane < Z ? lane : 0) * 4);
+                if (lane < Z) S.z[b * SM::ZP + lane] = zmine;
+                if (lane == 0) {
+                    S.znorm[b] = nz;
+                    if (b < rows && a.shrink_lambda != 0.f) {
+                        const float contrib = a.shrink_lambda * nz / (float)rows;
+                        if (is_train) loss_acc += contrib; else vloss_acc += contrib;
+                    }
                 }
             }
             __syncthreads();
@@ -383,29 +479,61 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
             // ---- backward ----
             layer_dgrad<BT, D, H, 4, true>(S.dxT, S.W + S_W4, W4P, S.h2, SM::HP, S.dp2T);
             __syncthreads();
-            float prox_acc = 0.f;
-            AdamStep st;
-            st.step_size = S.sc[0]; st.inv_sqrt_bc2 = S.sc[1]; st.mu = a.fedprox_mu;
-            // (update W4,b4) || (dz = dp2 W3 + shrink gradient)
-            wgrad_adam<BT, D, H, 7>(tid, S.dxT, S.h2, SM::HP, S_W4, W4P, S_B4, S.W, S.M, S.V, As, st, prox_acc);
-            layer_dgrad<BT, H, Z, 4, false>(S.dp2T, S.W + S_W3, W3P, nullptr, 0, S.dzT);
-            __syncthreads();
-            if (a.shrink_lambda != 0.f && tid < Z * BT) {
-                const int i = tid / BT, b = tid - i * BT;
-                if (b < rows) {
+            // bottleneck backward, one warp per batch row: dz = dp2 W3 + shrink gradient, dp1 = relu'(h1) * (dz W2)
+            for (int b = warp; b < BT; b += NT / 32) {
+                const int i = lane >> 2, sK = lane & 3;
+                float dzp = 0.f;
+                if (i < Z) {
+#pragma unroll
+                    for (int j = sK; j < H; j += 4) dzp = fmaf(S.dp2T[j * BT + b], S.W[S_W3 + j * W3P + i], dzp);
+                }
+                dzp += __shfl_xor_sync(0xffffffffu, dzp, 1);
+                dzp += __shfl_xor_sync(0xffffffffu, dzp, 2);
+                if (i < Z && a.shrink_lambda != 0.f && b < rows) {
                     const float nz = S.znorm[b];
-                    if (nz > 0.f) S.dzT[i * BT + b] += a.shrink_lambda / (float)rows * S.z[b * SM::ZP + i] / nz;
+                    if (nz > 0.f) dzp += a.shrink_lambda / (float)rows * S.z[b * SM::ZP + i] / nz;
+                }
+                float dzz[Z];
+#pragma unroll
+                for (int k = 0; k < Z; ++k) dzz[k] = __shfl_sync(0xffffffffu, dzp, k * 4);
+                const float dzmine = __shfl_sync(0xffffffffu, dzp, (lane < Z ? lane : 0) * 4);
+                if (lane < Z) S.dzT[lane * BT + b] = dzmine;
+                if (lane < H) {
+                    float gsum = 0.f;
+#pragma unroll
+                    for (int k = 0; k < Z; ++k) gsum = fmaf(dzz[k], S.W[S_W2 + k * W2P + lane], gsum);
+                    S.dp1T[lane * BT + b] = S.h1[b * SM::HP + lane] > 0.f ? gsum : 0.f;
                 }
             }
             __syncthreads();
-            // (update W3,b3) || (dp1 = relu'(h1) * dz W2)
-            wgrad_adam<BT, H, Z, 2>(tid, S.dp2T, S.z, SM::ZP, S_W3, W3P, S_B3, S.W, S.M, S.V, As, st, prox_acc);
-            layer_dgrad<BT, Z, H, 1, true>(S.dzT, S.W + S_W2, W2P, S.h1, SM::HP, S.dp1T);
-            __syncthreads();
-            // update W2,b2 and W1,b1
-            wgrad_adam<BT, Z, H, 7>(tid, S.dzT, S.h1, SM::HP, S_W2, W2P, S_B2, S.W, S.M, S.V, As, st, prox_acc);
-            wgrad_adam<BT, H, D, 29>(tid, S.dp1T, X, XP, S_W1, W1P, S_B1, S.W, S.M, S.V, As, st, prox_acc);
-            if (prox) loss_acc = fmaf(a.fedprox_mu, prox_acc, loss_acc);
+            // ---- all parameter updates in one balanced phase (roles are warp aligned) ----
+            {
+                float prox_acc = 0.f;
+                AdamStep st;
+                st.step_size = S.sc[0]; st.inv_sqrt_bc2 = S.sc[1]; st.mu = a.fedprox_mu;
+                if (tid < ROLE_W4) {
+                    if (tid < W1_TILES)
+                        wgrad_adam_tile<BT, H, 29>(tid, S.dp1T, X, XP, S_W1, W1P, S.W, As, st, tm, tv, prox_acc);
+                } else if (tid < ROLE_SMALL) {
+                    if (tid - ROLE_W4 < W4_TILES)
+                        wgrad_adam_tile<BT, D, 7>(tid - ROLE_W4, S.dxT, S.h2, SM::HP, S_W4, W4P, S.W, As, st, tm, tv, prox_acc);
+                } else {
+                    constexpr int NS = NT - ROLE_SMALL;
+                    const int t0 = tid - ROLE_SMALL;
+                    wgrad_adam<BT, H, Z, 2, NS>(t0, S.dp2T, S.z, SM::ZP, S_W3, W3P, S_B3, S.W, S.M, S.V, As, st, prox_acc);
+                    wgrad_adam<BT, Z, H, 7, NS>(t0, S.dzT, S.h1, SM::HP, S_W2, W2P, S_B2, S.W, S.M, S.V, As, st, prox_acc);
+                    // biases of the two big layers (their weight tiles live in registers of other threads)
+                    for (int n = t0; n < H + D; n += NS) {
+                        const bool first = n < H;
+                        const float* gt = first ? S.dp1T + n * BT : S.dxT + (n - H) * BT;
+                        float gsum = 0.f;
+#pragma unroll
+                        for (int bb = 0; bb < BT; ++bb) gsum += gt[bb];
+                        adam_update(S.W, S.M, S.V, As, first ? S_B1 + n : S_B4 + (n - H), gsum, st, prox_acc);
+                    }
+                }
+                if (prox) loss_acc = fmaf(a.fedprox_mu, prox_acc, loss_acc);
+            }
             __syncthreads();
         }
         // ---- epoch bookkeeping (reference: client_trainer.py:385, :404-417) ----
@@ -439,8 +567,12 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
     __syncthreads();
     for (int p = tid; p < NP; p += NT) {
         const int s = sidx(p);
-        gp[p] = S.W[s]; gm[p] = S.M[s]; gv[p] = S.V[s];
+        gp[p] = S.W[s];
+        const int tt = tensor_of(p);
+        if (tt != 0 && tt != 6) { gm[p] = S.M[s]; gv[p] = S.V[s]; }     // W1 / W4 moments live in registers
     }
+    if (tid < ROLE_W4) { if (tid < W1_TILES) tile_moments_io<H, D, 29>(tid, OFF_W1, gm, gv, tm, tv, true); }
+    else if (tid < ROLE_SMALL) { if (tid - ROLE_W4 < W4_TILES) tile_moments_io<D, H, 7>(tid - ROLE_W4, OFF_W4, gm, gv, tm, tv, true); }
     if (tid == 0) {
         a.adam_t[c] = t_step;
         a.epochs_run[c] = epochs_done;

@@ -132,7 +132,8 @@ def load() -> C.CDLL:
     for name, argt in (
         ("fm_train_clients", [C.POINTER(FmTrainArgs), c_vp]),
         ("fm_score_rows", [C.POINTER(FmScoreArgs), c_vp]),
-        ("fm_score_rows_tc", [C.POINTER(FmScoreArgs), C.c_int64, C.c_int32, c_vp]),
+        ("fm_score_rows_tc", [C.POINTER(FmScoreArgs), C.c_int64, C.c_int32, c_vp, c_vp]),
+        ("fm_split_residual", [c_vp, c_vp, C.c_int64, c_vp]),
         ("fm_vote_normalise", [c_vp, C.c_int32, c_vp, c_vp]),
         ("fm_chunk_mean", [c_vp, C.c_int32, C.c_int32, C.c_int32, c_vp, c_vp, C.c_int32, C.c_int32,
                            C.c_int32, c_vp, c_vp]),

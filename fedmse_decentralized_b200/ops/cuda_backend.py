@@ -64,6 +64,7 @@ class CudaBackend:
         self.launches = 0
         self._slabs = []
         self._tile_cache: Dict = {}
+        self._resid: Dict = {}
 
     # ------------------------------------------------------------------ setup
     def _stream(self) -> int:
@@ -145,6 +146,27 @@ class CudaBackend:
         self._pin_ev[i] = ev
         self.agg_pos.fill_(-1)
 
+    def _residual(self, X: torch.Tensor, refresh: bool = False) -> torch.Tensor:
+        """Residual shard ``X - trunc_tf32(X)`` of a data matrix for the 3xTF32 scoring kernel (made once
+        per matrix; call with ``refresh=True`` after the matrix was overwritten with new rows)."""
+        key = X.data_ptr()
+        ent = self._resid.get(key)
+        if ent is None or ent.shape != X.shape:
+            ent = torch.empty_like(X)
+            self._resid[key] = ent
+            refresh = True
+        if refresh:
+            _lib.check(self.lib.fm_split_residual(_ptr(X), _ptr(ent), X.shape[0], self._stream()), "split_residual")
+            self.launches += 1
+        return ent
+
+    def data_updated(self, *mats: torch.Tensor) -> None:
+        """Tell the backend that device-resident data matrices were overwritten (fresh traffic)."""
+        if self.tc == 3:
+            for X in mats:
+                if X.data_ptr() in self._resid:
+                    self._residual(X, refresh=True)
+
     def _tiles(self, key, builder) -> torch.Tensor:
         t = self._tile_cache.get(key)
         if t is None:
@@ -158,7 +180,9 @@ class CudaBackend:
         a = _lib.FmScoreArgs(_ptr(slab), _ptr(slot_client), first, n_local, _ptr(X), _ptr(tiles),
                              tiles.shape[0], _ptr(out_sse), _ptr(out_lat))
         if self.tc:
-            _lib.check(self.lib.fm_score_rows_tc(C.byref(a), X.shape[0], self.tc, self._stream()), "score_rows_tc")
+            lo = self._residual(X) if self.tc == 3 else None
+            _lib.check(self.lib.fm_score_rows_tc(C.byref(a), X.shape[0], self.tc, _ptr(lo), self._stream()),
+                       "score_rows_tc")
         else:
             _lib.check(self.lib.fm_score_rows(C.byref(a), self._stream()), "score_rows")
         self.launches += 1

@@ -339,6 +339,23 @@ class FederationEngine:
             n = res.epochs_run.get(g, 0)
             artefacts.save_tracking(d, [(float(logs[k, e, 0]), float(logs[k, e, 1])) for e in range(n)])
 
+    # ------------------------------------------------------------------ streaming data
+    def update_local_data(self, train_x: Optional[torch.Tensor] = None, valid_x: Optional[torch.Tensor] = None
+                          ) -> None:
+        """Replace the rank's local training / validation rows with fresh traffic (same shapes), e.g. from
+        pinned host memory each round; copies are asynchronous on the current stream."""
+        sh = self.sh
+        touched = []
+        if train_x is not None:
+            sh.train.x.copy_(train_x, non_blocking=True)
+            touched.append(sh.train.x)
+        if valid_x is not None:
+            v0, v1 = sh.valid.off_host[self.first], sh.valid.off_host[self.first + self.n_local]
+            sh.valid.x[v0:v1].copy_(valid_x, non_blocking=True)
+            touched.append(sh.valid.x)
+        if touched and hasattr(self.backend, "data_updated"):
+            self.backend.data_updated(*touched)
+
     # ------------------------------------------------------------------ resume (absent in the reference)
     def snapshot(self) -> Dict:
         return {"state": self.state.state_dict(), "agg_count_host": list(self.agg_count_host),

@@ -88,8 +88,11 @@ int fm_score_rows(const FmScoreArgs* args, void* stream);
 /* Same contract on the tensor cores (tcgen05.mma kind::tf32, accumulators in TMEM, tiles by TMA):
  * tiles hold up to 128 rows; x_rows = number of rows behind X (rows past it read as zero).
  * precision 1: single TF32 pass (inputs truncated to 10-bit mantissa, fp32 accumulate);
- * precision 3: error-compensated 3xTF32 (hi/lo split of both operands, ~fp32 accuracy). */
-int fm_score_rows_tc(const FmScoreArgs* args, int64_t x_rows, int32_t precision, void* stream);
+ * precision 3: error-compensated 3xTF32 (hi/lo split of both operands, ~fp32 accuracy);
+ * precision 3 reads X as the hi part (the tensor core ignores the low 13 mantissa bits of an fp32
+ * operand) and needs x_lo = X - trunc_tf32(X), the residual shard made once by fm_split_residual. */
+int fm_score_rows_tc(const FmScoreArgs* args, int64_t x_rows, int32_t precision, const float* x_lo, void* stream);
+int fm_split_residual(const float* x, float* x_lo, int64_t rows, void* stream);
 
 /* Column-normalise a vote matrix: out = (V - mean) / (unbiased std + 1e-8)
  * (reference: client_trainer.py:221-223).  V and out are [rows][FM_XP]; out is caller scratch. */
