@@ -17,6 +17,9 @@
 
 namespace fm {
 
+// phase timing (debug): thread 0 of CTA 0 accumulates SM cycles per phase when args.phase_cycles != NULL
+#define FM_TICK(slot) do { if (dbg) { dbg_sink += *reinterpret_cast<volatile int*>(&S.flag[0]); /* forces the deferred barrier wait */ const long long now_ = clock64(); dbg_acc[slot] += now_ - dbg_t; dbg_t = now_; } } while (0)
+
 constexpr int NT = 512;  // threads per CTA
 
 // shared-memory weight layout: every matrix row padded to a multiple of 4 floats so rows can be
@@ -366,9 +369,9 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
         bulk_g2s(&S.x[buf][0], src, bytes, &S.bar[buf]);
     };
 
-    int t_step = a.adam_t[c];    // tracked by thread 0 only
+    int t_step = a.adam_t[c];    // tracked by thread NT-1 only
     double b1t = 1.0, b2t = 1.0;
-    if (tid == 0) { b1t = pow(0.9, (double)t_step); b2t = pow(0.999, (double)t_step); }
+    if (tid == NT - 1) { b1t = pow(0.9, (double)t_step); b2t = pow(0.999, (double)t_step); }
     float min_valid = __int_as_float(0x7f800000);
     int worse = 0, epochs_done = 0;
     uint32_t uses0 = 0, uses1 = 0;   // completed waits per buffer -> parity
@@ -378,6 +381,10 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
     outstanding = (steps_per_epoch > 0 && a.epochs > 0 && n_tr > 0);
     const int n_epochs = (n_tr > 0) ? a.epochs : 0;
 
+    const bool dbg = a.phase_cycles != nullptr && blockIdx.x == 0 && tid == 0;
+    long long dbg_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long dbg_t = clock64();
+    int dbg_sink = 0;
     for (int e = 0; e < n_epochs; ++e) {
         float loss_acc = 0.f;   // this thread's share of sum over train batches of batch loss
         float vloss_acc = 0.f;
@@ -387,20 +394,23 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
             const int r0 = is_train ? qe * B : (qe - nbt) * B;
             const int rows = min(B, (is_train ? n_tr : n_va) - r0);
             // S0: wait for this batch, prefetch the next one into the other buffer
+            FM_TICK(7);
             mbar_wait(&S.bar[buf], (buf ? uses1 : uses0) & 1u);
             if (buf) ++uses1; else ++uses0;
             const bool has_next = (qe + 1 < steps_per_epoch) || (e + 1 < n_epochs);
             if (tid == 0 && has_next) issue((qe + 1) % steps_per_epoch, buf ^ 1);
             outstanding = has_next;
             const float* X = &S.x[buf][0];
-            if (is_train && tid == 0) {     // bias corrections in double, broadcast through smem
-                ++t_step; b1t *= 0.9; b2t *= 0.999;
+            FM_TICK(0);
+            if (is_train && tid == NT - 1) {   // bias corrections in double by an otherwise idle thread (warp 15 has
+                ++t_step; b1t *= 0.9; b2t *= 0.999;   // no items in the first layer); consumed three barriers later
                 S.sc[0] = (float)((double)a.lr / (1.0 - b1t));
                 S.sc[1] = (float)(1.0 / sqrt(1.0 - b2t));
             }
             // ---- forward ----
             layer_nt<BT, H, 29, 4, true>(X, XP, S.W + S_W1, W1P, S.W + S_B1, S.h1, SM::HP);
             __syncthreads();
+            FM_TICK(1);
             // bottleneck 27 -> 7 -> 27: one warp per batch row, no block barrier between the two layers
             for (int b = warp; b < BT; b += NT / 32) {
                 const int i = lane >> 2, sK = lane & 3;
@@ -436,6 +446,7 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
                 }
             }
             __syncthreads();
+            FM_TICK(2);
             // output layer fused with the reconstruction loss and its gradient
             {
                 constexpr int ITEMS = D * (BT / 4);
@@ -475,10 +486,12 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
                 if (is_train) loss_acc = fmaf(lsum, inv, loss_acc); else vloss_acc = fmaf(lsum, inv, vloss_acc);
             }
             __syncthreads();
+            FM_TICK(3);
             if (!is_train) continue;
             // ---- backward ----
             layer_dgrad<BT, D, H, 4, true>(S.dxT, S.W + S_W4, W4P, S.h2, SM::HP, S.dp2T);
             __syncthreads();
+            FM_TICK(4);
             // bottleneck backward, one warp per batch row: dz = dp2 W3 + shrink gradient, dp1 = relu'(h1) * (dz W2)
             for (int b = warp; b < BT; b += NT / 32) {
                 const int i = lane >> 2, sK = lane & 3;
@@ -506,6 +519,7 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
                 }
             }
             __syncthreads();
+            FM_TICK(5);
             // ---- all parameter updates in one balanced phase (roles are warp aligned) ----
             {
                 float prox_acc = 0.f;
@@ -535,6 +549,7 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
                 if (prox) loss_acc = fmaf(a.fedprox_mu, prox_acc, loss_acc);
             }
             __syncthreads();
+            FM_TICK(6);
         }
         // ---- epoch bookkeeping (reference: client_trainer.py:385, :404-417) ----
         float prox_val = 0.f;
@@ -573,8 +588,9 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
     }
     if (tid < ROLE_W4) { if (tid < W1_TILES) tile_moments_io<H, D, 29>(tid, OFF_W1, gm, gv, tm, tv, true); }
     else if (tid < ROLE_SMALL) { if (tid - ROLE_W4 < W4_TILES) tile_moments_io<D, H, 7>(tid - ROLE_W4, OFF_W4, gm, gv, tm, tv, true); }
+    if (dbg) { FM_TICK(7); for (int i = 0; i < 8; ++i) a.phase_cycles[i] = (unsigned long long)dbg_acc[i] + (dbg_sink & 0); }
+    if (tid == NT - 1) a.adam_t[c] = t_step;
     if (tid == 0) {
-        a.adam_t[c] = t_step;
         a.epochs_run[c] = epochs_done;
         a.trained_rounds[c] += 1;
         for (int e = epochs_done; e < a.log_stride; ++e) {

@@ -31,7 +31,7 @@ class FmTrainArgs(C.Structure):
                 ("sel_local", c_vp), ("n_sel", C.c_int32), ("first_client", C.c_int32),
                 ("epochs", C.c_int32), ("batch", C.c_int32), ("patience", C.c_int32),
                 ("log_stride", C.c_int32), ("lr", C.c_float), ("shrink_lambda", C.c_float),
-                ("fedprox_mu", C.c_float)]
+                ("fedprox_mu", C.c_float), ("phase_cycles", c_vp)]
 
 
 class FmScoreArgs(C.Structure):

@@ -199,7 +199,8 @@ class CudaBackend:
             _ptr(st.loss_log), _ptr(st.epochs_run), _ptr(st.trained_rounds),
             _ptr(sh.train.x), _ptr(sh.train.off), _ptr(sh.valid.x), _ptr(sh.valid.off),
             _ptr(self.ctl_sel_local), n, sh.first_client, hp.epochs, hp.batch_size, hp.patience,
-            st.loss_log.shape[1], hp.lr, hp.shrink_lambda, hp.fedprox_mu)
+            st.loss_log.shape[1], hp.lr, hp.shrink_lambda, hp.fedprox_mu,
+            _ptr(getattr(self, "phase_cycles", None)))
         _lib.check(self.lib.fm_train_clients(C.byref(a), self._stream()), "train_clients")
         self.launches += 1
 

@@ -128,7 +128,7 @@ class ClientTrainer:
         a = _lib.FmTrainArgs(p.data_ptr(), m.data_ptr(), v.data_ptr(), t.data_ptr(), self.anchor.data_ptr(),
                              best.data_ptr(), logbuf.data_ptr(), ep.data_ptr(), tr.data_ptr(), xt.data_ptr(),
                              toff.data_ptr(), xv.data_ptr(), voff.data_ptr(), sel.data_ptr(), 1, 0, hp.epochs,
-                             hp.batch_size, hp.patience, logbuf.shape[1], hp.lr, hp.shrink_lambda, hp.fedprox_mu)
+                             hp.batch_size, hp.patience, logbuf.shape[1], hp.lr, hp.shrink_lambda, hp.fedprox_mu, 0)
         _lib.check(lib.fm_train_clients(C.byref(a), torch.cuda.current_stream(dev).cuda_stream), "train_clients")
         self.adam_t = int(t.item())
         n = int(ep.item())

@@ -24,6 +24,7 @@ ap.add_argument("--iters", type=int, default=3)
 ap.add_argument("--epochs", type=int, default=5)
 ap.add_argument("--patience", type=int, default=1)
 ap.add_argument("--score-precision", default="fp32")
+ap.add_argument("--phase-cycles", action="store_true")
 a = ap.parse_args()
 dev = torch.device("cuda", 0)
 random.seed(0); np.random.seed(0); torch.manual_seed(0)
@@ -33,6 +34,8 @@ cfg = ExperimentConfig(epoch=a.epochs, network_size=a.clients, backend="cuda", w
                        save_client_models=False, local_patience=a.patience, score_precision=a.score_precision)
 eng = FederationEngine(cfg, sh, "hybrid", "mse_avg")
 be, st = eng.backend, eng.state
+if a.phase_cycles:
+    be.phase_cycles = torch.zeros(8, dtype=torch.int64, device=dev)
 ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
 for it in range(a.iters):
     ctl = eng.make_control(it)
@@ -52,3 +55,8 @@ for it in range(a.iters):
         ep = st.epochs_run[st.epochs_run > 0]
         extra = f" epochs max {int(ep.max())} mean {float(ep.float().mean()):.2f}"
     print(f"{a.what} iter {it}: {ev[0].elapsed_time(ev[1]):.3f} ms{extra}")
+    if a.phase_cycles and a.what == "train":
+        names = ["wait-batch", "P1 fwd 115->27", "bottleneck fwd", "P4 out+loss", "B1 dgrad", "bottleneck bwd", "update", "loop/epoch"]
+        cyc = be.phase_cycles.tolist()
+        tot = sum(cyc)
+        print("  phase cycles (CTA 0): " + ", ".join(f"{n} {c/1e3:.0f}k ({100*c/tot:.0f}%)" for n, c in zip(names, cyc)))
