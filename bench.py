@@ -167,6 +167,7 @@ def run_ours(args):
         return float(mx[0]), float(mx[1]) / 1e3, int(tot[2]), eng.backend.launches - launches0, res
 
     timed(args.warmup, 0, False)
+    eng.timer.reset()               # phase means below are steady state (first-use costs stay in the warm-up)
     sampler = ClockSampler(torch.cuda.current_device())
     if comm.rank == 0:
         sampler.start()

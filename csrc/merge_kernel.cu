@@ -21,10 +21,54 @@ __device__ __forceinline__ void owner_of(int g, int n_global, int world, int& ra
     else { const int q = (g - cut) / base; rank = rem + q; local = (g - cut) - q * base; }
 }
 
+// ---- cross-GPU scalar exchange through peer-mapped control blocks (no NCCL on the merge path) ----
+// Every rank owns a control block {float board[2][FM_MAX_SEL]; unsigned arrive[4]} in peer-mapped memory.
+// A producer writes the entries it owns into the board of EVERY rank (plain stores over NVLink), fences at
+// system scope, and bumps arrive[which] on every rank with a release reduction; a consumer kernel spins with
+// acquire loads on its own arrive[which] until all ranks of this exchange have arrived, then reads its board.
+__device__ __forceinline__ void signal_release_add(unsigned* addr) {
+    asm volatile("red.release.sys.global.add.u32 [%0], 1;" ::"l"(addr) : "memory");
+}
+__device__ __forceinline__ unsigned load_acquire_sys(const unsigned* addr) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+    return v;
+}
+// block-wide: returns once arrive >= expect (thread 0 polls; everyone else waits at the barrier)
+__device__ __forceinline__ void wait_arrivals(const unsigned* arrive, unsigned expect) {
+    if (arrive == nullptr) return;
+    if (threadIdx.x == 0) {
+        while ((int)(load_acquire_sys(arrive) - expect) < 0) __nanosleep(64);
+    }
+    __syncthreads();
+}
+
+constexpr int CTL_BOARD_FLOATS = 2 * FM_MAX_SEL;      // two boards (vote, mse)
+__device__ __forceinline__ float* ctl_board(float* ctl, int which) { return ctl + which * FM_MAX_SEL; }
+__device__ __forceinline__ unsigned* ctl_arrive(float* ctl, int which) {
+    return reinterpret_cast<unsigned*>(ctl + CTL_BOARD_FLOATS) + which;
+}
+
+__global__ void __launch_bounds__(256) publish_kernel(const float* __restrict__ local, const int* __restrict__ slot_client,
+                                                      int first_client, int n_local, int n, float* const* peer_ctl,
+                                                      int world, int which) {
+    for (int slot = threadIdx.x; slot < n; slot += blockDim.x) {
+        const int c = (slot_client ? slot_client[slot] : first_client + slot) - first_client;
+        if (c < 0 || c >= n_local) continue;          // not mine: its owner publishes it
+        const float v = local[slot];
+        for (int r = 0; r < world; ++r) ctl_board(peer_ctl[r], which)[slot] = v;
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x < world) signal_release_add(ctl_arrive(peer_ctl[threadIdx.x], which));
+}
+
 __global__ void elect_kernel(const float* __restrict__ scores, const int* __restrict__ sel, int n_sel, int voter_pos,
-                             const int* __restrict__ agg_count, int max_agg, int* __restrict__ agg_pos) {
+                             const int* __restrict__ agg_count, int max_agg, int* __restrict__ agg_pos,
+                             const unsigned* arrive, unsigned expect) {
     // single warp: lexicographic (score, position) argmin over eligible candidates
     const int lane = threadIdx.x;
+    wait_arrivals(arrive, expect);        // multi-GPU: scores is this rank's board, complete once all ranks arrived
     float best = __int_as_float(0x7f800000);
     int bpos = 0x7fffffff;
     if (voter_pos >= 0) {
@@ -56,8 +100,12 @@ __global__ void __launch_bounds__(MNT) merge_kernel(const FmMergeArgs a) {
     float* wts = reinterpret_cast<float*>(msm + (size_t)a.n_sel * sizeof(float*));   // [n_sel]
     __shared__ double red[34];
     const int ap = a.agg_pos[0];
-    if (ap < 0) return;
     const int tid = threadIdx.x, n = a.n_sel;
+    if (ap < 0) {                         // nothing to merge; keep the arrival counters in step with the host
+        if (a.done_ctl != nullptr && blockIdx.x == 0 && tid < a.world) signal_release_add(ctl_arrive(a.done_ctl[tid], 2));
+        return;
+    }
+    wait_arrivals(a.arrive, a.expect);    // multi-GPU: a.mse is this rank's board
     for (int k = tid; k < n; k += MNT) {
         int r, l;
         owner_of(a.sel[k], a.n_global, a.world, r, l);
@@ -107,6 +155,18 @@ __global__ void __launch_bounds__(MNT) merge_kernel(const FmMergeArgs a) {
         a.theta[p] = acc;
     }
     if (blockIdx.x == 0 && tid == 0) a.agg_count[a.sel[ap]] += 1;
+    // tell every rank that this rank has finished pulling rows: owners may overwrite their slabs afterwards
+    if (a.done_ctl != nullptr) {
+        __shared__ unsigned last;
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) last = atomicAdd(a.done_counter, 1u);
+        __syncthreads();
+        if (last == gridDim.x - 1) {
+            if (tid == 0) *a.done_counter = 0u;
+            if (tid < a.world) signal_release_add(ctl_arrive(a.done_ctl[tid], 2));
+        }
+    }
 }
 
 constexpr int VNT = 256;
@@ -148,6 +208,7 @@ __device__ __forceinline__ void verify_decide_and_apply(float* params_c, float* 
 __global__ void __launch_bounds__(VNT) verify_kernel(const FmVerifyArgs a) {
     __shared__ double red[34];
     if (a.agg_pos[0] < 0) return;
+    wait_arrivals(a.arrive, a.expect);    // multi-GPU: every rank is done reading the pre-merge slabs
     const int c = blockIdx.x, tid = threadIdx.x;
     const int g = a.first_client + c;
     float* params_c = a.params + (size_t)c * P_PAD;
@@ -170,8 +231,10 @@ __global__ void __launch_bounds__(VNT) verify_kernel(const FmVerifyArgs a) {
 }  // namespace fm
 
 extern "C" int fm_elect(const float* scores, const int32_t* sel, int32_t n_sel, int32_t voter_pos,
-                        const int32_t* agg_count, int32_t max_agg, int32_t* agg_pos, void* stream) {
-    fm::elect_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(scores, sel, n_sel, voter_pos, agg_count, max_agg, agg_pos);
+                        const int32_t* agg_count, int32_t max_agg, int32_t* agg_pos, const uint32_t* arrive,
+                        uint32_t expect, void* stream) {
+    fm::elect_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(scores, sel, n_sel, voter_pos, agg_count, max_agg, agg_pos,
+                                                         arrive, expect);
     return (int)cudaGetLastError();
 }
 
@@ -187,5 +250,13 @@ extern "C" int fm_verify_update(const FmVerifyArgs* args, void* stream) {
     using namespace fm;
     if (args->n_local <= 0) return 0;
     verify_kernel<<<args->n_local, VNT, 0, (cudaStream_t)stream>>>(*args);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int fm_publish(const float* local, const int32_t* slot_client, int32_t first_client, int32_t n_local,
+                          int32_t n, float* const* peer_ctl, int32_t world, int32_t which, void* stream) {
+    if (world > 32 || which < 0 || which > 1 || n > FM_MAX_SEL) return (int)cudaErrorInvalidValue;
+    fm::publish_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(local, slot_client, first_client, n_local, n, peer_ctl,
+                                                            world, which);
     return (int)cudaGetLastError();
 }

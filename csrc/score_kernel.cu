@@ -17,9 +17,7 @@ __global__ void __launch_bounds__(SNT, 2) score_rows_kernel(const FmScoreArgs a,
     extern __shared__ __align__(128) unsigned char smem_raw[];
     ScoreSmem& S = *reinterpret_cast<ScoreSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const int t_begin = blockIdx.x * tiles_per_cta;
-    const int t_end = min(a.n_tiles, t_begin + tiles_per_cta);
-    if (t_begin >= t_end) return;
+    if (blockIdx.x * tiles_per_cta >= a.n_tiles) return;
     for (int i = tid; i < 2 * TILE * XP; i += SNT) (&S.x[0][0])[i] = 0.f;
     if (tid == 0) { mbar_init(&S.bar[0], 1); mbar_init(&S.bar[1], 1); fence_mbar_init(); }
     fence_proxy_async();
@@ -40,6 +38,9 @@ __global__ void __launch_bounds__(SNT, 2) score_rows_kernel(const FmScoreArgs a,
     };
     uint32_t uses0 = 0, uses1 = 0;
     int cur_model = -1;
+    // units of `tiles_per_cta` consecutive tiles dealt round-robin to CTAs (balances ranks that own 1/world of the slots)
+    for (int t_begin = blockIdx.x * tiles_per_cta; t_begin < a.n_tiles; t_begin += gridDim.x * tiles_per_cta) {
+    const int t_end = min(a.n_tiles, t_begin + tiles_per_cta);
     if (tid == 0) issue(t_begin, 0);
     for (int t = t_begin; t < t_end; ++t) {
         const int buf = (t - t_begin) & 1;
@@ -66,6 +67,7 @@ __global__ void __launch_bounds__(SNT, 2) score_rows_kernel(const FmScoreArgs a,
                 a.out_sse[tl.w + r0 + lane] = lane == 0 ? sse[0] : lane == 1 ? sse[1] : lane == 2 ? sse[2] : sse[3];
         }
         __syncthreads();   // everyone is done with x[buf] before it is refilled two tiles later
+    }
     }
 }
 
@@ -129,9 +131,10 @@ extern "C" int fm_score_rows(const FmScoreArgs* args, void* stream) {
     const size_t smem = sizeof(ScoreSmem);
     cudaError_t err = cudaFuncSetAttribute(score_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return (int)err;
-    int grid = min(args->n_tiles, 2 * sms);
-    const int per = (args->n_tiles + grid - 1) / grid;
-    grid = (args->n_tiles + per - 1) / per;
+    int per = (args->n_tiles + 2 * sms - 1) / (2 * sms);
+    if (per > 32) per = 32;
+    int grid = (args->n_tiles + per - 1) / per;
+    if (grid > 2 * sms) grid = 2 * sms;
     score_rows_kernel<<<grid, SNT, smem, (cudaStream_t)stream>>>(*args, per);
     return (int)cudaGetLastError();
 }

@@ -15,17 +15,13 @@
 // Warp roles: warps 0-3 own TMEM lanes 32w..32w+31 (= tile rows) and run both epilogues; one elected
 // lane of warp 4 issues TMA and MMA; completion travels through mbarriers (tcgen05.commit).  Two CTAs
 // per SM (256 TMEM columns each) overlap one tile's epilogue with the other's copy and MMAs.
-#include <cuda.h>
-#include "common.cuh"
+#include "tc_common.cuh"
 #include "../include/fedmse_b200.h"
 
 namespace fm {
 namespace tc {
 
-constexpr int TROWS = 128;                 // rows per tile = MMA M
 constexpr int NT_TC = 160;                 // 4 epilogue warps + 1 producer/MMA warp
-constexpr int XBLK = TROWS * 128;          // bytes of one K-block of X: 128 rows x 128 B
-constexpr int W1BLK = 32 * 128;            // one K-block of the W1 operand: 32 rows (N) x 128 B
 constexpr int TMEM_COLS = 256;
 constexpr int COL_D1A = 0, COL_D1B = 32, COL_A2 = 64, COL_A2LO = 96, COL_D2 = 128;
 
@@ -48,81 +44,7 @@ struct TcSmem {
     uint32_t tmem_base;
 };
 
-// ---- PTX wrappers ---------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t cvt_tf32(float f) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(f));
-    return r;
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-                 ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-// K-major, 128-byte swizzle shared-memory matrix descriptor (sm_100 format, version 1):
-// rows are 128 B apart inside an 8-row swizzle atom, atoms are SBO = 1024 B apart; LBO is unused.
-__device__ __forceinline__ uint64_t smem_desc_sw128(const void* p) {
-    const uint32_t a = smem_u32(p);
-    uint64_t d = 0;
-    d |= (uint64_t)((a & 0x3FFFFu) >> 4);          // start address  [0,14)
-    d |= (uint64_t)1 << 16;                         // leading byte offset (ignored for swizzled K-major)
-    d |= (uint64_t)(1024 >> 4) << 32;               // stride byte offset [32,46)
-    d |= (uint64_t)1 << 46;                         // descriptor version (Blackwell)
-    d |= (uint64_t)2 << 61;                         // layout type: SWIZZLE_128B
-    return d;
-}
-// instruction descriptor: D=F32, A=B=TF32, both K-major, dense
-__host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
-    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
-}
-__device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}\n"
-                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum), "r"(0u) : "memory");
-}
-__device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, {%5, %5, %5, %5}, p;\n\t}\n"
-                 ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accum), "r"(0u) : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
-                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-                   "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-                   "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                 : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
-                 "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
-                 "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};\n"
-                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
-                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
-                   "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
-                   "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
-                 : "memory");
-    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-}
-
-// byte offset of element (row, k) inside a [rows x 32 floats] K-block with the 128-B swizzle
-__device__ __forceinline__ int sw128(int row, int k) {
-    return row * 128 + ((((k >> 2) ^ (row & 7)) << 4) | ((k & 3) << 2));
-}
-
 // stage one model into the UMMA operand layouts (TF32, round-to-nearest) and plain fp32 tables
-__device__ __forceinline__ uint32_t trunc_tf32(float f) { return __float_as_uint(f) & 0xFFFFE000u; }
-
 template <int PREC>
 __device__ __forceinline__ void stage_model(TcSmem<PREC>& S, const float* __restrict__ row) {
     const int tid = threadIdx.x;
@@ -190,9 +112,10 @@ score_rows_tc_kernel(const FmScoreArgs a, const __grid_constant__ CUtensorMap xm
     using SM = TcSmem<PREC>;
     SM& S = *reinterpret_cast<SM*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int t_begin = blockIdx.x * tiles_per_cta;
-    const int t_end = min(a.n_tiles, t_begin + tiles_per_cta);
-    if (t_begin >= t_end) return;
+    // work units of `tiles_per_cta` consecutive tiles are dealt round-robin to the CTAs: with several ranks
+    // only 1/world of the slots is owned locally, and interleaving keeps the owned work balanced
+    const int unit = tiles_per_cta;
+    if (blockIdx.x * unit >= a.n_tiles) return;
     const bool need_sse = a.out_sse != nullptr;
 
     if (tid == 0) {
@@ -219,7 +142,9 @@ score_rows_tc_kernel(const FmScoreArgs a, const __grid_constant__ CUtensorMap xm
     constexpr uint32_t XBYTES = (PREC == 3 ? 2u : 1u) * 4u * XBLK;
     uint32_t g = 0;               // tiles processed so far by this CTA: selects D1 buffer and barrier parities
 
-    int t = t_begin;
+    for (int u0 = blockIdx.x * unit; u0 < a.n_tiles; u0 += gridDim.x * unit) {
+    const int t_end = min(a.n_tiles, u0 + unit);
+    int t = u0;
     while (t < t_end) {
         // ---- a run = consecutive tiles of one slot (= one model) ----
         const int slot = tiles[t].x;
@@ -388,6 +313,7 @@ score_rows_tc_kernel(const FmScoreArgs a, const __grid_constant__ CUtensorMap xm
         g += (uint32_t)(te - t);
         t = te;
     }
+    }
     // teardown: everyone done with tensor memory, then the allocating warp frees it
     tc_fence_before();
     __syncthreads();
@@ -457,9 +383,11 @@ extern "C" int fm_score_rows_tc(const FmScoreArgs* args, int64_t x_rows, int32_t
     cudaError_t err = x3 ? cudaFuncSetAttribute(score_rows_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
                          : cudaFuncSetAttribute(score_rows_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return (int)err;
-    int grid = min(args->n_tiles, (x3 ? 1 : 2) * sms);
-    const int per = (args->n_tiles + grid - 1) / grid;
-    grid = (args->n_tiles + per - 1) / per;
+    const int max_cta = (x3 ? 1 : 2) * sms;
+    int per = (args->n_tiles + max_cta - 1) / max_cta;        // contiguous share ...
+    if (per > 32) per = 32;                                     // ... capped: units of <= 32 tiles, dealt round-robin
+    int grid = (args->n_tiles + per - 1) / per;
+    if (grid > max_cta) grid = max_cta;
     if (x3) score_rows_tc_kernel<3><<<grid, NT_TC, smem, (cudaStream_t)stream>>>(*args, map, lomap, (long long)x_rows, per);
     else score_rows_tc_kernel<1><<<grid, NT_TC, smem, (cudaStream_t)stream>>>(*args, map, lomap, (long long)x_rows, per);
     return (int)cudaGetLastError();

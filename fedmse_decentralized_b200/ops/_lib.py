@@ -39,6 +39,15 @@ class FmScoreArgs(C.Structure):
                 ("X", c_vp), ("tiles", c_vp), ("n_tiles", C.c_int32), ("out_sse", c_vp), ("out_lat", c_vp)]
 
 
+class FmMultiScoreArgs(C.Structure):
+    _fields_ = [("slab", c_vp), ("slot_client", c_vp), ("n_slots", C.c_int32), ("first_client", C.c_int32),
+                ("n_local", C.c_int32), ("X", c_vp), ("X_lo", c_vp), ("x_rows", C.c_int64), ("precision", C.c_int32),
+                ("images", c_vp), ("owned_slots", c_vp), ("n_owned", c_vp), ("out_sse", c_vp)]
+
+
+TC_IMAGE_BYTES = 67584
+
+
 class FmVoteArgs(C.Structure):
     _fields_ = [("slab", c_vp), ("sel", c_vp), ("n_sel", C.c_int32), ("first_client", C.c_int32),
                 ("n_local", C.c_int32), ("V", c_vp), ("rows", C.c_int32), ("chunk", C.c_int32),
@@ -53,6 +62,8 @@ class FmVoteStaticArgs(C.Structure):
                 ("scores", c_vp)]
 
 
+MAX_SEL = 4096
+CTL_FLOATS = 2 * MAX_SEL + 16
 STATIC_VOTE_MAX_ROWS = 1024
 STATIC_VOTE_MAX_SEL = 64
 
@@ -60,14 +71,16 @@ STATIC_VOTE_MAX_SEL = 64
 class FmMergeArgs(C.Structure):
     _fields_ = [("peer_slabs", c_vp), ("world", C.c_int32), ("rank", C.c_int32), ("n_global", C.c_int32),
                 ("sel", c_vp), ("n_sel", C.c_int32), ("mse", c_vp), ("mode", C.c_int32), ("compat", C.c_int32),
-                ("agg_pos", c_vp), ("agg_count", c_vp), ("theta", c_vp), ("weights_out", c_vp)]
+                ("agg_pos", c_vp), ("agg_count", c_vp), ("theta", c_vp), ("weights_out", c_vp),
+                ("arrive", c_vp), ("expect", C.c_uint32), ("done_ctl", c_vp), ("done_counter", c_vp)]
 
 
 class FmVerifyArgs(C.Structure):
     _fields_ = [("params", c_vp), ("anchor", c_vp), ("hist", c_vp), ("hist_perf", c_vp), ("hist_valid", c_vp),
                 ("rejected", c_vp), ("n_local", C.c_int32), ("first_client", C.c_int32), ("theta", c_vp),
                 ("agg_pos", c_vp), ("sse", c_vp), ("sse_off", c_vp), ("shared_segment", C.c_int32),
-                ("thr_change", C.c_float), ("thr_perf", C.c_float), ("out_change", c_vp), ("out_dperf", c_vp)]
+                ("thr_change", C.c_float), ("thr_perf", C.c_float), ("out_change", c_vp), ("out_dperf", c_vp),
+                ("arrive", c_vp), ("expect", C.c_uint32)]
 
 
 class FmAucArgs(C.Structure):
@@ -134,12 +147,14 @@ def load() -> C.CDLL:
         ("fm_score_rows", [C.POINTER(FmScoreArgs), c_vp]),
         ("fm_score_rows_tc", [C.POINTER(FmScoreArgs), C.c_int64, C.c_int32, c_vp, c_vp]),
         ("fm_split_residual", [c_vp, c_vp, C.c_int64, c_vp]),
+        ("fm_score_multi_tc", [C.POINTER(FmMultiScoreArgs), c_vp]),
         ("fm_vote_normalise", [c_vp, C.c_int32, c_vp, c_vp]),
         ("fm_chunk_mean", [c_vp, C.c_int32, C.c_int32, C.c_int32, c_vp, c_vp, C.c_int32, C.c_int32,
                            C.c_int32, c_vp, c_vp]),
         ("fm_vote_scores", [C.POINTER(FmVoteArgs), c_vp]),
         ("fm_vote_scores_static", [C.POINTER(FmVoteStaticArgs), c_vp]),
-        ("fm_elect", [c_vp, c_vp, C.c_int32, C.c_int32, c_vp, C.c_int32, c_vp, c_vp]),
+        ("fm_elect", [c_vp, c_vp, C.c_int32, C.c_int32, c_vp, C.c_int32, c_vp, c_vp, C.c_uint32, c_vp]),
+        ("fm_publish", [c_vp, c_vp, C.c_int32, C.c_int32, C.c_int32, c_vp, C.c_int32, C.c_int32, c_vp]),
         ("fm_merge", [C.POINTER(FmMergeArgs), c_vp]),
         ("fm_verify_update", [C.POINTER(FmVerifyArgs), c_vp]),
         ("fm_auc", [C.POINTER(FmAucArgs), c_vp]),

@@ -125,6 +125,19 @@ class CudaBackend:
                                              sh.valid.off_host[f + c]) for c in range(C_)], self.tile).to(dev)
         self.verify_off_own = torch.tensor([sh.valid.off_host[f + c] for c in range(C_ + 1)], **i32)
         self.peer_table = self.param_slab.table
+        # multi-GPU: peer-mapped control block (score boards + arrival counters) -> no NCCL on the merge path
+        self.exchanges_scores = comm.is_dist
+        self.seq = [0, 0, 0]
+        if comm.is_dist:
+            from ..parallel.symmetric import SymmetricSlab
+            if n_sel_max > _lib.MAX_SEL:
+                raise ValueError(f"{n_sel_max} selected clients exceed FM_MAX_SEL={_lib.MAX_SEL}")
+            with torch.cuda.device(dev):
+                self.ctl_slab = SymmetricSlab(1, _lib.CTL_FLOATS, comm)
+            self._slabs.append(self.ctl_slab)
+            self.ctl = self.ctl_slab.tensor.view(-1)
+            self.ctl_arrive_ptr = self.ctl_slab.ptr + 4 * 2 * _lib.MAX_SEL
+            self.done_counter = torch.zeros(1, dtype=torch.int32, device=dev)
 
     def begin_round(self, ctl: RoundControl) -> None:
         """Upload the round's control block: selection (global + local ids) and jitter."""
@@ -215,12 +228,30 @@ class CudaBackend:
                             _ptr(self.vote_norm), _ptr(self.vote_sse), _ptr(self.scores))
         _lib.check(self.lib.fm_vote_scores(C.byref(a), self._stream()), "vote_scores")
         self.launches += 3
+        if self.exchanges_scores:
+            return self._publish(self.scores, n, 0)
         return self.scores[:n]
 
+    def _publish(self, local: torch.Tensor, n: int, which: int) -> torch.Tensor:
+        """Write this rank's entries into every rank's board `which` and signal arrival; returns the view of
+        the local board that is complete once `arrive[which] >= world * seq[which]` (consumers wait in-kernel)."""
+        sh, st = self.sh, self.st
+        _lib.check(self.lib.fm_publish(_ptr(local), _ptr(self.ctl_sel), sh.first_client, st.n_clients, n,
+                                       _ptr(self.ctl_slab.table), self.comm.world, which, self._stream()), "publish")
+        self.launches += 1
+        self.seq[which] += 1
+        return self.ctl[which * _lib.MAX_SEL: which * _lib.MAX_SEL + n]
+
+    def _arrive(self, which: int):
+        if not self.exchanges_scores:
+            return 0, 0
+        return self.ctl_arrive_ptr + 4 * which, self.comm.world * self.seq[which]
+
     def elect(self, st, scores: torch.Tensor, ctl: RoundControl, spec: MergeSpec) -> torch.Tensor:
+        arrive, expect = self._arrive(0)
         _lib.check(self.lib.fm_elect(_ptr(scores), _ptr(self.ctl_sel), len(ctl.sel), ctl.voter_pos,
                                      _ptr(st.agg_count), spec.max_aggregations, _ptr(self.agg_pos),
-                                     self._stream()), "elect")
+                                     arrive, expect, self._stream()), "elect")
         self.launches += 1
         return self.agg_pos
 
@@ -229,11 +260,26 @@ class CudaBackend:
         n, R = len(ctl.sel), self.dev_rows
         if self.merge_sse is None or self.merge_sse.numel() < n * R:
             self.merge_sse = torch.zeros(n * R, dtype=torch.float32, device=self.device)
-        tiles = self._tiles(("dev", n, R), lambda: make_tiles([(p, 0, R, p * R) for p in range(n)], self.tile))
-        self._score(st.params, st.n_clients, sh.first_client, self.ctl_sel, sh.dev, tiles, self.merge_sse, None)
+        if self.tc:
+            # tensor-core path: dev tile resident in smem, all locally owned models looped over it
+            if getattr(self, "_images", None) is None:
+                self._images = torch.empty(max(1, st.n_clients) * _lib.TC_IMAGE_BYTES, dtype=torch.uint8,
+                                           device=self.device)
+                self._owned = torch.zeros(max(1, sh.n_global) + 1, dtype=torch.int32, device=self.device)
+            lo = self._residual(sh.dev) if self.tc == 3 else None
+            a = _lib.FmMultiScoreArgs(_ptr(st.params), _ptr(self.ctl_sel), n, sh.first_client, st.n_clients,
+                                      _ptr(sh.dev), _ptr(lo), R, self.tc, _ptr(self._images),
+                                      _ptr(self._owned[1:]), _ptr(self._owned[:1]), _ptr(self.merge_sse))
+            _lib.check(self.lib.fm_score_multi_tc(C.byref(a), self._stream()), "score_multi_tc")
+            self.launches += 2
+        else:
+            tiles = self._tiles(("dev", n, R), lambda: make_tiles([(p, 0, R, p * R) for p in range(n)], self.tile))
+            self._score(st.params, st.n_clients, sh.first_client, self.ctl_sel, sh.dev, tiles, self.merge_sse, None)
         _lib.check(self.lib.fm_chunk_mean(_ptr(self.merge_sse), n, R, 0, 0, _ptr(self.ctl_sel), sh.first_client,
                                           st.n_clients, -1, _ptr(self.mse), self._stream()), "chunk_mean")
         self.launches += 1
+        if self.exchanges_scores:
+            return self._publish(self.mse, n, 1)
         return self.mse[:n]
 
     def merge(self, st, sh, ctl: RoundControl, spec: MergeSpec, mse, agg_pos, rows=None) -> torch.Tensor:
@@ -241,12 +287,16 @@ class CudaBackend:
         a = _lib.FmMergeArgs(_ptr(self.peer_table), self.comm.world, self.comm.rank, sh.n_global,
                              _ptr(self.ctl_sel), n, _ptr(mse), 1 if spec.update_type == "mse_avg" else 0,
                              1 if spec.compat_alias else 0, _ptr(agg_pos), _ptr(st.agg_count), _ptr(self.theta),
-                             _ptr(self.weights))
+                             _ptr(self.weights), 0, 0, 0, 0)
+        if self.exchanges_scores:
+            if mse is not None:
+                a.arrive, a.expect = self._arrive(1)
+            # after its reduction every rank bumps arrive[2] everywhere; verify waits for all of them before
+            # any owner overwrites rows that peers may still be pulling
+            a.done_ctl, a.done_counter = _ptr(self.ctl_slab.table), _ptr(self.done_counter)
+            self.seq[2] += 1
         _lib.check(self.lib.fm_merge(C.byref(a), self._stream()), "merge")
         self.launches += 1
-        if self.comm.is_dist:
-            # every rank must have finished pulling peers' rows before anyone overwrites its slab
-            self.comm.sum_(self._barrier_token())
         return self.theta
 
     def _barrier_token(self) -> torch.Tensor:
@@ -273,7 +323,7 @@ class CudaBackend:
         a = _lib.FmVerifyArgs(_ptr(st.params), _ptr(st.anchor), _ptr(st.hist), _ptr(st.hist_perf),
                               _ptr(st.hist_valid), _ptr(st.rejected), st.n_clients, sh.first_client, _ptr(theta),
                               _ptr(agg_pos), _ptr(self.verify_sse), _ptr(off), shared,
-                              spec.verification_threshold, spec.performance_threshold, 0, 0)
+                              spec.verification_threshold, spec.performance_threshold, 0, 0, *self._arrive(2))
         _lib.check(self.lib.fm_verify_update(C.byref(a), self._stream()), "verify_update")
         self.launches += 1
 

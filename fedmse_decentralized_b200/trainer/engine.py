@@ -170,12 +170,16 @@ class FederationEngine:
         agg_pos = None
         if ctl.voter_pos >= 0:
             with tm.phase("vote"):
-                scores = cm.sum_(be.vote_scores(st, sh, ctl, self.spec))
+                scores = be.vote_scores(st, sh, ctl, self.spec)
+                if not getattr(be, "exchanges_scores", False):     # CUDA multi-GPU exchanges in-kernel (P2P boards)
+                    scores = cm.sum_(scores)
                 agg_pos = be.elect(st, scores, ctl, self.spec)
             with tm.phase("merge"):
                 mse = None
                 if self.update_type == "mse_avg":
-                    mse = cm.sum_(be.merge_scores(st, sh, ctl))
+                    mse = be.merge_scores(st, sh, ctl)
+                    if not getattr(be, "exchanges_scores", False):
+                        mse = cm.sum_(mse)
                 rows = None
                 if cm.is_dist and not getattr(be, "reads_peers", False):
                     rows = cm.gather_rows(st.params, ctl.sel, self.first)

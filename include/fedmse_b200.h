@@ -95,6 +95,22 @@ int fm_score_rows(const FmScoreArgs* args, void* stream);
 int fm_score_rows_tc(const FmScoreArgs* args, int64_t x_rows, int32_t precision, const float* x_lo, void* stream);
 int fm_split_residual(const float* x, float* x_lo, int64_t rows, void* stream);
 
+/* ---- many models on one shared matrix (MSE-weight scoring on the pooled dev set) -----------
+ * Inverts the loop of fm_score_rows_tc: each CTA keeps one 128-row tile of X resident in shared memory
+ * and runs every locally owned slot's model over it (operand images pre-staged by a prep kernel and
+ * pulled with bulk async copies), so X is read once per tile instead of once per (tile, model).
+ * out_sse is laid out [n_slots][x_rows]; rows of slots owned by other ranks are left untouched.
+ * Scratch (caller): images >= owned * FM_TC_IMAGE_BYTES bytes, owned_slots[n_slots] ints, n_owned[1] int.
+ * (reference: the full-batch dev-set forward of fed_mse_avg, client_trainer.py:118-124). */
+#define FM_TC_IMAGE_BYTES 67584
+typedef struct FmMultiScoreArgs {
+    const float* slab; const int32_t* slot_client; int32_t n_slots; int32_t first_client; int32_t n_local;
+    const float* X; const float* X_lo; int64_t x_rows; int32_t precision;
+    unsigned char* images; int32_t* owned_slots; int32_t* n_owned;
+    float* out_sse;
+} FmMultiScoreArgs;
+int fm_score_multi_tc(const FmMultiScoreArgs* args, void* stream);
+
 /* Column-normalise a vote matrix: out = (V - mean) / (unbiased std + 1e-8)
  * (reference: client_trainer.py:221-223).  V and out are [rows][FM_XP]; out is caller scratch. */
 int fm_vote_normalise(const float* V, int32_t rows, float* out, void* stream);
@@ -151,7 +167,20 @@ const char* fm_vote_scores_static_error(void);
  * agg_pos[0] = argmin over positions p != voter_pos with agg_count[sel[p]] < max_agg of
  * scores[p] (NaN = +inf, ties: first); -1 if none.  agg_pos[1] = the elected global id or -1. */
 int fm_elect(const float* scores, const int32_t* sel, int32_t n_sel, int32_t voter_pos,
-             const int32_t* agg_count, int32_t max_agg, int32_t* agg_pos, void* stream);
+             const int32_t* agg_count, int32_t max_agg, int32_t* agg_pos, const uint32_t* arrive,
+             uint32_t expect, void* stream);
+
+/* ---- cross-GPU scalar exchange without NCCL (multi-GPU election scores / merge MSEs) --------
+ * Every rank owns a peer-mapped control block of FM_CTL_FLOATS floats: two boards of FM_MAX_SEL
+ * floats (0 = vote scores, 1 = merge MSEs) followed by four uint32 arrival counters (0, 1 = the
+ * boards, 2 = "done pulling rows").  fm_publish writes the entries this rank owns into the board
+ * `which` of every rank (P2P stores), fences at system scope and bumps arrive[which] on every rank
+ * with a release reduction.  A consumer (fm_elect, fm_merge, fm_verify_update) given
+ * arrive = &own_ctl.arrive[which] and expect = world * (number of exchanges so far) spins with
+ * acquire loads until every rank has arrived and then reads its own board.  Counters only grow. */
+#define FM_CTL_FLOATS (2 * FM_MAX_SEL + 16)
+int fm_publish(const float* local, const int32_t* slot_client, int32_t first_client, int32_t n_local,
+               int32_t n, float* const* peer_ctl, int32_t world, int32_t which, void* stream);
 
 /* ---- T2 merge: weights + weighted parameter reduction with in-kernel peer loads ----------
  * theta = sum_k w_k * model(sel[k]), where model(g) is read from the owner rank's slab through
@@ -174,6 +203,10 @@ typedef struct FmMergeArgs {
     int32_t* agg_count;             /* [n_global] */
     float* theta;                   /* [P_PAD] out */
     float* weights_out;             /* [n_sel] out (diagnostics), or NULL */
+    const uint32_t* arrive;         /* multi-GPU: wait for arrive[0] >= expect before reading mse; NULL = no wait */
+    uint32_t expect;
+    float* const* done_ctl;         /* multi-GPU: peers' control blocks; after the reduction every rank bumps */
+    uint32_t* done_counter;         /*   arrive[2] on all of them (done_counter: zeroed device scratch); NULL = off */
 } FmMergeArgs;
 int fm_merge(const FmMergeArgs* args, void* stream);
 
@@ -192,6 +225,7 @@ typedef struct FmVerifyArgs {
     const float* sse; const int32_t* sse_off; int32_t shared_segment; /* 1: every client uses segment 0 */
     float thr_change; float thr_perf;
     float* out_change; float* out_dperf; /* [n_local] diagnostics or NULL */
+    const uint32_t* arrive; uint32_t expect; /* multi-GPU: wait until all ranks are done pulling rows; NULL = no wait */
 } FmVerifyArgs;
 int fm_verify_update(const FmVerifyArgs* args, void* stream);
 
