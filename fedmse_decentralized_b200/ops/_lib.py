@@ -159,6 +159,10 @@ def load() -> C.CDLL:
         ("fm_verify_update", [C.POINTER(FmVerifyArgs), c_vp]),
         ("fm_auc", [C.POINTER(FmAucArgs), c_vp]),
         ("fm_gossip", [C.POINTER(FmGossipArgs), c_vp]),
+        ("fm_weighted_rows", [c_vp, c_vp, C.c_int32, c_vp, C.c_int64, c_vp, C.c_uint32, c_vp, C.c_int32, C.c_int32,
+                              c_vp, c_vp]),
+        ("fm_slice_reduce", [c_vp, C.c_int32, C.c_int32, c_vp, C.c_int64, c_vp, C.c_uint32, c_vp, C.c_int32, c_vp, c_vp]),
+        ("fm_slice_gather", [c_vp, C.c_int32, c_vp, C.c_int64, c_vp, C.c_uint32, c_vp]),
         ("fm_slab_alloc", [C.c_uint64, C.POINTER(c_vp)]),
         ("fm_slab_free", [c_vp]),
         ("fm_ipc_get_handle", [c_vp, C.c_char_p]),

@@ -262,6 +262,24 @@ typedef struct FmGossipArgs {
 } FmGossipArgs;
 int fm_gossip(const FmGossipArgs* args, void* stream);
 
+/* ---- wide-model weighted reduction across GPUs by in-kernel peer loads (no NCCL) ------------
+ * (BASELINE.json config 5; the reference's merge for a model of any size: client_trainer.py:107-130.)
+ * fm_weighted_rows:  out = sum_k w[k] * rows[k], rows = device table of row pointers (local or peer-mapped).
+ * fm_slice_reduce:   reduced[slice(rank)] = sum_q partials[q][slice(rank)]      (reduce-scatter by pulling)
+ * fm_slice_gather:   out[slice(q)] = reduced[q][slice(q)] for all q             (all-gather by pulling)
+ * Optional cross-rank ordering: wait until *arrive >= expect before reading (NULL = no wait); when
+ * peer_ctl != NULL the last block bumps arrival counter `which` (index into the uint32 counters that
+ * follow the two boards of a control block, see fm_publish) on every rank after its writes are fenced.
+ * n_floats must be a multiple of 4 and all buffers 16-B aligned. */
+int fm_weighted_rows(const float* const* rows, const float* w, int32_t n, float* out, int64_t n_floats,
+                     const uint32_t* arrive, uint32_t expect, float* const* peer_ctl, int32_t world,
+                     int32_t which, uint32_t* grid_counter, void* stream);
+int fm_slice_reduce(const float* const* partials, int32_t world, int32_t rank, float* reduced, int64_t n_floats,
+                    const uint32_t* arrive, uint32_t expect, float* const* peer_ctl, int32_t which,
+                    uint32_t* grid_counter, void* stream);
+int fm_slice_gather(const float* const* reduced, int32_t world, float* out, int64_t n_floats,
+                    const uint32_t* arrive, uint32_t expect, void* stream);
+
 /* ---- runtime: peer-mapped slabs (cudaMalloc + CUDA IPC), used for the parameter slab ------ */
 int fm_slab_alloc(uint64_t bytes, void** ptr);                 /* cudaMalloc, zeroed */
 int fm_slab_free(void* ptr);
