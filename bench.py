@@ -156,7 +156,7 @@ def run_ours(args):
         for r in range(r0, r0 + n_rounds):
             if with_h2d:    # this round's inputs: fresh local traffic from pinned host memory
                 eng.update_local_data(pin_train, pin_valid)
-            res = eng.run_round(r)              # includes the device->host read of the round's results
+            res = eng.run_round(r, prefetch_next=True)   # includes the device->host read of the round's results
             samples += res.samples
         e1.record()
         sync_all()

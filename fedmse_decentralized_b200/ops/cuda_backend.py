@@ -386,5 +386,45 @@ class CudaBackend:
         if self.comm.is_dist:
             self.comm.sum_(self._barrier_token())          # peers done reading before the next snapshot
 
+    # ------------------------------------------------------------------ one read-back per round
+    def readback(self, st, agg_pos: Optional[torch.Tensor], with_auc: bool):
+        """Gather the round's results with one D2H copy and one stream sync.  Multi-GPU: the per-rank blocks
+        are all-gathered on the device first (one small NCCL call), so the lists returned cover ALL clients:
+        (aggregator position, epochs_run[N], rejected[N], auc[N] or None)."""
+        C_, W = st.n_clients, self.comm.world
+        if getattr(self, "_rb_dev", None) is None:
+            cmax = C_
+            if self.comm.is_dist:
+                cmax = int(max(self.comm.all_gather_object(C_)))
+            self._rb_cmax = cmax
+            self._rb_counts = self.comm.all_gather_object(C_) if self.comm.is_dist else [C_]
+            self._rb_dev = torch.zeros(2 + 4 * cmax, dtype=torch.int32, device=self.device)
+            self._rb_all = torch.zeros(W * (2 + 4 * cmax), dtype=torch.int32, device=self.device)
+            self._rb_pin = torch.zeros_like(self._rb_all, device="cpu").pin_memory()
+        cm, rb = self._rb_cmax, self._rb_dev
+        rb[0:2].copy_(agg_pos if agg_pos is not None else self.agg_pos.new_full((2,), -1))
+        rb[2:2 + C_].copy_(st.epochs_run)
+        rb[2 + cm:2 + cm + C_].copy_(st.rejected)
+        if with_auc:
+            rb[2 + 2 * cm:2 + 2 * cm + 2 * C_].view(torch.float64).copy_(self.auc[:C_])
+        if self.comm.is_dist:
+            import torch.distributed as dist
+            dist.all_gather_into_tensor(self._rb_all, rb, group=self.comm.group)
+            src = self._rb_all
+        else:
+            src = rb
+        self._rb_pin[:src.numel()].copy_(src, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        host = self._rb_pin.numpy()
+        stride = 2 + 4 * cm
+        epochs, rejected, auc = [], [], ([] if with_auc else None)
+        for r, cnt in enumerate(self._rb_counts):
+            blk = host[r * stride:(r + 1) * stride]
+            epochs += blk[2:2 + cnt].tolist()
+            rejected += blk[2 + cm:2 + cm + cnt].tolist()
+            if with_auc:
+                auc += blk[2 + 2 * cm:2 + 2 * cm + 2 * cnt].view(np.float64).tolist()
+        return int(host[0]), epochs, rejected, auc
+
     def synchronize(self) -> None:
         torch.cuda.synchronize(self.device)

@@ -129,18 +129,43 @@ class FederationEngine:
         self.last_metrics: Optional[List[float]] = None
         self.history: List[RoundResult] = []
         self._neigh_cache = None
+        self._rand_fifo: List[float] = []
+        self._prefetched = None
         if hasattr(self.backend, "bind"):
             self.backend.bind(self.state, self.sh, self.comm, self.hp, self.spec, model_type)
 
     # ------------------------------------------------------------------ control (host RNG)
+    def _next_rand(self) -> float:
+        """Next ``torch.rand(1).item()`` of the reference's stream (possibly drawn ahead of time)."""
+        if self._rand_fifo:
+            return self._rand_fifo.pop(0)
+        return torch.rand(1).item()
+
+    def prefetch_control(self, round_idx: int) -> None:
+        """Do the host work of the NEXT round's control block while the GPU is busy with this one: the
+        client selection and the uniform draws the common case needs (first voter succeeds).  Values go
+        through a FIFO, so the RNG streams are consumed in exactly the reference's order either way."""
+        if self._prefetched is not None:
+            return
+        n_sel = max(1, int(self.cfg.num_participants * self.N))
+        sel = random.sample(range(self.N), n_sel)
+        need = (n_sel - 1) + (n_sel if self.update_type == "mse_avg" else 0)
+        while len(self._rand_fifo) < need:
+            self._rand_fifo.append(torch.rand(1).item())
+        self._prefetched = (round_idx, sel)
+
     def make_control(self, round_idx: int) -> RoundControl:
         cfg = self.cfg
         n_sel = max(1, int(cfg.num_participants * self.N))
-        sel = random.sample(range(self.N), n_sel)
+        if self._prefetched is not None:
+            _, sel = self._prefetched
+            self._prefetched = None
+        else:
+            sel = random.sample(range(self.N), n_sel)
         quota = cfg.max_aggregation_threshold
         voter_pos, jitter = -1, [1.0] * n_sel
         for k in range(n_sel):
-            draws = [1.0 + (torch.rand(1).item() - 0.5) * 0.0002 for _ in range(n_sel - 1)]
+            draws = [1.0 + (self._next_rand() - 0.5) * 0.0002 for _ in range(n_sel - 1)]
             if any(self.agg_count_host[g] < quota for p, g in enumerate(sel) if p != k):
                 voter_pos = k
                 it = iter(draws)
@@ -148,7 +173,7 @@ class FederationEngine:
                 break
         if voter_pos >= 0 and self.update_type == "mse_avg":
             for _ in range(n_sel):          # quirk Q7: aggregate_models draws once per client
-                torch.rand(1)
+                self._next_rand()
         verify_client = self.N - 1 if (cfg.reference_compat and cfg.verification_method == "val") else -1
         return RoundControl(round=round_idx, sel=sel, voter_pos=voter_pos, jitter=jitter,
                             vote_client=sel[0], verify_client=verify_client)
@@ -158,7 +183,11 @@ class FederationEngine:
 
     # ------------------------------------------------------------------ one round
     def run_round(self, round_idx: int, ctl: Optional[RoundControl] = None,
-                  evaluate: bool = True, want_latents: Optional[bool] = None) -> RoundResult:
+                  evaluate: bool = True, want_latents: Optional[bool] = None,
+                  prefetch_next: bool = False) -> RoundResult:
+        """One federated round.  ``prefetch_next`` prepares the next round's selection and random draws on
+        the host while the device executes this round (use it when more rounds follow)."""
+        self._prefetch_next = prefetch_next and ctl is None and self.cfg.aggregation != "gossip"
         if self.cfg.aggregation == "gossip":
             return self._run_round_gossip(round_idx, ctl, evaluate, want_latents)
         be, st, sh, cm, tm = self.backend, self.state, self.sh, self.comm, self.timer
@@ -194,23 +223,28 @@ class FederationEngine:
         if want_latents is None:
             want_latents = cfg.write_latents and self.model_type == "hybrid"
         metrics: List[float] = []
-        lat = None
+        lat, auc64, auc_dev = None, None, None
         if evaluate:
             with tm.phase("evaluate"):
                 auc_dev, auc64, lat = be.evaluate(st, sh, self.model_type, want_latents, cfg.metric)
-        # ---- single readback of the round's results --------------------------------
-        a = int(agg_pos[0]) if agg_pos is not None else -1
+        if getattr(self, "_prefetch_next", False):
+            self.prefetch_control(ctl.round + 1)       # overlaps with the kernels enqueued above
+        # ---- single readback of the round's results (global lists) ------------------------
+        if hasattr(be, "readback") and (not evaluate or auc64 is None):
+            a, epochs_all, rejected, auc_all = be.readback(st, agg_pos, evaluate)
+            if evaluate:
+                metrics = auc_all
+        else:
+            a = int(agg_pos[0]) if agg_pos is not None else -1
+            if evaluate:
+                if auc64 is None:
+                    auc64 = [float(x) for x in auc_dev.tolist()]
+                metrics = self._gather_list(auc64)
+            rejected = self._gather_list(st.rejected.tolist())
+            epochs_all = self._gather_list(st.epochs_run.tolist())
         aggregator = ctl.sel[a] if a >= 0 else -1
         if aggregator >= 0:
             self.agg_count_host[aggregator] += 1
-        epochs_local = st.epochs_run.tolist()
-        rejected_local = st.rejected.tolist()
-        if evaluate:
-            if auc64 is None:
-                auc64 = [float(x) for x in auc_dev.tolist()]
-            metrics = self._gather_list(auc64)
-        rejected = self._gather_list(rejected_local)
-        epochs_all = self._gather_list(epochs_local)
         verification = []
         if aggregator >= 0:
             for g in range(self.N):
@@ -292,7 +326,7 @@ class FederationEngine:
         out = []
         for r in range(cfg.num_rounds):
             log.info("Starting round %d/%d", r + 1, cfg.num_rounds)
-            res = self.run_round(r)
+            res = self.run_round(r, prefetch_next=r + 1 < cfg.num_rounds)
             out.append(res)
             if res.aggregator >= 0:
                 log.info("Client %d selected as aggregator", res.aggregator + 1)
@@ -365,7 +399,8 @@ class FederationEngine:
         return {"state": self.state.state_dict(), "agg_count_host": list(self.agg_count_host),
                 "py_random": random.getstate(), "np_random": np.random.get_state(),
                 "torch_random": torch.get_rng_state(), "rounds_done": len(self.history),
-                "model_type": self.model_type, "update_type": self.update_type, "run": self.run}
+                "model_type": self.model_type, "update_type": self.update_type, "run": self.run,
+                "rand_fifo": list(self._rand_fifo), "prefetched": self._prefetched}
 
     def restore(self, snap: Dict) -> None:
         self.state.load_state_dict(snap["state"])
@@ -373,3 +408,5 @@ class FederationEngine:
         random.setstate(snap["py_random"])
         np.random.set_state(snap["np_random"])
         torch.set_rng_state(snap["torch_random"])
+        self._rand_fifo = list(snap.get("rand_fifo", []))
+        self._prefetched = snap.get("prefetched")

@@ -149,3 +149,15 @@ def test_gossip_round_topologies(tiny_clients, tmp_path):
         assert res.aggregator == -1 and len(res.client_metrics) == 6
         assert all(not torch.equal(eng.state.params[c], before[c]) for c in range(6))
         assert int(eng.state.hist_valid.sum()) == 6
+
+
+def test_control_prefetch_keeps_rng_order(tiny_clients, tmp_path):
+    """Preparing the next round's selection / jitter draws ahead of time must not change any decision."""
+    cfg = make_cfg(tmp_path, epoch=1, num_participants=0.7)
+    a = make_engine(cfg, make_shards(tiny_clients), "hybrid", "mse_avg")
+    ra = [a.run_round(r) for r in range(3)]
+    b = make_engine(cfg, make_shards(tiny_clients), "hybrid", "mse_avg")
+    rb = [b.run_round(r, prefetch_next=True) for r in range(3)]
+    for x, y in zip(ra, rb):
+        assert x.selected == y.selected and x.aggregator == y.aggregator and x.client_metrics == y.client_metrics
+    assert torch.equal(a.state.params, b.state.params)

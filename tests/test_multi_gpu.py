@@ -65,3 +65,20 @@ def test_n_gpus_match_one_gpu(tmp_path, agg, upd):
     assert one["agg"] == many["agg"] and one["ver"] == many["ver"] and one["epochs"] == many["epochs"]
     for a, b in zip(one["metrics"], many["metrics"]):
         assert len(a) == 9 and max(abs(x - y) for x, y in zip(a, b)) < 1e-6
+
+
+def test_p2p_weighted_allreduce_matches_nccl(tmp_path):
+    """Wide-model reduction by in-kernel peer loads (reduce-scatter + all-gather by pulling) vs NCCL all_reduce."""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = 2 if n < 4 else (4 if n < 8 else 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
+           "127.0.0.1", "--master-port", "29641", os.path.join(ROOT, "scripts/bench_bandwidth_sweep.py"),
+           "--sizes-mb", "0.5", "8", "--clients-per-gpu", "3", "--iters", "3"]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, MASTER_ADDR="127.0.0.1"))
+    assert p.returncode == 0, p.stderr[-3000:]
+    lines = [json.loads(l) for l in p.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 2
+    for l in lines:
+        assert l["max_rel_err"] < 1e-5 and l["max_rel_err_pull_all"] < 1e-5 and l["gpus"] == world
