@@ -197,7 +197,10 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_con
             const uint32_t b = (uint32_t)(g & 1), ph = (uint32_t)(g & 1), ph1 = (uint32_t)((g >> 1) & 1);
             const int row0 = ((int)blockIdx.x + tile_i * (int)gridDim.x) * TROWS;
             const float* T = S.tbl[b];
-            mbar_wait(&S.bar_w1, ph);                               // tables of this pair have landed
+            // The tables of this pair arrived with the w1 image: the producer observed bar_w1 before it issued
+            // MMA 1, whose completion (bar_d1) is observed here, so they are visible.  The epilogue must NOT wait
+            // on bar_w1 itself: the producer may already have armed and completed the NEXT w1 phase, and a waiter
+            // two phases behind an mbarrier never wakes up.
             mbar_wait(&S.bar_d1[b], ph1);
             tc_fence_after();
             uint32_t v[32];

@@ -394,6 +394,51 @@ class FederationEngine:
         if touched and hasattr(self.backend, "data_updated"):
             self.backend.data_updated(*touched)
 
+    def stage_next_data(self, train_x: Optional[torch.Tensor] = None, valid_x: Optional[torch.Tensor] = None) -> None:
+        """Start uploading the NEXT round's local rows (e.g. from pinned host memory) into shadow shards on
+        a side stream, so the copy overlaps with the round that is about to run on the current shards.
+        Call ``commit_staged_data()`` before the round that should see them."""
+        sh, dev = self.sh, self.state.device
+        if dev.type != "cuda":
+            self._staged = (train_x, valid_x, None)
+            return
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            self._shadow_train = sh.train.x.clone()
+            self._shadow_valid = sh.valid.x.clone()
+            torch.cuda.current_stream(dev).synchronize()
+        v0, v1 = sh.valid.off_host[self.first], sh.valid.off_host[self.first + self.n_local]
+        with torch.cuda.stream(self._copy_stream):
+            if train_x is not None:
+                self._shadow_train.copy_(train_x, non_blocking=True)
+            if valid_x is not None:
+                self._shadow_valid[v0:v1].copy_(valid_x, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._copy_stream)
+        self._staged = (train_x is not None, valid_x is not None, ev)
+
+    def commit_staged_data(self) -> None:
+        """Make the staged rows current (pointer swap after the side-stream copy has finished)."""
+        staged = getattr(self, "_staged", None)
+        if staged is None:
+            return
+        self._staged = None
+        sh, dev = self.sh, self.state.device
+        if dev.type != "cuda":
+            self.update_local_data(staged[0], staged[1])
+            return
+        has_t, has_v, ev = staged
+        torch.cuda.current_stream(dev).wait_event(ev)
+        touched = []
+        if has_t:
+            sh.train.x, self._shadow_train = self._shadow_train, sh.train.x
+            touched.append(sh.train.x)
+        if has_v:
+            sh.valid.x, self._shadow_valid = self._shadow_valid, sh.valid.x
+            touched.append(sh.valid.x)
+        if touched and hasattr(self.backend, "data_updated"):
+            self.backend.data_updated(*touched)
+
     # ------------------------------------------------------------------ resume (absent in the reference)
     def snapshot(self) -> Dict:
         return {"state": self.state.state_dict(), "agg_count_host": list(self.agg_count_host),

@@ -206,3 +206,23 @@ def test_full_round_with_tensor_core_scoring(tiny_clients, tmp_path, dev):
         assert res_gpu.aggregator == res_ref.aggregator
         assert_close(e_gpu.state.params, e_ref.state.params, 3e-3, 3e-5, f"params r{r}")
         assert_close(torch.tensor(res_gpu.client_metrics), torch.tensor(res_ref.client_metrics), 0, 2e-3, "auc")
+
+
+def test_staged_upload_swaps_shards_and_refreshes_residuals(tiny_clients, tmp_path, dev):
+    cfg = make_cfg(tmp_path, epoch=1, score_precision="tf32x3")
+    eng = make_engine(cfg, make_shards(tiny_clients, dev), "hybrid", "mse_avg", "cuda")
+    r0 = eng.run_round(0)
+    host_train = (eng.sh.train.x * 0.9).cpu().pin_memory()
+    v0, v1 = eng.sh.valid.off_host[0], eng.sh.valid.off_host[6]
+    host_valid = eng.sh.valid.x[v0:v1].cpu().pin_memory()
+    for r in range(1, 3):
+        eng.stage_next_data(host_train, host_valid)
+        eng.commit_staged_data()
+        res = eng.run_round(r)
+    torch.cuda.synchronize()
+    assert torch.equal(eng.sh.train.x.cpu(), host_train) and len(res.client_metrics) == 6
+    lo = eng.backend._resid.get(eng.sh.train.x.data_ptr())
+    if lo is not None:       # residual shard belongs to the *current* buffer and matches its contents
+        x = eng.sh.train.x
+        hi = (x.view(torch.int32) & -8192).view(torch.float32)
+        assert torch.equal(lo, x - hi)

@@ -161,3 +161,18 @@ def test_control_prefetch_keeps_rng_order(tiny_clients, tmp_path):
     for x, y in zip(ra, rb):
         assert x.selected == y.selected and x.aggregator == y.aggregator and x.client_metrics == y.client_metrics
     assert torch.equal(a.state.params, b.state.params)
+
+
+def test_streaming_data_update(tiny_clients, tmp_path):
+    cfg = make_cfg(tmp_path, epoch=1)
+    eng = make_engine(cfg, make_shards(tiny_clients), "hybrid", "avg")
+    new_train = eng.sh.train.x * 0.5
+    v0, v1 = eng.sh.valid.off_host[0], eng.sh.valid.off_host[6]
+    new_valid = eng.sh.valid.x[v0:v1] * 2.0
+    eng.stage_next_data(new_train.clone(), new_valid.clone())
+    assert not torch.equal(eng.sh.train.x, new_train)          # not visible before the commit
+    eng.commit_staged_data()
+    assert torch.equal(eng.sh.train.x, new_train) and torch.equal(eng.sh.valid.x[v0:v1], new_valid)
+    eng.update_local_data(train_x=new_train * 2.0)
+    assert torch.equal(eng.sh.train.x, new_train * 2.0)
+    assert len(eng.run_round(0).client_metrics) == 6
