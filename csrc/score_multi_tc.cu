@@ -21,9 +21,10 @@
 namespace fm {
 namespace tc {
 
-constexpr int NT_MM = 160;
-constexpr int MM_TMEM_COLS = 256;
-constexpr int C_D1A = 0, C_D1B = 32, C_A2 = 64, C_A2LO = 96, C_D2 = 128;
+constexpr int NT_MM = 288;                 // warps 0-3: epilogue 1, warps 4-7: epilogue 2, warp 8: TMA + MMA producer
+constexpr int PRODUCER_WARP = 8;
+constexpr int MM_TMEM_COLS = 512;
+constexpr int C_D1A = 0, C_D1B = 32, C_A2A = 64, C_A2B = 96, C_A2LOA = 128, C_A2LOB = 160, C_D2A = 256, C_D2B = 384;
 constexpr int TBL_FLOATS = 512;                            // w2[7][28] | w3[27][8] | b1[32] | b2[8] | b3[32] (+pad)
 constexpr int T_W2 = 0, T_W3 = 196, T_B1 = 412, T_B2 = 444, T_B3 = 452;
 // operand image of one model in global memory (bytes): w1 hi | w1 lo | tables | w4 hi | w4 lo
@@ -36,12 +37,13 @@ struct MmSmem {
     static constexpr int LO = PREC == 3 ? 1 : 0;
     alignas(1024) unsigned char x[4 * XBLK];
     alignas(1024) unsigned char xlo[LO ? 4 * XBLK : 1024];
-    alignas(1024) unsigned char w1[4 * W1BLK];
-    alignas(1024) unsigned char w1lo[LO ? 4 * W1BLK : 1024];
+    static constexpr int NB1 = PREC == 3 ? 1 : 2;          // w1 image buffers (two hide the image load latency)
+    alignas(1024) unsigned char w1[NB1][4 * W1BLK];
+    alignas(1024) unsigned char w1lo[NB1][LO ? 4 * W1BLK : 1024];
     alignas(1024) unsigned char w4[128 * 128];
     alignas(1024) unsigned char w4lo[LO ? 128 * 128 : 1024];
     alignas(16) float tbl[2][TBL_FLOATS];
-    alignas(8) uint64_t bar_x, bar_xfree, bar_w1, bar_w4, bar_d1[2], bar_h2, bar_d2;
+    alignas(8) uint64_t bar_x, bar_xfree, bar_w1[2], bar_w4, bar_d1[2], bar_h2[2], bar_d2[2], bar_d2free[2];
     uint32_t tmem_base;
 };
 
@@ -86,7 +88,8 @@ template <int PREC>
 __global__ void __launch_bounds__(NT_MM, 1)
 score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_constant__ CUtensorMap xlomap,
                       const unsigned char* __restrict__ images, const int* __restrict__ owned_slots,
-                      const int* __restrict__ n_owned_ptr, int x_rows, float* __restrict__ out_sse) {
+                      const int* __restrict__ n_owned_ptr, int x_rows, float* __restrict__ out_sse,
+                      unsigned long long* __restrict__ dbg) {
     extern __shared__ unsigned char smem_dyn[];
     using SM = MmSmem<PREC>;
     SM& S = *reinterpret_cast<SM*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
@@ -96,11 +99,13 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_con
     if (n_models <= 0 || (int)blockIdx.x >= n_tiles) return;
 
     if (tid == 0) {
-        mbar_init(&S.bar_x, 1); mbar_init(&S.bar_w1, 1); mbar_init(&S.bar_w4, 1);
-        mbar_init(&S.bar_d1[0], 1); mbar_init(&S.bar_d1[1], 1); mbar_init(&S.bar_d2, 1); mbar_init(&S.bar_h2, 128); mbar_init(&S.bar_xfree, 128);
+        mbar_init(&S.bar_x, 1); mbar_init(&S.bar_w1[0], 1); mbar_init(&S.bar_w1[1], 1); mbar_init(&S.bar_w4, 1);
+        mbar_init(&S.bar_d1[0], 1); mbar_init(&S.bar_d1[1], 1); mbar_init(&S.bar_d2[0], 1); mbar_init(&S.bar_d2[1], 1);
+        mbar_init(&S.bar_h2[0], 128); mbar_init(&S.bar_h2[1], 128); mbar_init(&S.bar_xfree, 128);
+        mbar_init(&S.bar_d2free[0], 128); mbar_init(&S.bar_d2free[1], 128);
         fence_mbar_init();
     }
-    if (warp == 4) {
+    if (warp == PRODUCER_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)), "r"(MM_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
@@ -115,14 +120,20 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_con
     const int my_tiles = (n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
     const long long total = (long long)my_tiles * n_models;       // (tile, model) pairs of this CTA, in order
 
-    if (warp == 4) {
+    // Software pipeline inside a tile (n_models pairs): the tensor core runs MMA 1 of model k+1 while the
+    // epilogue warps finish model k, and the epilogue warps run epilogue 1 of model k+1 while the tensor core
+    // runs MMA 2 of model k.  D1, the h2 operand and D2 are all double buffered in TMEM (buffer = pair & 1).
+    // The two epilogues run on different warp groups (both groups own the same TMEM lane quarters), one pair apart.
+    // Rule kept throughout: no waiter can fall two phases behind the mbarrier it waits on.
+    if (warp == PRODUCER_WARP) {
         if (lane == 0) {
             auto load_w1 = [&](long long g) {             // w1 image + tables of pair g
                 const unsigned char* img = images + (size_t)(g % n_models) * IMG_BYTES;
-                mbar_expect_tx(&S.bar_w1, W1BYTES);
-                bulk_load(S.w1, img + IMG_W1, 16384, &S.bar_w1);
-                if (PREC == 3) bulk_load(S.w1lo, img + IMG_W1LO, 16384, &S.bar_w1);
-                bulk_load(S.tbl[g & 1], img + IMG_TBL, TBL_FLOATS * 4, &S.bar_w1);
+                const int wb = (int)(g % SM::NB1);
+                mbar_expect_tx(&S.bar_w1[wb], W1BYTES);
+                bulk_load(S.w1[wb], img + IMG_W1, 16384, &S.bar_w1[wb]);
+                if (PREC == 3) bulk_load(S.w1lo[wb], img + IMG_W1LO, 16384, &S.bar_w1[wb]);
+                bulk_load(S.tbl[g & 1], img + IMG_TBL, TBL_FLOATS * 4, &S.bar_w1[wb]);
             };
             auto load_w4 = [&](long long g) {
                 const unsigned char* img = images + (size_t)(g % n_models) * IMG_BYTES;
@@ -139,71 +150,94 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_con
                     if (PREC == 3) tma_load_2d(S.xlo + kb * XBLK, &xlomap, kb * 32, row0, &S.bar_x);
                 }
             };
-            load_x(0); load_w1(0); load_w4(0);
-            int tile_i = 0, k = 0;
-            for (long long g = 0; g < total; ++g) {
-                const uint32_t b = (uint32_t)(g & 1), ph = (uint32_t)(g & 1), ph1 = (uint32_t)((g >> 1) & 1);
-                if (k == 0) mbar_wait(&S.bar_x, (uint32_t)(tile_i & 1));
-                mbar_wait(&S.bar_w1, ph);
+            const uint64_t dx = smem_desc_sw128(S.x), dxlo = smem_desc_sw128(S.xlo);
+            const uint64_t dw1a = smem_desc_sw128(S.w1[0]), dw1b = smem_desc_sw128(S.w1[SM::NB1 - 1]);
+            const uint64_t dw1loa = smem_desc_sw128(S.w1lo[0]), dw1lob = smem_desc_sw128(S.w1lo[SM::NB1 - 1]);
+            const uint64_t dw4 = smem_desc_sw128(S.w4), dw4lo = smem_desc_sw128(S.w4lo);
+            auto issue_mma1 = [&](long long g) {          // needs: x tile resident, w1(g) landed, D1[g&1] free
+                const int wb = (int)(g % SM::NB1);
+                mbar_wait(&S.bar_w1[wb], (uint32_t)((g / SM::NB1) & 1));
                 tc_fence_after();
-                const uint32_t d1 = tmem + (b ? C_D1B : C_D1A);
+                const uint32_t d1 = tmem + ((g & 1) ? C_D1B : C_D1A);
+                // descriptors differ only in the 14-bit start-address field (units of 16 B): base + constant
+                const uint64_t bw1 = wb ? dw1b : dw1a, bw1lo = wb ? dw1lob : dw1loa;
 #pragma unroll
                 for (int kb = 0; kb < 4; ++kb) {
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks) {
-                        const uint64_t ad = smem_desc_sw128(S.x + kb * XBLK + ks * 32);
-                        const uint64_t bd = smem_desc_sw128(S.w1 + kb * W1BLK + ks * 32);
+                        const uint64_t ad = dx + (uint64_t)((kb * XBLK + ks * 32) >> 4);
+                        const uint64_t bd = bw1 + (uint64_t)((kb * W1BLK + ks * 32) >> 4);
                         mma_ss(d1, ad, bd, IDESC1, (kb | ks) ? 1u : 0u);
                         if (PREC == 3) {
-                            mma_ss(d1, ad, smem_desc_sw128(S.w1lo + kb * W1BLK + ks * 32), IDESC1, 1u);
-                            mma_ss(d1, smem_desc_sw128(S.xlo + kb * XBLK + ks * 32), bd, IDESC1, 1u);
+                            mma_ss(d1, ad, bw1lo + (uint64_t)((kb * W1BLK + ks * 32) >> 4), IDESC1, 1u);
+                            mma_ss(d1, dxlo + (uint64_t)((kb * XBLK + ks * 32) >> 4), bd, IDESC1, 1u);
                         }
                     }
                 }
-                tc_commit(&S.bar_d1[b]);
-                mbar_wait(&S.bar_d1[b], ph1);                       // MMA 1 done: w1 (and, after the last model, x) reusable
-                const bool last_model = (k == n_models - 1);
-                if (g + 1 < total) load_w1(g + 1);
-                mbar_wait(&S.bar_h2, ph);                           // epilogue 1 of this pair done (h2 in TMEM)
-                mbar_wait(&S.bar_w4, ph);
-                tc_fence_after();
-#pragma unroll
-                for (int ks = 0; ks < 4; ++ks) {
-                    const uint64_t bd = smem_desc_sw128(S.w4 + ks * 32);
-                    mma_ts(tmem + C_D2, tmem + C_A2 + ks * 8, bd, IDESC2, ks ? 1u : 0u);
-                    if (PREC == 3) {
-                        mma_ts(tmem + C_D2, tmem + C_A2 + ks * 8, smem_desc_sw128(S.w4lo + ks * 32), IDESC2, 1u);
-                        mma_ts(tmem + C_D2, tmem + C_A2LO + ks * 8, bd, IDESC2, 1u);
+                tc_commit(&S.bar_d1[g & 1]);
+            };
+            long long t_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            long long t_prev = clock64();
+            const bool timing = dbg != nullptr && blockIdx.x == 0;
+#define MM_TICK(slot) do { if (timing) { const long long now_ = clock64(); t_acc[slot] += now_ - t_prev; t_prev = now_; } } while (0)
+            load_x(0); load_w1(0); load_w4(0);
+            if (SM::NB1 == 2 && total > 1) load_w1(1);      // second image in flight from the start
+            long long g = 0;
+            for (int tile_i = 0; tile_i < my_tiles; ++tile_i) {
+                mbar_wait(&S.bar_x, (uint32_t)(tile_i & 1));
+                issue_mma1(g);
+                for (int k = 0; k < n_models; ++k, ++g) {
+                    const uint32_t b = (uint32_t)(g & 1), ph2 = (uint32_t)((g >> 1) & 1);
+                    MM_TICK(0);
+                    mbar_wait(&S.bar_d1[b], ph2);                   // MMA 1 (g) done: its w1 buffer is reusable
+                    MM_TICK(1);
+                    if (SM::NB1 == 1) { if (g + 1 < total) load_w1(g + 1); }
+                    if (g >= 1) {                                   // MMA 2 (g-1) precedes MMA 1 (g) in the pipe: done by now
+                        mbar_wait(&S.bar_d2[b ^ 1u], (uint32_t)(((g - 1) >> 1) & 1));
+                        load_w4(g);                                 // w4 buffer free again -> image of this pair
                     }
+                    if (k + 1 < n_models) issue_mma1(g + 1);        // same x tile; D1[(g+1)&1] was released by epi 1 (g-1)
+                    MM_TICK(2);
+                    mbar_wait(&S.bar_h2[b], ph2);                   // epilogue 1 (g) done: h2(g) in TMEM, tables[b] free
+                    MM_TICK(3);
+                    if (SM::NB1 == 2) { if (g + 2 < total) load_w1(g + 2); }   // into the buffer MMA 1 (g) just released
+                    mbar_wait(&S.bar_w4, (uint32_t)(g & 1));
+                    MM_TICK(4);
+                    if (g >= 2) mbar_wait(&S.bar_d2free[b], (uint32_t)(((g - 2) >> 1) & 1));   // epilogue 2 (g-2) has read D2[b]
+                    MM_TICK(5);
+                    tc_fence_after();
+                    const uint32_t d2 = tmem + (b ? C_D2B : C_D2A), a2 = tmem + (b ? C_A2B : C_A2A), a2lo = tmem + (b ? C_A2LOB : C_A2LOA);
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        const uint64_t bd = dw4 + (uint64_t)((ks * 32) >> 4);
+                        mma_ts(d2, a2 + ks * 8, bd, IDESC2, ks ? 1u : 0u);
+                        if (PREC == 3) {
+                            mma_ts(d2, a2 + ks * 8, dw4lo + (uint64_t)((ks * 32) >> 4), IDESC2, 1u);
+                            mma_ts(d2, a2lo + ks * 8, bd, IDESC2, 1u);
+                        }
+                    }
+                    tc_commit(&S.bar_d2[b]);                        // completion is awaited one pair later (see above)
+                    MM_TICK(6);
                 }
-                tc_commit(&S.bar_d2);
-                mbar_wait(&S.bar_d2, ph);                           // MMA 2 done: w4 reusable
-                if (g + 1 < total) load_w4(g + 1);
-                if (last_model) {
-                    // the resident x tile was read by MMA 1 of every model (all complete) and is still being read by
-                    // epilogue 2 of this last pair: refill it only after the epilogue warps release it
-                    mbar_wait(&S.bar_xfree, (uint32_t)(tile_i & 1));
-                    if (tile_i + 1 < my_tiles) load_x(tile_i + 1);
-                }
-                if (++k == n_models) { k = 0; ++tile_i; }
+                // tile boundary: drain.  Every MMA 1 of this tile has completed; epilogue 2 of the last model still
+                // reads x from shared memory, so the refill waits for the epilogue warps' release.
+                mbar_wait(&S.bar_xfree, (uint32_t)(tile_i & 1));
+                if (tile_i + 1 < my_tiles) load_x(tile_i + 1);
+                MM_TICK(7);
             }
+            if (timing) for (int i = 0; i < 8; ++i) dbg[i] = (unsigned long long)t_acc[i];
         }
         __syncwarp();
     } else {
-        const int r = warp * 32 + lane;
-        const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
-        int tile_i = 0, k = 0;
-        for (long long g = 0; g < total; ++g) {
-            const uint32_t b = (uint32_t)(g & 1), ph = (uint32_t)(g & 1), ph1 = (uint32_t)((g >> 1) & 1);
-            const int row0 = ((int)blockIdx.x + tile_i * (int)gridDim.x) * TROWS;
-            const float* T = S.tbl[b];
-            // The tables of this pair arrived with the w1 image: the producer observed bar_w1 before it issued
-            // MMA 1, whose completion (bar_d1) is observed here, so they are visible.  The epilogue must NOT wait
-            // on bar_w1 itself: the producer may already have armed and completed the NEXT w1 phase, and a waiter
-            // two phases behind an mbarrier never wakes up.
-            mbar_wait(&S.bar_d1[b], ph1);
+        const int r = (warp & 3) * 32 + lane;
+        const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+        uint32_t v[32];
+
+        auto epilogue1 = [&](long long g) {        // D1 -> bias/ReLU -> 27->7->27 bottleneck -> h2 (hi/lo) into TMEM
+            const uint32_t b = (uint32_t)(g & 1), ph2 = (uint32_t)((g >> 1) & 1);
+            const float* T = S.tbl[b];            // landed with w1(g); visible through bar_d1 (see note above)
+            mbar_wait(&S.bar_d1[b], ph2);
             tc_fence_after();
-            uint32_t v[32];
             tmem_ld32(lane_base + (b ? C_D1B : C_D1A), v);
             float h1[28];
 #pragma unroll
@@ -234,23 +268,28 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_con
             v[27] = __float_as_uint(1.0f);
 #pragma unroll
             for (int j = H + 1; j < 32; ++j) v[j] = 0u;
-            tmem_st32(lane_base + C_A2, v);
+            if (g >= 2) {                                  // MMA 2 (g-2) must have consumed the previous h2 in this buffer
+                mbar_wait(&S.bar_d2[b], (uint32_t)(((g - 2) >> 1) & 1));
+                tc_fence_after();
+            }
+            tmem_st32(lane_base + (b ? C_A2B : C_A2A), v);
             if (PREC == 3) {
 #pragma unroll
                 for (int j = 0; j < H; ++j) v[j] = __float_as_uint(h1[j]);
                 v[27] = 0u;
-                tmem_st32(lane_base + C_A2LO, v);
+                tmem_st32(lane_base + (b ? C_A2LOB : C_A2LOA), v);
             }
             tc_fence_before();
-            mbar_arrive(&S.bar_h2);
-            // ---- epilogue 2: x straight from the resident tile ----
-            if (k == 0) mbar_wait(&S.bar_x, (uint32_t)(tile_i & 1));   // acquire the TMA-written tile for generic loads
-            mbar_wait(&S.bar_d2, ph);
+            mbar_arrive(&S.bar_h2[b]);
+        };
+        auto epilogue2 = [&](long long g, int k, int row0) {   // D2 (= x_hat incl. b4) minus x from the resident tile
+            const uint32_t b = (uint32_t)(g & 1), ph2 = (uint32_t)((g >> 1) & 1);
+            mbar_wait(&S.bar_d2[b], ph2);
             tc_fence_after();
             float sse = 0.f;
 #pragma unroll
             for (int cb = 0; cb < 4; ++cb) {
-                tmem_ld32(lane_base + C_D2 + cb * 32, v);
+                tmem_ld32(lane_base + (b ? C_D2B : C_D2A) + cb * 32, v);
                 const unsigned char* xb = S.x + cb * XBLK + r * 128;
 #pragma unroll
                 for (int q4 = 0; q4 < 8; ++q4) {
@@ -266,13 +305,27 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_con
             }
             const int slot = owned_slots[k];
             if (row0 + r < x_rows) out_sse[(size_t)slot * x_rows + row0 + r] = sse;
-            if (k == n_models - 1) mbar_arrive(&S.bar_xfree);          // done with this x tile
-            if (++k == n_models) { k = 0; ++tile_i; }
+        };
+
+        long long g = 0;
+        if (warp < 4) {                            // group A: epilogue 1 of every pair, in order
+            for (; g < total; ++g) epilogue1(g);
+        } else {                                   // group B: epilogue 2 of every pair, releases D2 and the x tile
+            for (int tile_i = 0; tile_i < my_tiles; ++tile_i) {
+                const int row0 = ((int)blockIdx.x + tile_i * (int)gridDim.x) * TROWS;
+                mbar_wait(&S.bar_x, (uint32_t)(tile_i & 1));        // acquire the TMA-written tile for generic loads
+                for (int k = 0; k < n_models; ++k, ++g) {
+                    epilogue2(g, k, row0);
+                    tc_fence_before();
+                    mbar_arrive(&S.bar_d2free[g & 1]);
+                }
+                mbar_arrive(&S.bar_xfree);                          // done reading this x tile
+            }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(MM_TMEM_COLS));
+    if (warp == PRODUCER_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(MM_TMEM_COLS));
 }
 
 }  // namespace tc
@@ -329,7 +382,7 @@ extern "C" int fm_score_multi_tc(const FmMultiScoreArgs* a, void* stream) {
     if (err != cudaSuccess) return (int)err;
     const int n_tiles = (int)((a->x_rows + TROWS - 1) / TROWS);
     const int grid = n_tiles < sms ? n_tiles : sms;
-    if (x3) score_multi_tc_kernel<3><<<grid, NT_MM, smem, st>>>(map, lomap, a->images, a->owned_slots, a->n_owned, (int)a->x_rows, a->out_sse);
-    else score_multi_tc_kernel<1><<<grid, NT_MM, smem, st>>>(map, lomap, a->images, a->owned_slots, a->n_owned, (int)a->x_rows, a->out_sse);
+    if (x3) score_multi_tc_kernel<3><<<grid, NT_MM, smem, st>>>(map, lomap, a->images, a->owned_slots, a->n_owned, (int)a->x_rows, a->out_sse, a->dbg_cycles);
+    else score_multi_tc_kernel<1><<<grid, NT_MM, smem, st>>>(map, lomap, a->images, a->owned_slots, a->n_owned, (int)a->x_rows, a->out_sse, a->dbg_cycles);
     return (int)cudaGetLastError();
 }

@@ -42,7 +42,8 @@ class FmScoreArgs(C.Structure):
 class FmMultiScoreArgs(C.Structure):
     _fields_ = [("slab", c_vp), ("slot_client", c_vp), ("n_slots", C.c_int32), ("first_client", C.c_int32),
                 ("n_local", C.c_int32), ("X", c_vp), ("X_lo", c_vp), ("x_rows", C.c_int64), ("precision", C.c_int32),
-                ("images", c_vp), ("owned_slots", c_vp), ("n_owned", c_vp), ("out_sse", c_vp)]
+                ("images", c_vp), ("owned_slots", c_vp), ("n_owned", c_vp), ("out_sse", c_vp),
+                ("dbg_cycles", c_vp)]
 
 
 TC_IMAGE_BYTES = 67584

@@ -269,7 +269,8 @@ class CudaBackend:
             lo = self._residual(sh.dev) if self.tc == 3 else None
             a = _lib.FmMultiScoreArgs(_ptr(st.params), _ptr(self.ctl_sel), n, sh.first_client, st.n_clients,
                                       _ptr(sh.dev), _ptr(lo), R, self.tc, _ptr(self._images),
-                                      _ptr(self._owned[1:]), _ptr(self._owned[:1]), _ptr(self.merge_sse))
+                                      _ptr(self._owned[1:]), _ptr(self._owned[:1]), _ptr(self.merge_sse),
+                                      _ptr(getattr(self, "mm_cycles", None)))
             _lib.check(self.lib.fm_score_multi_tc(C.byref(a), self._stream()), "score_multi_tc")
             self.launches += 2
         else:

@@ -108,6 +108,7 @@ typedef struct FmMultiScoreArgs {
     const float* X; const float* X_lo; int64_t x_rows; int32_t precision;
     unsigned char* images; int32_t* owned_slots; int32_t* n_owned;
     float* out_sse;
+    unsigned long long* dbg_cycles; /* optional [8]: producer-thread wait breakdown of CTA 0 (SM cycles), or NULL */
 } FmMultiScoreArgs;
 int fm_score_multi_tc(const FmMultiScoreArgs* args, void* stream);
 

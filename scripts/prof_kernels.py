@@ -36,6 +36,7 @@ eng = FederationEngine(cfg, sh, "hybrid", "mse_avg")
 be, st = eng.backend, eng.state
 if a.phase_cycles:
     be.phase_cycles = torch.zeros(8, dtype=torch.int64, device=dev)
+    be.mm_cycles = torch.zeros(8, dtype=torch.int64, device=dev)
 ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
 for it in range(a.iters):
     ctl = eng.make_control(it)
@@ -60,3 +61,8 @@ for it in range(a.iters):
         cyc = be.phase_cycles.tolist()
         tot = sum(cyc)
         print("  phase cycles (CTA 0): " + ", ".join(f"{n} {c/1e3:.0f}k ({100*c/tot:.0f}%)" for n, c in zip(names, cyc)))
+    if a.phase_cycles and a.what == "score" and be.tc:
+        names = ["loop", "wait MMA1(g)", "issue MMA1(g+1)", "wait epi1(g)", "wait w4 image", "wait D2 free", "MMA2 issue+wait", "tile drain"]
+        cyc = be.mm_cycles.tolist()
+        tot = sum(cyc) or 1
+        print("  producer thread (CTA 0): " + ", ".join(f"{n} {c/1e3:.0f}k ({100*c/tot:.0f}%)" for n, c in zip(names, cyc)))
