@@ -10,8 +10,9 @@
 // prep kernel builds once per round; the producer thread pulls them with bulk async copies, software
 // pipelined against the MMAs and epilogues of the previous model:
 //
-//   w1 image (k+1) is fetched as soon as MMA 1 of model k has completed, w4 image (k+1) as soon as MMA 2 of
-//   model k has completed; D1 is double buffered in TMEM so MMA 1 (k+1) overlaps the epilogues of model k.
+//   the w1 image is double buffered (image k+2 is requested when epilogue 1 of model k is done), the w4 image
+//   of model k is requested as soon as MMA 2 of model k-1 has retired; D1, h2 and D2 are double buffered in
+//   TMEM so MMA 1 (k+1) and epilogue 1 (k+1) overlap MMA 2 and epilogue 2 of model k.
 //
 // Per (tile, model): 48 + 12 tcgen05.mma (3xTF32) or 16 + 4 (TF32), one thread per row for the 27->7->27
 // bottleneck and the squared error (x read back from the resident tile with swizzle-aware LDS.128).
@@ -25,11 +26,17 @@ constexpr int NT_MM = 288;                 // warps 0-3: epilogue 1, warps 4-7: 
 constexpr int PRODUCER_WARP = 8;
 constexpr int MM_TMEM_COLS = 512;
 constexpr int C_D1A = 0, C_D1B = 32, C_A2A = 64, C_A2B = 96, C_A2LOA = 128, C_A2LOB = 160, C_D2A = 256, C_D2B = 384;
-constexpr int TBL_FLOATS = 512;                            // w2[7][28] | w3[27][8] | b1[32] | b2[8] | b3[32] (+pad)
-constexpr int T_W2 = 0, T_W3 = 196, T_B1 = 412, T_B2 = 444, T_B3 = 452;
-// operand image of one model in global memory (bytes): w1 hi | w1 lo | tables | w4 hi | w4 lo
-constexpr int IMG_W1 = 0, IMG_W1LO = 16384, IMG_TBL = 32768, IMG_W4 = 32768 + TBL_FLOATS * 4, IMG_W4LO = IMG_W4 + 16384;
-constexpr int IMG_BYTES = IMG_W4LO + 16384;                // 67,584 B
+// small fp32 tables of a model: w2[7][28] | w3[27][8] | b1[32] | b2[8] | b3[32] = 484 floats.  They ride in the
+// five unused rows (n = 27..31) of the four K-blocks of the w1 operand image: the tensor core reads them as
+// operand rows of output columns nobody looks at, the epilogue reads them as plain floats.  160 floats per block.
+constexpr int T_W2 = 0, T_W3 = 196, T_B1 = 412, T_B2 = 444, T_B3 = 452, TBL_FLOATS = 484;
+__host__ __device__ constexpr int tbl_off(int t) {          // byte offset of table float t inside a w1 (hi) image
+    return (t / 160) * W1BLK + (27 + (t % 160) / 32) * 128 + (t % 32) * 4;
+}
+static_assert(TBL_FLOATS <= 4 * 160, "tables do not fit in the pad rows");
+// operand image of one model in global memory (bytes): w1 hi (+tables) | w1 lo | w4 hi | w4 lo
+constexpr int IMG_W1 = 0, IMG_W1LO = 16384, IMG_W4 = 32768, IMG_W4LO = IMG_W4 + 16384;
+constexpr int IMG_BYTES = IMG_W4LO + 16384;                // 65,536 B
 static_assert(IMG_BYTES == FM_TC_IMAGE_BYTES, "image size drifted from the header");
 
 template <int PREC>
@@ -37,12 +44,11 @@ struct MmSmem {
     static constexpr int LO = PREC == 3 ? 1 : 0;
     alignas(1024) unsigned char x[4 * XBLK];
     alignas(1024) unsigned char xlo[LO ? 4 * XBLK : 1024];
-    static constexpr int NB1 = PREC == 3 ? 1 : 2;          // w1 image buffers (two hide the image load latency)
+    static constexpr int NB1 = 2;                          // w1 image buffers (two hide the image load latency)
     alignas(1024) unsigned char w1[NB1][4 * W1BLK];
     alignas(1024) unsigned char w1lo[NB1][LO ? 4 * W1BLK : 1024];
     alignas(1024) unsigned char w4[128 * 128];
     alignas(1024) unsigned char w4lo[LO ? 128 * 128 : 1024];
-    alignas(16) float tbl[2][TBL_FLOATS];
     alignas(8) uint64_t bar_x, bar_xfree, bar_w1[2], bar_w4, bar_d1[2], bar_h2[2], bar_d2[2], bar_d2free[2];
     uint32_t tmem_base;
 };
@@ -63,7 +69,7 @@ __global__ void __launch_bounds__(256) prep_images_kernel(const float* __restric
     for (int i = tid; i < IMG_BYTES / 16; i += 256) reinterpret_cast<uint4*>(img)[i] = make_uint4(0, 0, 0, 0);
     __syncthreads();
     const float* row = slab + (size_t)c * P_PAD;
-    float* tbl = reinterpret_cast<float*>(img + IMG_TBL);
+    auto tset = [&](int t, float v) { *reinterpret_cast<float*>(img + IMG_W1 + tbl_off(t)) = v; };
     auto put = [&](int off_hi, int off_lo, int off, float v) {
         if (PREC == 3) {
             const uint32_t hi = trunc_tf32(v);
@@ -74,11 +80,11 @@ __global__ void __launch_bounds__(256) prep_images_kernel(const float* __restric
     for (int p = tid; p < NP; p += 256) {
         const float v = row[p];
         if (p < OFF_B1) { const int n = p / D, k = p - n * D; put(IMG_W1, IMG_W1LO, (k >> 5) * W1BLK + sw128(n, k & 31), v); }
-        else if (p < OFF_W2) tbl[T_B1 + p - OFF_B1] = v;
-        else if (p < OFF_B2) { const int q = p - OFF_W2, i = q / H, j = q - i * H; tbl[T_W2 + i * 28 + j] = v; }
-        else if (p < OFF_W3) tbl[T_B2 + p - OFF_B2] = v;
-        else if (p < OFF_B3) { const int q = p - OFF_W3, j = q / Z, i = q - j * Z; tbl[T_W3 + j * 8 + i] = v; }
-        else if (p < OFF_W4) tbl[T_B3 + p - OFF_B3] = v;
+        else if (p < OFF_W2) tset(T_B1 + p - OFF_B1, v);
+        else if (p < OFF_B2) { const int q = p - OFF_W2, i = q / H, j = q - i * H; tset(T_W2 + i * 28 + j, v); }
+        else if (p < OFF_W3) tset(T_B2 + p - OFF_B2, v);
+        else if (p < OFF_B3) { const int q = p - OFF_W3, j = q / Z, i = q - j * Z; tset(T_W3 + j * 8 + i, v); }
+        else if (p < OFF_W4) tset(T_B3 + p - OFF_B3, v);
         else if (p < OFF_B4) { const int q = p - OFF_W4, d = q / H, j = q - d * H; put(IMG_W4, IMG_W4LO, sw128(d, j), v); }
         else put(IMG_W4, IMG_W4LO, sw128(p - OFF_B4, 27), v);       // b4 rides in column 27 (h2[27] == 1)
     }
@@ -90,9 +96,10 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_con
                       const unsigned char* __restrict__ images, const int* __restrict__ owned_slots,
                       const int* __restrict__ n_owned_ptr, int x_rows, float* __restrict__ out_sse,
                       unsigned long long* __restrict__ dbg) {
-    extern __shared__ unsigned char smem_dyn[];
+    extern __shared__ __align__(1024) unsigned char smem_dyn[];
     using SM = MmSmem<PREC>;
-    SM& S = *reinterpret_cast<SM*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
+    SM& S = *reinterpret_cast<SM*>(smem_dyn);                // 3xTF32 uses 224 KB of operands: no room for alignment slack
+    if ((smem_u32(smem_dyn) & 1023u) != 0u) __trap();         // 128-B swizzle needs a 1024-B aligned base
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n_models = *n_owned_ptr;
     const int n_tiles = (x_rows + TROWS - 1) / TROWS;
@@ -115,7 +122,7 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_con
     const uint32_t tmem = S.tmem_base;
     constexpr uint32_t IDESC1 = idesc_tf32(128, 32), IDESC2 = idesc_tf32(128, 128);
     constexpr uint32_t XBYTES = (PREC == 3 ? 2u : 1u) * 4u * XBLK;
-    constexpr uint32_t W1BYTES = (PREC == 3 ? 2u : 1u) * 16384u + TBL_FLOATS * 4u;
+    constexpr uint32_t W1BYTES = (PREC == 3 ? 2u : 1u) * 16384u;
     constexpr uint32_t W4BYTES = (PREC == 3 ? 2u : 1u) * 16384u;
     const int my_tiles = (n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
     const long long total = (long long)my_tiles * n_models;       // (tile, model) pairs of this CTA, in order
@@ -133,7 +140,6 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_con
                 mbar_expect_tx(&S.bar_w1[wb], W1BYTES);
                 bulk_load(S.w1[wb], img + IMG_W1, 16384, &S.bar_w1[wb]);
                 if (PREC == 3) bulk_load(S.w1lo[wb], img + IMG_W1LO, 16384, &S.bar_w1[wb]);
-                bulk_load(S.tbl[g & 1], img + IMG_TBL, TBL_FLOATS * 4, &S.bar_w1[wb]);
             };
             auto load_w4 = [&](long long g) {
                 const unsigned char* img = images + (size_t)(g % n_models) * IMG_BYTES;
@@ -235,30 +241,33 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const __grid_con
 
         auto epilogue1 = [&](long long g) {        // D1 -> bias/ReLU -> 27->7->27 bottleneck -> h2 (hi/lo) into TMEM
             const uint32_t b = (uint32_t)(g & 1), ph2 = (uint32_t)((g >> 1) & 1);
-            const float* T = S.tbl[b];            // landed with w1(g); visible through bar_d1 (see note above)
+            // tables sit in the pad rows of the w1 image of this pair (buffer g & 1); they landed with it and are
+            // visible through bar_d1: the producer observed bar_w1 before it issued MMA 1 (see note above)
+            const unsigned char* TB = S.w1[b];
+            auto T1 = [&](int t) -> float { return *reinterpret_cast<const float*>(TB + tbl_off(t)); };
+            auto T4 = [&](int t) -> float4 { return *reinterpret_cast<const float4*>(TB + tbl_off(t)); };
             mbar_wait(&S.bar_d1[b], ph2);
             tc_fence_after();
             tmem_ld32(lane_base + (b ? C_D1B : C_D1A), v);
             float h1[28];
 #pragma unroll
-            for (int j = 0; j < H; ++j) h1[j] = fmaxf(__uint_as_float(v[j]) + T[T_B1 + j], 0.f);
+            for (int j = 0; j < H; ++j) h1[j] = fmaxf(__uint_as_float(v[j]) + T1(T_B1 + j), 0.f);
             h1[27] = 0.f;
             float z[8];
 #pragma unroll
             for (int i = 0; i < Z; ++i) {
-                float acc = T[T_B2 + i];
+                float acc = T1(T_B2 + i);
 #pragma unroll
                 for (int j4 = 0; j4 < 28; j4 += 4) {
-                    const float4 w = *reinterpret_cast<const float4*>(&T[T_W2 + i * 28 + j4]);
+                    const float4 w = T4(T_W2 + i * 28 + j4);
                     acc = fmaf(h1[j4], w.x, fmaf(h1[j4 + 1], w.y, fmaf(h1[j4 + 2], w.z, fmaf(h1[j4 + 3], w.w, acc))));
                 }
                 z[i] = acc;
             }
 #pragma unroll
             for (int j = 0; j < H; ++j) {
-                const float4 wa = *reinterpret_cast<const float4*>(&T[T_W3 + j * 8]);
-                const float4 wb = *reinterpret_cast<const float4*>(&T[T_W3 + j * 8 + 4]);
-                float acc = T[T_B3 + j];
+                const float4 wa = T4(T_W3 + j * 8), wb = T4(T_W3 + j * 8 + 4);
+                float acc = T1(T_B3 + j);
                 acc = fmaf(z[0], wa.x, fmaf(z[1], wa.y, fmaf(z[2], wa.z, fmaf(z[3], wa.w, acc))));
                 acc = fmaf(z[4], wb.x, fmaf(z[5], wb.y, fmaf(z[6], wb.z, acc)));
                 const float hv = fmaxf(acc, 0.f);
@@ -376,7 +385,7 @@ extern "C" int fm_score_multi_tc(const FmMultiScoreArgs* a, void* stream) {
     if (rc) return rc;
     static int sms = 0;
     if (!sms) { int dev; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
-    const size_t smem = (x3 ? sizeof(MmSmem<3>) : sizeof(MmSmem<1>)) + 1024;
+    const size_t smem = x3 ? sizeof(MmSmem<3>) : sizeof(MmSmem<1>);
     err = x3 ? cudaFuncSetAttribute(score_multi_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
              : cudaFuncSetAttribute(score_multi_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return (int)err;

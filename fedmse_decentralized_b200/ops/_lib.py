@@ -46,7 +46,7 @@ class FmMultiScoreArgs(C.Structure):
                 ("dbg_cycles", c_vp)]
 
 
-TC_IMAGE_BYTES = 67584
+TC_IMAGE_BYTES = 65536
 
 
 class FmVoteArgs(C.Structure):

@@ -102,7 +102,7 @@ int fm_split_residual(const float* x, float* x_lo, int64_t rows, void* stream);
  * out_sse is laid out [n_slots][x_rows]; rows of slots owned by other ranks are left untouched.
  * Scratch (caller): images >= owned * FM_TC_IMAGE_BYTES bytes, owned_slots[n_slots] ints, n_owned[1] int.
  * (reference: the full-batch dev-set forward of fed_mse_avg, client_trainer.py:118-124). */
-#define FM_TC_IMAGE_BYTES 67584
+#define FM_TC_IMAGE_BYTES 65536
 typedef struct FmMultiScoreArgs {
     const float* slab; const int32_t* slot_client; int32_t n_slots; int32_t first_client; int32_t n_local;
     const float* X; const float* X_lo; int64_t x_rows; int32_t precision;
