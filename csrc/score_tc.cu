@@ -163,7 +163,7 @@ score_rows_tc_kernel(const FmScoreArgs a, const __grid_constant__ CUtensorMap xm
         stage_model<PREC>(S, a.slab + (size_t)c * P_PAD);
 
         if (warp == 4) {
-            if (lane == 0) {
+            if (elect_one()) {      // elect.sync: ptxas emits the UTCHMMA sequence without per-MMA election loops
                 auto load_tile = [&](int ti) {
                     const int row0 = tiles[ti].y;
                     mbar_expect_tx(&S.bar_x, XBYTES);

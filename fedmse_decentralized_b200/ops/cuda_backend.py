@@ -266,9 +266,9 @@ class CudaBackend:
                 self._images = torch.empty(max(1, st.n_clients) * _lib.TC_IMAGE_BYTES, dtype=torch.uint8,
                                            device=self.device)
                 self._owned = torch.zeros(max(1, sh.n_global) + 1, dtype=torch.int32, device=self.device)
-            lo = self._residual(sh.dev) if self.tc == 3 else None
+            # (the kernel splits X into TF32 head + remainder itself while parking it in tensor memory: no residual shard)
             a = _lib.FmMultiScoreArgs(_ptr(st.params), _ptr(self.ctl_sel), n, sh.first_client, st.n_clients,
-                                      _ptr(sh.dev), _ptr(lo), R, self.tc, _ptr(self._images),
+                                      _ptr(sh.dev), None, R, self.tc, _ptr(self._images),
                                       _ptr(self._owned[1:]), _ptr(self._owned[:1]), _ptr(self.merge_sse),
                                       _ptr(getattr(self, "mm_cycles", None)))
             _lib.check(self.lib.fm_score_multi_tc(C.byref(a), self._stream()), "score_multi_tc")

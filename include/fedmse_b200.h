@@ -96,9 +96,11 @@ int fm_score_rows_tc(const FmScoreArgs* args, int64_t x_rows, int32_t precision,
 int fm_split_residual(const float* x, float* x_lo, int64_t rows, void* stream);
 
 /* ---- many models on one shared matrix (MSE-weight scoring on the pooled dev set) -----------
- * Inverts the loop of fm_score_rows_tc: each CTA keeps one 128-row tile of X resident in shared memory
- * and runs every locally owned slot's model over it (operand images pre-staged by a prep kernel and
- * pulled with bulk async copies), so X is read once per tile instead of once per (tile, model).
+ * Inverts the loop of fm_score_rows_tc: each CTA keeps one 128-row tile of X resident on chip (TF32 head and
+ * fp32 remainder in tensor memory as the A operand, the fp32 tile in shared memory for the error) and runs
+ * a chunk of the locally owned slots' models over it (operand images pre-staged by a prep kernel and pulled
+ * with bulk async copies), so X is read once per unit instead of once per (tile, model).
+ * X_lo is ignored since v5 (the split happens in the kernel); the field stays for ABI stability.
  * out_sse is laid out [n_slots][x_rows]; rows of slots owned by other ranks are left untouched.
  * Scratch (caller): images >= owned * FM_TC_IMAGE_BYTES bytes, owned_slots[n_slots] ints, n_owned[1] int.
  * (reference: the full-batch dev-set forward of fed_mse_avg, client_trainer.py:118-124). */
@@ -108,7 +110,7 @@ typedef struct FmMultiScoreArgs {
     const float* X; const float* X_lo; int64_t x_rows; int32_t precision;
     unsigned char* images; int32_t* owned_slots; int32_t* n_owned;
     float* out_sse;
-    unsigned long long* dbg_cycles; /* optional [8]: producer-thread wait breakdown of CTA 0 (SM cycles), or NULL */
+    unsigned long long* dbg_cycles; /* optional [32]: CTA 0 cycle breakdown (producer [0..7], epilogue 1 [8..11], epilogue 2 [12..15], clock stamps of the first unit boundaries [16..31]), or NULL */
 } FmMultiScoreArgs;
 int fm_score_multi_tc(const FmMultiScoreArgs* args, void* stream);
 

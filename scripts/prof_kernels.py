@@ -36,7 +36,7 @@ eng = FederationEngine(cfg, sh, "hybrid", "mse_avg")
 be, st = eng.backend, eng.state
 if a.phase_cycles:
     be.phase_cycles = torch.zeros(8, dtype=torch.int64, device=dev)
-    be.mm_cycles = torch.zeros(8, dtype=torch.int64, device=dev)
+    be.mm_cycles = torch.zeros(32, dtype=torch.int64, device=dev)
 ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
 for it in range(a.iters):
     ctl = eng.make_control(it)
@@ -62,7 +62,15 @@ for it in range(a.iters):
         tot = sum(cyc)
         print("  phase cycles (CTA 0): " + ", ".join(f"{n} {c/1e3:.0f}k ({100*c/tot:.0f}%)" for n, c in zip(names, cyc)))
     if a.phase_cycles and a.what == "score" and be.tc:
-        names = ["loop", "wait MMA1(g)", "issue MMA1(g+1)", "wait epi1(g)", "wait w4 image", "wait D2 free", "MMA2 issue+wait", "tile drain"]
+        names = ["issue MMA1(g+1)", "wait MMA2(g-1)", "wait epi1(g)", "wait w4 image", "wait D2 free", "issue MMA2(g)",
+                 "wait X in TMEM", "wait X staging free",
+                 "A: wait X smem", "A: X->TMEM", "A: wait MMA1", "A: epilogue 1",
+                 "B: unit entry", "B: wait MMA2", "B: D2->regs", "B: rest"]
         cyc = be.mm_cycles.tolist()
-        tot = sum(cyc) or 1
-        print("  producer thread (CTA 0): " + ", ".join(f"{n} {c/1e3:.0f}k ({100*c/tot:.0f}%)" for n, c in zip(names, cyc)))
+        tot = sum(cyc[:8]) or 1
+        print("  producer thread (CTA 0): " + ", ".join(f"{n} {c/1e3:.0f}k ({100*c/tot:.0f}%)" for n, c in zip(names[:8], cyc[:8])))
+        print("  epilogue warps (CTA 0):  " + ", ".join(f"{n} {c/1e3:.0f}k" for n, c in zip(names[8:], cyc[8:])))
+        for k in range(4):
+            w0, w1, a0, a1 = cyc[16 + 4 * k: 20 + 4 * k]
+            if w0:
+                print(f"  boundary {k}: producer waits {w1 - w0} cycles; A reaches the boundary {a0 - w0:+d}, X in TMEM {a1 - w0:+d} (relative to the producer's arrival)")

@@ -195,6 +195,37 @@ def test_tensor_core_scoring_matches_oracle(tiny_clients, tmp_path, dev, precisi
     assert_close(a_gpu, torch.tensor(a64), 0, 3e-3, "auc")
 
 
+@pytest.mark.parametrize("precision,rtol", [("tf32", 2e-2), ("tf32x3", 2e-4)])
+def test_multi_model_scoring_matches_oracle(tmp_path, dev, precision, rtol):
+    """Many models on the pooled dev matrix (X parked in tensor memory, (tile, model-chunk) work units):
+    every (model, row) squared error against the fp32 oracle, for full, small and single-model selections
+    (the last two leave some model chunks empty)."""
+    from fedmse_decentralized_b200.data import SyntheticSpec, make_clients, prepare_from_raw
+    spec = SyntheticSpec(n_normal=2400, n_abnormal=40, n_test_normal=20, jitter_rows=10)
+    clients = prepare_from_raw(make_clients(12, spec, seed=11), True, seed=5)
+    cfg = make_cfg(tmp_path, epoch=1, network_size=12, score_precision=precision, write_latents=False,
+                   save_client_models=False)
+    eng = make_engine(cfg, make_shards(clients, dev), "hybrid", "mse_avg", "cuda")
+    be, st, sh = eng.backend, eng.state, eng.sh
+    R = be.dev_rows
+    assert R > 6 * 128, "the test wants several tiles"
+    st.params.mul_(1.0 + 0.05 * torch.randn_like(st.params))        # different models per client
+    host = st.params.cpu()
+    X = sh.dev.cpu()[:R]
+    for sel in ([3, 0, 11, 7, 5, 1, 9, 2, 10, 4, 8, 6], [4, 9, 2], [6]):
+        ctl = RoundControl(round=0, sel=list(sel), voter_pos=0, jitter=[1.0] * len(sel), vote_client=sel[0],
+                           verify_client=-1)
+        be.begin_round(ctl)
+        be.merge_sse = None
+        mse = be.merge_scores(st, sh, ctl)
+        torch.cuda.synchronize()
+        got = be.merge_sse[:len(sel) * R].view(len(sel), R)
+        for p, c in enumerate(sel):
+            want = oracle.row_sse(host[c], X, L)
+            assert_close(got[p], want, rtol, rtol * 10, f"{precision} slot {p} client {c}")
+            assert_close(mse[p], want.double().mean() / L.dim, rtol, 0, f"{precision} mse slot {p}")
+
+
 def test_full_round_with_tensor_core_scoring(tiny_clients, tmp_path, dev):
     e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "autoencoder", "mse_avg", score_precision="tf32x3",
                          num_participants=0.7)
