@@ -193,9 +193,10 @@ def run_ours(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak",
             "vs_baseline": value / BASELINE_LOCAL_SAMPLES_PER_SEC,
-            "dtype": {"fp32": "fp32", "tf32": "fp32 training + tf32 scoring forwards",
-                      "tf32x3": "fp32 (training: fp32 FFMA; scoring forwards: error-compensated 3xTF32 on tcgen05, "
-                                "fp32 accumulate, ~1e-6 relative to fp32)"}[args.score_precision],
+            "dtype": {"fp32": "fp32 (training GEMMs: error-compensated 3xTF32 mma.sync, fp32 accumulate; rest FFMA)",
+                      "tf32": "fp32 training (3xTF32 GEMMs) + tf32 scoring forwards",
+                      "tf32x3": "fp32 (parameters, Adam, accumulation in fp32; GEMMs as error-compensated 3xTF32: training "
+                                "on mma.sync, scoring forwards on tcgen05; ~1e-6 relative to fp32 FFMA)"}[args.score_precision],
             "data": "synthetic", "impl": "ours",
             "rounds_per_sec": args.steps / (ms / 1e3),
             "config": {"model": f"SAE-CEN 115-27-7 ({args.model}) + {args.update}",

@@ -1,4 +1,4 @@
-// T1 -- persistent per-client local training (exact fp32, CUDA cores).
+// T1 -- persistent per-client local training (fp32; the three batch GEMMs on warp-level tensor-core MMA, 3xTF32).
 //
 // One CTA owns one selected client for its whole ClientTrainer.run() call
 // (reference: src/Trainer/client_trainer.py:360-419): weights (27 KB), Adam moments (54 KB) and,
@@ -9,9 +9,14 @@
 // fused; weight gradients are consumed by the Adam update in registers and never stored.
 //
 // The batch is 12 rows and every step depends on the previous step's weights, so the
-// matrix products are [12 x K] x [K x N] with N <= 115: far below a tcgen05 tile (M >= 64).
-// The products therefore run as register-tiled FFMA out of shared memory; what this kernel
-// buys over the reference is persistence (no launches, no host syncs, no HBM round trips).
+// matrix products are [12 x K] x [K x N] with N <= 115: far below a tcgen05 tile (M >= 64, and one
+// thread per TMEM lane in the epilogue).  The m16n8k8 warp-level MMA fits exactly: the batch is the
+// M = 16 tile.  Layer 1, the output layer (+ loss) and the data gradient run as error-compensated
+// 3xTF32 mma.sync (hi*hi + hi*lo + lo*hi, fp32 accumulate: fp32-grade, same trick as the scoring
+// kernels); operands come from shared memory with ldmatrix (pitches chosen conflict-free).  The
+// bottleneck 27 -> 7 -> 27, the weight gradients and Adam stay on FFMA.  FM_TRAIN_MMA=0 in the
+// environment selects the all-FFMA variant (also used for batches of 13..32 rows).
+#include <cstdlib>
 #include "common.cuh"
 #include "../include/fedmse_b200.h"
 
@@ -19,6 +24,9 @@ namespace fm {
 
 // phase timing (debug): thread 0 of CTA 0 accumulates SM cycles per phase when args.phase_cycles != NULL
 #define FM_TICK(slot) do { if (dbg) { dbg_sink += *reinterpret_cast<volatile int*>(&S.flag[0]); /* forces the deferred barrier wait */ const long long now_ = clock64(); dbg_acc[slot] += now_ - dbg_t; dbg_t = now_; } } while (0)
+
+// same clock, no forced barrier wait: splits a phase into "this warp's work" and "waiting for the others"
+#define FM_TICK_WORK(slot) do { if (dbg) { const long long now_ = clock64(); dbg_acc[slot] += now_ - dbg_t; dbg_t = now_; } } while (0)
 
 constexpr int NT = 512;  // threads per CTA
 
@@ -136,6 +144,48 @@ __device__ __forceinline__ void layer_dgrad(const float* __restrict__ GoutT, con
     }
 }
 
+// ---- warp-level tensor-core helpers (m16n8k8, TF32 inputs, fp32 accumulate) ---------------------
+// fragment coordinates, g = lane >> 2, t = lane & 3:  A: a0 (g, t) a1 (g+8, t) a2 (g, t+4) a3 (g+8, t+4);
+// B (k, n): b0 (t, g) b1 (t+4, g);  C: c0 (g, 2t) c1 (g, 2t+1) c2 (g+8, 2t) c3 (g+8, 2t+1).
+__device__ __forceinline__ void ldsm4(uint32_t (&r)[4], const float* row_ptr) {   // four 8 x (4 floats) blocks
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_u32(row_ptr)));
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// C += A B in 3xTF32: A = ah + al, B = bh + bl with ah/bh the fp32 values themselves (the tensor core ignores their
+// low 13 mantissa bits, i.e. sees trunc_tf32) and al/bl the exact fp32 remainders, which are kept in shared memory
+// next to their operands (tf32_lo below) -- the MMA loops contain no arithmetic, only ldmatrix and mma.sync.
+// Work split (measured with scripts/mma_sync_probe.cu: an mma.sync issues every 8 cycles per SM sub-partition with a
+// 20-cycle dependent latency; an ldmatrix.x4 costs 4 cycles of the SM's shared-memory bandwidth): eight warps, each
+// owning two adjacent 8-column output tiles (they share the A fragments, one ldmatrix.x4 fetches the B fragments of
+// both) and, for the two long-K products, one quarter of the k-steps.  The partial sums of the k-quarters meet in
+// shared memory and are added by the consumer of the result (the warp-per-row bottleneck code), so no extra block
+// barrier is needed.  Per phase: 128 ldmatrix (512 cycles of smem bandwidth) and 48 MMAs per sub-partition (420).
+struct Acc2 {
+    float hh[4], sm[4];             // head product | the two small cross terms
+    __device__ __forceinline__ void zero() {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { hh[i] = 0.f; sm[i] = 0.f; }
+    }
+    __device__ __forceinline__ float sum(int i) const { return sm[i] + hh[i]; }
+};
+// one k-step for two adjacent 8-column output tiles that share the A fragments; b* = {tile0 b0, tile0 b1, tile1 b0, tile1 b1}.
+// Issue order keeps four MMAs between two writes of the same accumulator.
+__device__ __forceinline__ void mma3x2(Acc2& c0, Acc2& c1, const uint32_t (&ah)[4], const uint32_t (&al)[4],
+                                       const uint32_t (&bh)[4], const uint32_t (&bl)[4]) {
+    mma_tf32(c0.hh, ah, bh[0], bh[1]);
+    mma_tf32(c1.hh, ah, bh[2], bh[3]);
+    mma_tf32(c0.sm, ah, bl[0], bl[1]);
+    mma_tf32(c1.sm, ah, bl[2], bl[3]);
+    mma_tf32(c0.sm, al, bh[0], bh[1]);
+    mma_tf32(c1.sm, al, bh[2], bh[3]);
+}
+__device__ __forceinline__ float tf32_lo(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
+
 struct AdamStep {
     float step_size;     // lr / (1 - b1^t)
     float inv_sqrt_bc2;  // 1 / sqrt(1 - b2^t)
@@ -232,7 +282,7 @@ __device__ __forceinline__ void wgrad_adam(int item0, const float* __restrict__ 
 // are read once per tile instead of once per output feature, and the weights are touched once per step.
 template <int BT, int N, int K4>
 __device__ __forceinline__ void wgrad_adam_tile(int item, const float* __restrict__ GT, const float* __restrict__ A,
-                                                int AP, int sW, int WP, float* Ws, const float* As, const AdamStep& st,
+                                                int AP, int sW, int WP, float* Ws, float* Wlo, const float* As, const AdamStep& st,
                                                 float (&m)[16], float (&v)[16], float& prox_acc) {
     const int nt = item / K4, kc = item - nt * K4;
     const int n0 = nt * 4, nvalid = min(4, N - n0);
@@ -269,6 +319,7 @@ __device__ __forceinline__ void wgrad_adam_tile(int item, const float* __restric
             adam1(w.z, m[q * 4 + 2], v[q * 4 + 2], an.z, g[q * 4 + 2], st, prox_acc);
             adam1(w.w, m[q * 4 + 3], v[q * 4 + 3], an.w, g[q * 4 + 3], st, prox_acc);
             *reinterpret_cast<float4*>(Ws + idx) = w;
+            if (Wlo) *reinterpret_cast<float4*>(Wlo + idx) = make_float4(tf32_lo(w.x), tf32_lo(w.y), tf32_lo(w.z), tf32_lo(w.w));
         }
     }
 }
@@ -295,32 +346,44 @@ constexpr int W4_TILES = ((D + 3) / 4) * 7;     // 29 x 7 = 203
 constexpr int ROLE_W1 = 0, ROLE_W4 = 224, ROLE_SMALL = 448;   // first thread of each role (warp aligned)
 static_assert(W1_TILES <= ROLE_W4 - ROLE_W1 && W4_TILES <= ROLE_SMALL - ROLE_W4, "role ranges too small");
 
-template <int BT>
+template <int BT, bool MMA>
 struct TrainSmem {
-    static constexpr int HP = 28, ZP = 8, XHP = 116;
+    // MMA variant: 16-row operand tiles (rows BT..15 stay zero), pitches 132 / 36 floats so that the eight
+    // 16-byte rows of an ldmatrix block land in eight different bank groups
+    static constexpr int RB = MMA ? 16 : BT;
+    static constexpr int XS = MMA ? 132 : XP;
+    static constexpr int HP = MMA ? 36 : 28, ZP = 8;
     alignas(16) float W[S_TOT];
     alignas(16) float M[S_TOT];
     alignas(16) float V[S_TOT];
-    alignas(16) float x[2][BT * XP];
-    alignas(16) float h1[BT * HP];
+    alignas(16) float x[2][RB * XS];
+    alignas(16) float h1[RB * HP];
     alignas(16) float z[BT * ZP];
-    alignas(16) float h2[BT * HP];
+    alignas(16) float h2[RB * HP];
+    alignas(16) float dxr[MMA ? 16 * 132 : 4];   // d(loss)/d(xhat) row-major [b][d]: A operand of the data gradient
+    // exact TF32 remainders (x - trunc_tf32(x)) of the tensor-core operands, same indexing as their heads
+    alignas(16) float Wlo[MMA ? S_TOT + 32 : 4];  // W1 / W4 regions only (+32: operand tiles read a little past the end)
+    alignas(16) float xlo[MMA ? 16 * 132 : 4];
+    alignas(16) float h2lo[MMA ? 16 * 36 : 4];
+    alignas(16) float dxrlo[MMA ? 16 * 132 : 4];
+    alignas(16) float part[MMA ? 4 * 16 * 32 : 4];   // partial sums of the four k-quarters: [kq][row][column]
     alignas(16) float dxT[D * BT];     // d(loss)/d(xhat), transposed [d][b]
     alignas(16) float dp2T[H * BT];    // grad wrt pre-activation of decoder hidden
     alignas(16) float dzT[Z * BT];
     alignas(16) float dp1T[H * BT];
     float znorm[BT];
     double red[34];
-    float sc[8];                        // step scalars broadcast by thread 0
+    float sctab[64];                    // Adam bias corrections (step size, 1/sqrt(1 - b2^t)) of the next 32 train steps
     int flag[4];
     alignas(8) uint64_t bar[2];
     // FedProx anchor (S_TOT floats) follows only when mu != 0
 };
 
-template <int BT>
+template <int BT, bool MMA>
 __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    using SM = TrainSmem<BT>;
+    using SM = TrainSmem<BT, MMA>;
+    constexpr int XS = SM::XS;
     SM& S = *reinterpret_cast<SM*>(smem_raw);
     float* As = reinterpret_cast<float*>(smem_raw + ((sizeof(SM) + 15) / 16) * 16);  // valid iff mu != 0
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -338,8 +401,13 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
 
     // ---- load state into shared memory -----------------------------------------------------
     for (int i = tid; i < S_TOT; i += NT) { S.W[i] = 0.f; S.M[i] = 0.f; S.V[i] = 0.f; if (prox) As[i] = 0.f; }
-    for (int i = tid; i < 2 * BT * XP; i += NT) (&S.x[0][0])[i] = 0.f;
-    for (int i = tid; i < BT * SM::HP; i += NT) { S.h1[i] = 0.f; S.h2[i] = 0.f; }
+    for (int i = tid; i < 2 * SM::RB * XS; i += NT) (&S.x[0][0])[i] = 0.f;
+    for (int i = tid; i < SM::RB * SM::HP; i += NT) { S.h1[i] = 0.f; S.h2[i] = 0.f; }
+    if (MMA) {
+        for (int i = tid; i < 16 * 132; i += NT) { S.dxr[i] = 0.f; S.dxrlo[i] = 0.f; S.xlo[i] = 0.f; }
+        for (int i = tid; i < 16 * 36; i += NT) S.h2lo[i] = 0.f;
+        for (int i = tid; i < S_TOT + 32; i += NT) S.Wlo[i] = 0.f;
+    }
     for (int i = tid; i < BT * SM::ZP; i += NT) S.z[i] = 0.f;
     for (int i = tid; i < D * BT; i += NT) S.dxT[i] = 0.f;
     for (int i = tid; i < H * BT; i += NT) { S.dp2T[i] = 0.f; S.dp1T[i] = 0.f; }
@@ -351,6 +419,10 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
         S.W[s] = gp[p]; S.M[s] = gm[p]; S.V[s] = gv[p];
         if (prox) As[s] = a.anchor[(size_t)c * P_PAD + p];
     }
+    if (MMA) {
+        __syncthreads();
+        for (int i = tid; i < S_TOT; i += NT) S.Wlo[i] = tf32_lo(S.W[i]);
+    }
     float tm[16], tv[16];          // Adam moments of this thread's register tile (roles W1 / W4)
 #pragma unroll
     for (int i = 0; i < 16; ++i) { tm[i] = 0.f; tv[i] = 0.f; }
@@ -360,29 +432,40 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
     __syncthreads();
 
     // batch stream: per epoch nbt train batches then nbv validation batches
-    auto issue = [&](int q_in_epoch, int buf) {   // thread 0 only
+    constexpr int ISSUE_WARP = 14;                // a warp without tensor-core work in layer 1
+    auto issue = [&](int q_in_epoch, int buf) {   // called by every lane of warp ISSUE_WARP
         const float* src; int rows;
         if (q_in_epoch < nbt) { const int r0 = q_in_epoch * B; rows = min(B, n_tr - r0); src = a.x_train + (size_t)(tr0 + r0) * XP; }
         else { const int r0 = (q_in_epoch - nbt) * B; rows = min(B, n_va - r0); src = a.x_valid + (size_t)(va0 + r0) * XP; }
         const uint32_t bytes = (uint32_t)rows * XP * 4u;
-        mbar_expect_tx(&S.bar[buf], bytes);
-        bulk_g2s(&S.x[buf][0], src, bytes, &S.bar[buf]);
+        if (lane == 0) mbar_expect_tx(&S.bar[buf], bytes);
+        __syncwarp();
+        if (MMA) {       // padded shared-memory pitch: one 512-byte copy per row, one lane each
+            if (lane < rows) bulk_g2s(&S.x[buf][lane * XS], src + (size_t)lane * XP, XP * 4u, &S.bar[buf]);
+        } else if (lane == 0) bulk_g2s(&S.x[buf][0], src, bytes, &S.bar[buf]);
     };
 
-    int t_step = a.adam_t[c];    // tracked by thread NT-1 only
-    double b1t = 1.0, b2t = 1.0;
-    if (tid == NT - 1) { b1t = pow(0.9, (double)t_step); b2t = pow(0.999, (double)t_step); }
+    // Adam bias corrections are computed in double like the reference (torch computes them on the host), but FP64
+    // divide + sqrt cost ~1k cycles on one thread -- longer than the tensor-core layer 1 they used to hide behind.
+    // Warp 15 therefore tabulates them for 32 steps at a time, one step per lane.
+    const int t_step0 = a.adam_t[c];
+    int ts = 0;                                         // train steps taken in this launch (uniform)
+    double b1t = 1.0, b2t = 1.0, p1 = 1.0, p2 = 1.0;    // warp 15: beta^t at the last tabulated step; beta^(lane+1)
+    if (warp == 15) {
+        b1t = pow(0.9, (double)t_step0); b2t = pow(0.999, (double)t_step0);
+        p1 = pow(0.9, (double)(lane + 1)); p2 = pow(0.999, (double)(lane + 1));
+    }
     float min_valid = __int_as_float(0x7f800000);
     int worse = 0, epochs_done = 0;
     uint32_t uses0 = 0, uses1 = 0;   // completed waits per buffer -> parity
     long long q = 0;                  // global step index (selects the buffer)
     bool outstanding = false;
-    if (tid == 0 && steps_per_epoch > 0 && a.epochs > 0 && n_tr > 0) issue(0, 0);
+    if (warp == ISSUE_WARP && steps_per_epoch > 0 && a.epochs > 0 && n_tr > 0) issue(0, 0);
     outstanding = (steps_per_epoch > 0 && a.epochs > 0 && n_tr > 0);
     const int n_epochs = (n_tr > 0) ? a.epochs : 0;
 
     const bool dbg = a.phase_cycles != nullptr && blockIdx.x == 0 && tid == 0;
-    long long dbg_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long dbg_acc[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     long long dbg_t = clock64();
     int dbg_sink = 0;
     for (int e = 0; e < n_epochs; ++e) {
@@ -398,21 +481,70 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
             mbar_wait(&S.bar[buf], (buf ? uses1 : uses0) & 1u);
             if (buf) ++uses1; else ++uses0;
             const bool has_next = (qe + 1 < steps_per_epoch) || (e + 1 < n_epochs);
-            if (tid == 0 && has_next) issue((qe + 1) % steps_per_epoch, buf ^ 1);
+            // (tensor-core variant: the twelve row copies are issued after the remainder pass below, while warps 0-7 run
+            // the layer-1 MMAs -- issued here they delay the block barrier of that pass by ~800 cycles)
+            if (!MMA && warp == ISSUE_WARP && has_next) issue((qe + 1) % steps_per_epoch, buf ^ 1);
             outstanding = has_next;
             const float* X = &S.x[buf][0];
             FM_TICK(0);
-            if (is_train && tid == NT - 1) {   // bias corrections in double by an otherwise idle thread (warp 15 has
-                ++t_step; b1t *= 0.9; b2t *= 0.999;   // no items in the first layer); consumed three barriers later
-                S.sc[0] = (float)((double)a.lr / (1.0 - b1t));
-                S.sc[1] = (float)(1.0 / sqrt(1.0 - b2t));
+            if (is_train && warp == 15 && (ts & 31) == 0) {   // consumed five barriers later, rewritten 32 steps later
+                const double B1 = b1t * p1, B2 = b2t * p2;
+                S.sctab[2 * lane] = (float)((double)a.lr / (1.0 - B1));
+                S.sctab[2 * lane + 1] = (float)(1.0 / sqrt(1.0 - B2));
+                b1t = __shfl_sync(0xffffffffu, B1, 31);
+                b2t = __shfl_sync(0xffffffffu, B2, 31);
             }
             // ---- forward ----
-            layer_nt<BT, H, 29, 4, true>(X, XP, S.W + S_W1, W1P, S.W + S_B1, S.h1, SM::HP);
+            if constexpr (MMA) {
+                // remainders of this batch for the tensor cores: one float4 per thread (16 rows x 128 columns)
+                {
+                    const int o = (tid >> 5) * XS + (tid & 31) * 4;
+                    const float4 xv = *reinterpret_cast<const float4*>(X + o);
+                    *reinterpret_cast<float4*>(S.xlo + o) = make_float4(tf32_lo(xv.x), tf32_lo(xv.y), tf32_lo(xv.z), tf32_lo(xv.w));
+                }
+                __syncthreads();
+                FM_TICK(11);
+                if (warp == ISSUE_WARP && has_next) issue((qe + 1) % steps_per_epoch, buf ^ 1);
+                // h1[16 x 32] = X[16 x 120] W1^T: warp (kq, nh) = (k-steps kq, kq+4, .., output columns 16nh..16nh+15)
+                if (warp < 8) {
+                    const int g = lane >> 2, t = lane & 3, kq = warp & 3, nh = warp >> 2;
+                    Acc2 c0, c1;
+                    c0.zero(); c1.zero();
+                    const int aoff = ((lane & 7) + ((lane >> 3) & 1) * 8) * XS + (lane >> 4) * 4;
+                    const int boff = S_W1 + (8 * (2 * nh + (lane >> 4)) + (lane & 7)) * W1P + ((lane >> 3) & 1) * 4;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int ks = kq + 4 * i;               // K = 115 -> 15 steps (x is zero past column 114)
+                        if (ks < 15) {
+                            uint32_t ah[4], al[4], bh[4], bl[4];
+                            ldsm4(bh, S.W + boff + 8 * ks);
+                            ldsm4(bl, S.Wlo + boff + 8 * ks);
+                            ldsm4(ah, X + aoff + 8 * ks);
+                            ldsm4(al, S.xlo + aoff + 8 * ks);
+                            mma3x2(c0, c1, ah, al, bh, bl);
+                        }
+                    }
+                    float* pp = S.part + (kq * 16 + g) * 32 + 16 * nh + 2 * t;
+                    *reinterpret_cast<float2*>(pp) = make_float2(c0.sum(0), c0.sum(1));
+                    *reinterpret_cast<float2*>(pp + 8) = make_float2(c1.sum(0), c1.sum(1));
+                    *reinterpret_cast<float2*>(pp + 8 * 32) = make_float2(c0.sum(2), c0.sum(3));
+                    *reinterpret_cast<float2*>(pp + 8 * 32 + 8) = make_float2(c1.sum(2), c1.sum(3));
+                }
+            } else {
+                layer_nt<BT, H, 29, 4, true>(X, XS, S.W + S_W1, W1P, S.W + S_B1, S.h1, SM::HP);
+            }
+            FM_TICK_WORK(8);
             __syncthreads();
             FM_TICK(1);
             // bottleneck 27 -> 7 -> 27: one warp per batch row, no block barrier between the two layers
             for (int b = warp; b < BT; b += NT / 32) {
+                if constexpr (MMA) {       // layer-1 epilogue: add the k-quarter partial sums, bias, ReLU
+                    if (lane < H) {
+                        const float* pp = S.part + b * 32 + lane;
+                        S.h1[b * SM::HP + lane] = fmaxf(((pp[0] + pp[512]) + (pp[1024] + pp[1536])) + S.W[S_B1 + lane], 0.f);
+                    }
+                    __syncwarp();
+                }
                 const int i = lane >> 2, sK = lane & 3;
                 float zp = 0.f;
                 if (i < Z) {
@@ -433,7 +565,9 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
                     float acc = S.W[S_B3 + lane];
                     acc = fmaf(zz[0], wa.x, fmaf(zz[1], wa.y, fmaf(zz[2], wa.z, fmaf(zz[3], wa.w, acc))));
                     acc = fmaf(zz[4], wb.x, fmaf(zz[5], wb.y, fmaf(zz[6], wb.z, acc)));
-                    S.h2[b * SM::HP + lane] = fmaxf(acc, 0.f);
+                    const float hv = fmaxf(acc, 0.f);
+                    S.h2[b * SM::HP + lane] = hv;
+                    if (MMA) S.h2lo[b * SM::HP + lane] = tf32_lo(hv);
                 }
                 const float zmine = __shfl_sync(0xffffffffu, zp, (lane < Z ? lane : 0) * 4);
                 if (lane < Z) S.z[b * SM::ZP + lane] = zmine;
@@ -448,7 +582,57 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
             __syncthreads();
             FM_TICK(2);
             // output layer fused with the reconstruction loss and its gradient
-            {
+            if constexpr (MMA) {
+                // xhat[16 x 120] = h2[16 x 32] W4^T: warp w owns features 16w..16w+15 (features >= 115 are masked)
+                if (warp < 8) {
+                    const int g = lane >> 2, t = lane & 3;
+                    Acc2 c0, c1;
+                    c0.zero(); c1.zero();
+                    const int aoff = ((lane & 7) + ((lane >> 3) & 1) * 8) * SM::HP + (lane >> 4) * 4;
+                    const int btile = min(2 * warp + (lane >> 4), 14);      // the 16th tile does not exist: re-read the 15th
+                    const int boff = S_W4 + (8 * btile + (lane & 7)) * W4P + ((lane >> 3) & 1) * 4;
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {                        // h2 is zero past column 26
+                        uint32_t ah[4], al[4], bh[4], bl[4];
+                        ldsm4(bh, S.W + boff + 8 * ks);
+                        ldsm4(bl, S.Wlo + boff + 8 * ks);
+                        ldsm4(ah, S.h2 + aoff + 8 * ks);
+                        ldsm4(al, S.h2lo + aoff + 8 * ks);
+                        mma3x2(c0, c1, ah, al, bh, bl);
+                    }
+                    const float inv = 1.f / ((float)rows * (float)D);
+                    const float sc2 = 2.f * inv;
+                    float lsum = 0.f;
+#pragma unroll
+                    for (int nt = 0; nt < 2; ++nt) {
+                        const Acc2& c = nt ? c1 : c0;
+                        const int d0 = 16 * warp + 8 * nt + 2 * t;
+                        if (d0 < 120) {
+                            const float bb0 = S.W[S_B4 + d0], bb1 = S.W[S_B4 + d0 + 1];
+#pragma unroll
+                            for (int half = 0; half < 2; ++half) {
+                                const int b = g + 8 * half;
+                                const float2 xv = *reinterpret_cast<const float2*>(X + b * XS + d0);
+                                float e0 = (c.sum(2 * half) + bb0) - xv.x;
+                                float e1 = (c.sum(2 * half + 1) + bb1) - xv.y;
+                                e0 = (b < rows && d0 < D) ? e0 : 0.f;
+                                e1 = (b < rows && d0 + 1 < D) ? e1 : 0.f;
+                                lsum = fmaf(e0, e0, fmaf(e1, e1, lsum));
+                                if (is_train) {
+                                    const float s0 = e0 * sc2, s1 = e1 * sc2;
+                                    *reinterpret_cast<float2*>(S.dxr + b * 132 + d0) = make_float2(s0, s1);
+                                    *reinterpret_cast<float2*>(S.dxrlo + b * 132 + d0) = make_float2(tf32_lo(s0), tf32_lo(s1));
+                                    if (b < BT) {
+                                        if (d0 < D) S.dxT[d0 * BT + b] = s0;
+                                        if (d0 + 1 < D) S.dxT[(d0 + 1) * BT + b] = s1;
+                                    }
+                                }
+                            }
+                        }
+                    }
+                    if (is_train) loss_acc = fmaf(lsum, inv, loss_acc); else vloss_acc = fmaf(lsum, inv, vloss_acc);
+                }
+            } else {
                 constexpr int ITEMS = D * (BT / 4);
                 const float inv = 1.f / ((float)rows * (float)D);
                 float lsum = 0.f;
@@ -471,10 +655,10 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
                     }
                     const float bb = S.W[S_B4 + d];
                     const int b0 = bg * 4;
-                    float e0 = (acc0 + bb) - X[(b0 + 0) * XP + d];
-                    float e1 = (acc1 + bb) - X[(b0 + 1) * XP + d];
-                    float e2 = (acc2 + bb) - X[(b0 + 2) * XP + d];
-                    float e3 = (acc3 + bb) - X[(b0 + 3) * XP + d];
+                    float e0 = (acc0 + bb) - X[(b0 + 0) * XS + d];
+                    float e1 = (acc1 + bb) - X[(b0 + 1) * XS + d];
+                    float e2 = (acc2 + bb) - X[(b0 + 2) * XS + d];
+                    float e3 = (acc3 + bb) - X[(b0 + 3) * XS + d];
                     e0 = (b0 + 0 < rows) ? e0 : 0.f; e1 = (b0 + 1 < rows) ? e1 : 0.f;
                     e2 = (b0 + 2 < rows) ? e2 : 0.f; e3 = (b0 + 3 < rows) ? e3 : 0.f;
                     lsum = fmaf(e0, e0, fmaf(e1, e1, fmaf(e2, e2, fmaf(e3, e3, lsum))));
@@ -485,15 +669,57 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
                 }
                 if (is_train) loss_acc = fmaf(lsum, inv, loss_acc); else vloss_acc = fmaf(lsum, inv, vloss_acc);
             }
+            FM_TICK_WORK(9);
             __syncthreads();
             FM_TICK(3);
             if (!is_train) continue;
             // ---- backward ----
-            layer_dgrad<BT, D, H, 4, true>(S.dxT, S.W + S_W4, W4P, S.h2, SM::HP, S.dp2T);
+            if constexpr (MMA) {
+                // dp2[16 x 32] = relu'(h2) * (dx[16 x 120] W4[120 x 32]): warp (kq, nh) as in layer 1; the mask and the sum
+                // over the k-quarters are applied by the bottleneck backward below
+                if (warp < 8) {
+                    const int g = lane >> 2, t = lane & 3, kq = warp & 3, nh = warp >> 2;
+                    Acc2 c0, c1;
+                    c0.zero(); c1.zero();
+                    const int aoff = ((lane & 7) + ((lane >> 3) & 1) * 8) * 132 + (lane >> 4) * 4;
+                    const int boff = S_W4 + t * W4P + 16 * nh + g;                 // B[k = d][n = j] = W4[d][j]
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int ks = kq + 4 * i;                                 // dx is zero past feature 114
+                        if (ks < 15) {
+                            uint32_t ah[4], al[4], bh[4], bl[4];
+                            const int o0 = boff + (8 * ks) * W4P, o1 = o0 + 4 * W4P;
+                            bh[0] = __float_as_uint(S.W[o0]); bh[1] = __float_as_uint(S.W[o1]);
+                            bh[2] = __float_as_uint(S.W[o0 + 8]); bh[3] = __float_as_uint(S.W[o1 + 8]);
+                            bl[0] = __float_as_uint(S.Wlo[o0]); bl[1] = __float_as_uint(S.Wlo[o1]);
+                            bl[2] = __float_as_uint(S.Wlo[o0 + 8]); bl[3] = __float_as_uint(S.Wlo[o1 + 8]);
+                            ldsm4(ah, S.dxr + aoff + 8 * ks);
+                            ldsm4(al, S.dxrlo + aoff + 8 * ks);
+                            mma3x2(c0, c1, ah, al, bh, bl);
+                        }
+                    }
+                    float* pp = S.part + (kq * 16 + g) * 32 + 16 * nh + 2 * t;
+                    *reinterpret_cast<float2*>(pp) = make_float2(c0.sum(0), c0.sum(1));
+                    *reinterpret_cast<float2*>(pp + 8) = make_float2(c1.sum(0), c1.sum(1));
+                    *reinterpret_cast<float2*>(pp + 8 * 32) = make_float2(c0.sum(2), c0.sum(3));
+                    *reinterpret_cast<float2*>(pp + 8 * 32 + 8) = make_float2(c1.sum(2), c1.sum(3));
+                }
+            } else {
+                layer_dgrad<BT, D, H, 4, true>(S.dxT, S.W + S_W4, W4P, S.h2, SM::HP, S.dp2T);
+            }
+            FM_TICK_WORK(10);
             __syncthreads();
             FM_TICK(4);
             // bottleneck backward, one warp per batch row: dz = dp2 W3 + shrink gradient, dp1 = relu'(h1) * (dz W2)
             for (int b = warp; b < BT; b += NT / 32) {
+                if constexpr (MMA) {       // data-gradient epilogue: add the k-quarter partial sums, ReLU mask
+                    if (lane < H) {
+                        const float* pp = S.part + b * 32 + lane;
+                        const float gsum = (pp[0] + pp[512]) + (pp[1024] + pp[1536]);
+                        S.dp2T[lane * BT + b] = S.h2[b * SM::HP + lane] > 0.f ? gsum : 0.f;
+                    }
+                    __syncwarp();
+                }
                 const int i = lane >> 2, sK = lane & 3;
                 float dzp = 0.f;
                 if (i < Z) {
@@ -524,13 +750,13 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
             {
                 float prox_acc = 0.f;
                 AdamStep st;
-                st.step_size = S.sc[0]; st.inv_sqrt_bc2 = S.sc[1]; st.mu = a.fedprox_mu;
+                st.step_size = S.sctab[2 * (ts & 31)]; st.inv_sqrt_bc2 = S.sctab[2 * (ts & 31) + 1]; st.mu = a.fedprox_mu;
                 if (tid < ROLE_W4) {
                     if (tid < W1_TILES)
-                        wgrad_adam_tile<BT, H, 29>(tid, S.dp1T, X, XP, S_W1, W1P, S.W, As, st, tm, tv, prox_acc);
+                        wgrad_adam_tile<BT, H, 29>(tid, S.dp1T, X, XS, S_W1, W1P, S.W, MMA ? S.Wlo : nullptr, As, st, tm, tv, prox_acc);
                 } else if (tid < ROLE_SMALL) {
                     if (tid - ROLE_W4 < W4_TILES)
-                        wgrad_adam_tile<BT, D, 7>(tid - ROLE_W4, S.dxT, S.h2, SM::HP, S_W4, W4P, S.W, As, st, tm, tv, prox_acc);
+                        wgrad_adam_tile<BT, D, 7>(tid - ROLE_W4, S.dxT, S.h2, SM::HP, S_W4, W4P, S.W, MMA ? S.Wlo : nullptr, As, st, tm, tv, prox_acc);
                 } else {
                     constexpr int NS = NT - ROLE_SMALL;
                     const int t0 = tid - ROLE_SMALL;
@@ -548,6 +774,7 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
                 }
                 if (prox) loss_acc = fmaf(a.fedprox_mu, prox_acc, loss_acc);
             }
+            ++ts;
             __syncthreads();
             FM_TICK(6);
         }
@@ -588,8 +815,8 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
     }
     if (tid < ROLE_W4) { if (tid < W1_TILES) tile_moments_io<H, D, 29>(tid, OFF_W1, gm, gv, tm, tv, true); }
     else if (tid < ROLE_SMALL) { if (tid - ROLE_W4 < W4_TILES) tile_moments_io<D, H, 7>(tid - ROLE_W4, OFF_W4, gm, gv, tm, tv, true); }
-    if (dbg) { FM_TICK(7); for (int i = 0; i < 8; ++i) a.phase_cycles[i] = (unsigned long long)dbg_acc[i] + (dbg_sink & 0); }
-    if (tid == NT - 1) a.adam_t[c] = t_step;
+    if (dbg) { FM_TICK(7); for (int i = 0; i < 16; ++i) a.phase_cycles[i] = (unsigned long long)dbg_acc[i] + (dbg_sink & 0); }
+    if (tid == NT - 1) a.adam_t[c] = t_step0 + ts;
     if (tid == 0) {
         a.epochs_run[c] = epochs_done;
         a.trained_rounds[c] += 1;
@@ -610,16 +837,23 @@ extern "C" int fm_train_clients(const FmTrainArgs* args, void* stream) {
     const bool prox = args->fedprox_mu != 0.f;
     cudaStream_t st = (cudaStream_t)stream;
     cudaError_t err;
-    if (args->batch <= 12) {
-        size_t smem = ((sizeof(TrainSmem<12>) + 15) / 16) * 16 + (prox ? S_TOT * sizeof(float) : 0);
-        err = cudaFuncSetAttribute(train_clients_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static int use_mma = -1;
+    if (use_mma < 0) { const char* e = getenv("FM_TRAIN_MMA"); use_mma = (e && e[0] == '0') ? 0 : 1; }
+    if (args->batch <= 12 && use_mma) {
+        size_t smem = ((sizeof(TrainSmem<12, true>) + 15) / 16) * 16 + (prox ? S_TOT * sizeof(float) : 0);
+        err = cudaFuncSetAttribute(train_clients_kernel<12, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return (int)err;
-        train_clients_kernel<12><<<args->n_sel, NT, smem, st>>>(*args);
+        train_clients_kernel<12, true><<<args->n_sel, NT, smem, st>>>(*args);
+    } else if (args->batch <= 12) {
+        size_t smem = ((sizeof(TrainSmem<12, false>) + 15) / 16) * 16 + (prox ? S_TOT * sizeof(float) : 0);
+        err = cudaFuncSetAttribute(train_clients_kernel<12, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (err != cudaSuccess) return (int)err;
+        train_clients_kernel<12, false><<<args->n_sel, NT, smem, st>>>(*args);
     } else {
-        size_t smem = ((sizeof(TrainSmem<32>) + 15) / 16) * 16 + (prox ? S_TOT * sizeof(float) : 0);
-        err = cudaFuncSetAttribute(train_clients_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        size_t smem = ((sizeof(TrainSmem<32, false>) + 15) / 16) * 16 + (prox ? S_TOT * sizeof(float) : 0);
+        err = cudaFuncSetAttribute(train_clients_kernel<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return (int)err;
-        train_clients_kernel<32><<<args->n_sel, NT, smem, st>>>(*args);
+        train_clients_kernel<32, false><<<args->n_sel, NT, smem, st>>>(*args);
     }
     return (int)cudaGetLastError();
 }

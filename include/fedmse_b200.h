@@ -61,7 +61,7 @@ typedef struct FmTrainArgs {
     float lr;
     float shrink_lambda;      /* 0 => plain AE loss */
     float fedprox_mu;         /* 0 => no proximal term */
-    unsigned long long* phase_cycles; /* optional [8] debug counters: SM cycles per phase of CTA 0, or NULL */
+    unsigned long long* phase_cycles; /* optional [16] debug counters: SM cycles per phase of CTA 0 ([8..10]: warp 0's own work inside three of them), or NULL */
 } FmTrainArgs;
 int fm_train_clients(const FmTrainArgs* args, void* stream);
 

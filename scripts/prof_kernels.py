@@ -35,7 +35,7 @@ cfg = ExperimentConfig(epoch=a.epochs, network_size=a.clients, backend="cuda", w
 eng = FederationEngine(cfg, sh, "hybrid", "mse_avg")
 be, st = eng.backend, eng.state
 if a.phase_cycles:
-    be.phase_cycles = torch.zeros(8, dtype=torch.int64, device=dev)
+    be.phase_cycles = torch.zeros(16, dtype=torch.int64, device=dev)
     be.mm_cycles = torch.zeros(32, dtype=torch.int64, device=dev)
 ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
 for it in range(a.iters):
@@ -59,8 +59,14 @@ for it in range(a.iters):
     if a.phase_cycles and a.what == "train":
         names = ["wait-batch", "P1 fwd 115->27", "bottleneck fwd", "P4 out+loss", "B1 dgrad", "bottleneck bwd", "update", "loop/epoch"]
         cyc = be.phase_cycles.tolist()
+        work = cyc[8:11]
+        pre = cyc[11]
+        cyc = cyc[:8]
+        cyc[1] += work[0] + pre; cyc[3] += work[1]; cyc[4] += work[2]
+        print(f"  P1 split: remainder prepass + barrier {pre/1e3:.0f}k")
         tot = sum(cyc)
         print("  phase cycles (CTA 0): " + ", ".join(f"{n} {c/1e3:.0f}k ({100*c/tot:.0f}%)" for n, c in zip(names, cyc)))
+        print(f"  of which warp 0's own work (rest = waiting for other warps): P1 {work[0]/1e3:.0f}k, P4 {work[1]/1e3:.0f}k, B1 {work[2]/1e3:.0f}k")
     if a.phase_cycles and a.what == "score" and be.tc:
         names = ["issue MMA1(g+1)", "wait MMA2(g-1)", "wait epi1(g)", "wait w4 image", "wait D2 free", "issue MMA2(g)",
                  "wait X in TMEM", "wait X staging free",
