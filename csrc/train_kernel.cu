@@ -363,7 +363,7 @@ struct TrainSmem {
     alignas(16) float dxr[MMA ? 16 * 132 : 4];   // d(loss)/d(xhat) row-major [b][d]: A operand of the data gradient
     // exact TF32 remainders (x - trunc_tf32(x)) of the tensor-core operands, same indexing as their heads
     alignas(16) float Wlo[MMA ? S_TOT + 32 : 4];  // W1 / W4 regions only (+32: operand tiles read a little past the end)
-    alignas(16) float xlo[MMA ? 16 * 132 : 4];
+    alignas(16) float xlo[2][MMA ? 16 * 132 : 4];   // per batch buffer; filled one step ahead by warps that idle in the output layer
     alignas(16) float h2lo[MMA ? 16 * 36 : 4];
     alignas(16) float dxrlo[MMA ? 16 * 132 : 4];
     alignas(16) float part[MMA ? 4 * 16 * 32 : 4];   // partial sums of the four k-quarters: [kq][row][column]
@@ -404,7 +404,7 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
     for (int i = tid; i < 2 * SM::RB * XS; i += NT) (&S.x[0][0])[i] = 0.f;
     for (int i = tid; i < SM::RB * SM::HP; i += NT) { S.h1[i] = 0.f; S.h2[i] = 0.f; }
     if (MMA) {
-        for (int i = tid; i < 16 * 132; i += NT) { S.dxr[i] = 0.f; S.dxrlo[i] = 0.f; S.xlo[i] = 0.f; }
+        for (int i = tid; i < 16 * 132; i += NT) { S.dxr[i] = 0.f; S.dxrlo[i] = 0.f; S.xlo[0][i] = 0.f; S.xlo[1][i] = 0.f; }
         for (int i = tid; i < 16 * 36; i += NT) S.h2lo[i] = 0.f;
         for (int i = tid; i < S_TOT + 32; i += NT) S.Wlo[i] = 0.f;
     }
@@ -481,9 +481,9 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
             mbar_wait(&S.bar[buf], (buf ? uses1 : uses0) & 1u);
             if (buf) ++uses1; else ++uses0;
             const bool has_next = (qe + 1 < steps_per_epoch) || (e + 1 < n_epochs);
-            // (tensor-core variant: the twelve row copies are issued after the remainder pass below, while warps 0-7 run
-            // the layer-1 MMAs -- issued here they delay the block barrier of that pass by ~800 cycles)
-            if (!MMA && warp == ISSUE_WARP && has_next) issue((qe + 1) % steps_per_epoch, buf ^ 1);
+            // (tensor-core variant: twelve row copies, ~800 cycles of issue on warp 14 -- hidden behind the layer-1 MMAs of
+            // warps 0-7, there is no block barrier before those)
+            if (warp == ISSUE_WARP && has_next) issue((qe + 1) % steps_per_epoch, buf ^ 1);
             outstanding = has_next;
             const float* X = &S.x[buf][0];
             FM_TICK(0);
@@ -496,15 +496,15 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
             }
             // ---- forward ----
             if constexpr (MMA) {
-                // remainders of this batch for the tensor cores: one float4 per thread (16 rows x 128 columns)
-                {
+                // TF32 remainders of the batch: computed one step ahead (see the output layer); only the first batch of the
+                // launch is split here, one float4 per thread (16 rows x 128 columns)
+                if (q == 0) {
                     const int o = (tid >> 5) * XS + (tid & 31) * 4;
                     const float4 xv = *reinterpret_cast<const float4*>(X + o);
-                    *reinterpret_cast<float4*>(S.xlo + o) = make_float4(tf32_lo(xv.x), tf32_lo(xv.y), tf32_lo(xv.z), tf32_lo(xv.w));
+                    *reinterpret_cast<float4*>(S.xlo[buf] + o) = make_float4(tf32_lo(xv.x), tf32_lo(xv.y), tf32_lo(xv.z), tf32_lo(xv.w));
+                    __syncthreads();
                 }
-                __syncthreads();
                 FM_TICK(11);
-                if (warp == ISSUE_WARP && has_next) issue((qe + 1) % steps_per_epoch, buf ^ 1);
                 // h1[16 x 32] = X[16 x 120] W1^T: warp (kq, nh) = (k-steps kq, kq+4, .., output columns 16nh..16nh+15)
                 if (warp < 8) {
                     const int g = lane >> 2, t = lane & 3, kq = warp & 3, nh = warp >> 2;
@@ -520,7 +520,7 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
                             ldsm4(bh, S.W + boff + 8 * ks);
                             ldsm4(bl, S.Wlo + boff + 8 * ks);
                             ldsm4(ah, X + aoff + 8 * ks);
-                            ldsm4(al, S.xlo + aoff + 8 * ks);
+                            ldsm4(al, S.xlo[buf] + aoff + 8 * ks);
                             mma3x2(c0, c1, ah, al, bh, bl);
                         }
                     }
@@ -631,6 +631,20 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
                         }
                     }
                     if (is_train) loss_acc = fmaf(lsum, inv, loss_acc); else vloss_acc = fmaf(lsum, inv, vloss_acc);
+                } else if (has_next) {
+                    // idle here: split the NEXT batch (requested at the top of this step, long since landed) into its TF32
+                    // remainders so that the next step starts without a pass + block barrier of its own
+                    const int nb = buf ^ 1;
+                    mbar_wait(&S.bar[nb], (nb ? uses1 : uses0) & 1u);      // the wait every thread repeats at the next step
+                    const float* Xn = &S.x[nb][0];
+                    float* Ln = S.xlo[nb];
+#pragma unroll
+                    for (int h2i = 0; h2i < 2; ++h2i) {
+                        const int e = (tid - 256) + 256 * h2i;                // 512 float4: 16 rows x 32
+                        const int o = (e >> 5) * XS + (e & 31) * 4;
+                        const float4 xv = *reinterpret_cast<const float4*>(Xn + o);
+                        *reinterpret_cast<float4*>(Ln + o) = make_float4(tf32_lo(xv.x), tf32_lo(xv.y), tf32_lo(xv.z), tf32_lo(xv.w));
+                    }
                 }
             } else {
                 constexpr int ITEMS = D * (BT / 4);

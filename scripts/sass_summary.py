@@ -22,13 +22,14 @@ for line in txt.splitlines():
     m = re.match(r"\s+/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
     if m and cur:
         op = m.group(1)
-        keep_full = op.startswith(("UTC", "UTMA", "UBLK", "LDTM", "STTM", "SYNCS", "RED", "HMMA", "LDS.128", "LDG.E.STRONG"))
+        keep_full = op.startswith(("UTC", "UTMA", "UBLK", "LDTM", "STTM", "SYNCS", "RED", "HMMA", "LDSM", "USETMAXREG", "LDS.128", "LDG.E.STRONG"))
         counts[cur][op if keep_full else op.split(".")[0]] += 1
 print("SASS evidence per kernel: cuobjdump -sass of libfedmse_b200.so (sm_100a), counts of selected mnemonics.")
 print("tcgen05.mma -> UTCHMMA, tcgen05.ld/st -> LDTM/STTM, tcgen05.commit -> UTCBAR, TMA tensor loads -> UTMALDG,")
-print("cp.async.bulk -> UBLKCP, mbarrier -> SYNCS.*, red.release.sys -> REDG...SYS, ld.acquire.sys -> LDG.E.STRONG.SYS\n")
+print("cp.async.bulk -> UBLKCP, mbarrier -> SYNCS.*, red.release.sys -> REDG...SYS, ld.acquire.sys -> LDG.E.STRONG.SYS,")
+print("mma.sync tf32 -> HMMA.1688.F32.TF32, ldmatrix -> LDSM, setmaxnreg -> USETMAXREG\n")
 for f, c in counts.items():
     name = subprocess.run(["c++filt", f], capture_output=True, text=True).stdout.strip()
-    sel = {k: v for k, v in c.items() if k.startswith(("UTC", "UTMA", "UBLK", "LDTM", "STTM", "SYNCS", "RED", "HMMA", "LDG.E.STRONG"))
+    sel = {k: v for k, v in c.items() if k.startswith(("UTC", "UTMA", "UBLK", "LDTM", "STTM", "SYNCS", "RED", "HMMA", "LDSM", "USETMAXREG", "LDG.E.STRONG"))
            or k in ("FFMA", "LDS.128", "BAR", "SHFL", "MUFU")}
     print(f"{name[:120]}\n    {sum(c.values())} instructions: " + ", ".join(f"{k} {v}" for k, v in sorted(sel.items(), key=lambda kv: -kv[1])))
