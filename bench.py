@@ -162,7 +162,9 @@ def run_ours(args):
                 # the NEXT round's fresh local traffic leaves pinned host memory now, on a side stream, and
                 # lands in shadow shards while this round computes: one upload per round, overlapped
                 eng.stage_next_data(pin_train, pin_valid)
-            res = eng.run_round(r, prefetch_next=True)   # includes the device->host read of the round's results
+            # includes the device->host read of the round's results; while more rounds follow, the next round's
+            # control upload and local training are enqueued before the host blocks on that read
+            res = eng.run_round(r, prefetch_next=True, pipeline_next=not last)
             samples += res.samples
             if with_h2d and not last:
                 eng.commit_staged_data()

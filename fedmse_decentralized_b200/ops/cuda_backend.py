@@ -389,9 +389,15 @@ class CudaBackend:
 
     # ------------------------------------------------------------------ one read-back per round
     def readback(self, st, agg_pos: Optional[torch.Tensor], with_auc: bool):
-        """Gather the round's results with one D2H copy and one stream sync.  Multi-GPU: the per-rank blocks
+        """Gather the round's results with one D2H copy and one wait.  Multi-GPU: the per-rank blocks
         are all-gathered on the device first (one small NCCL call), so the lists returned cover ALL clients:
         (aggregator position, epochs_run[N], rejected[N], auc[N] or None)."""
+        return self.readback_wait(self.readback_async(st, agg_pos, with_auc))
+
+    def readback_async(self, st, agg_pos: Optional[torch.Tensor], with_auc: bool):
+        """Enqueue the packing of the round's results and their D2H copy; returns a handle for
+        ``readback_wait``.  More work (the next round's training) may be enqueued in between: the wait is on
+        an event recorded right behind the copy, not on the stream."""
         C_, W = st.n_clients, self.comm.world
         if getattr(self, "_rb_dev", None) is None:
             cmax = C_
@@ -402,6 +408,7 @@ class CudaBackend:
             self._rb_dev = torch.zeros(2 + 4 * cmax, dtype=torch.int32, device=self.device)
             self._rb_all = torch.zeros(W * (2 + 4 * cmax), dtype=torch.int32, device=self.device)
             self._rb_pin = torch.zeros_like(self._rb_all, device="cpu").pin_memory()
+            self._rb_event = torch.cuda.Event()
         cm, rb = self._rb_cmax, self._rb_dev
         rb[0:2].copy_(agg_pos if agg_pos is not None else self.agg_pos.new_full((2,), -1))
         rb[2:2 + C_].copy_(st.epochs_run)
@@ -415,7 +422,13 @@ class CudaBackend:
         else:
             src = rb
         self._rb_pin[:src.numel()].copy_(src, non_blocking=True)
-        torch.cuda.current_stream(self.device).synchronize()
+        self._rb_event.record(torch.cuda.current_stream(self.device))
+        return (with_auc, src.numel())
+
+    def readback_wait(self, handle):
+        with_auc, _ = handle
+        self._rb_event.synchronize()
+        cm = self._rb_cmax
         host = self._rb_pin.numpy()
         stride = 2 + 4 * cm
         epochs, rejected, auc = [], [], ([] if with_auc else None)

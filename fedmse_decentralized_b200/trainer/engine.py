@@ -131,6 +131,7 @@ class FederationEngine:
         self._neigh_cache = None
         self._rand_fifo: List[float] = []
         self._prefetched = None
+        self._pre = None                 # (round, control) whose upload + local training are already enqueued
         if hasattr(self.backend, "bind"):
             self.backend.bind(self.state, self.sh, self.comm, self.hp, self.spec, model_type)
 
@@ -178,24 +179,55 @@ class FederationEngine:
         return RoundControl(round=round_idx, sel=sel, voter_pos=voter_pos, jitter=jitter,
                             vote_client=sel[0], verify_client=verify_client)
 
+    def _voter_is_decided(self, next_sel: Sequence[int], cur_sel: Sequence[int]) -> bool:
+        """Can the next round's voter be determined before this round's aggregator is known?  The only host
+        state the control block depends on is the aggregation count, and this round raises it by one for one
+        client of ``cur_sel``.  Scan the candidates like ``make_control``: a candidate is surely valid if some
+        other selected client stays under the quota even after such an increment, surely invalid if none is
+        under it now; anything in between has to wait for the read-back."""
+        quota = self.cfg.max_aggregation_threshold
+        cur = set(cur_sel)
+        for k in range(len(next_sel)):
+            low = [g for p, g in enumerate(next_sel) if p != k and self.agg_count_host[g] < quota]
+            if any(self.agg_count_host[g] + (1 if g in cur else 0) < quota for g in low):
+                return True
+            if low:
+                return False
+        return True                       # nobody can vote, whatever this round elects
+
     def _sel_local(self, sel: Sequence[int]) -> List[int]:
         return [g - self.first for g in sel if self.first <= g < self.first + self.n_local]
 
     # ------------------------------------------------------------------ one round
     def run_round(self, round_idx: int, ctl: Optional[RoundControl] = None,
                   evaluate: bool = True, want_latents: Optional[bool] = None,
-                  prefetch_next: bool = False) -> RoundResult:
+                  prefetch_next: bool = False, pipeline_next: bool = False) -> RoundResult:
         """One federated round.  ``prefetch_next`` prepares the next round's selection and random draws on
-        the host while the device executes this round (use it when more rounds follow)."""
-        self._prefetch_next = prefetch_next and ctl is None and self.cfg.aggregation != "gossip"
+        the host while the device executes this round (use it when more rounds follow).
+
+        ``pipeline_next`` is a promise that ``run_round(round_idx + 1)`` WILL be called next with default
+        control: this call then also uploads the next round's control block and enqueues its local training
+        before it waits for its own results, so the device never idles on the host's bookkeeping (staged
+        data, if any, is committed first).  The next call picks up from there.  Results are identical to
+        the unpipelined sequence; if the next voter cannot be determined yet (quota nearly exhausted) the
+        call silently falls back to the plain order."""
+        self._prefetch_next = (prefetch_next or pipeline_next) and ctl is None and self.cfg.aggregation != "gossip"
+        self._pipeline_next = pipeline_next and self._prefetch_next
         if self.cfg.aggregation == "gossip":
             return self._run_round_gossip(round_idx, ctl, evaluate, want_latents)
         be, st, sh, cm, tm = self.backend, self.state, self.sh, self.comm, self.timer
-        ctl = ctl or self.make_control(round_idx)
-        if hasattr(be, "begin_round"):
-            be.begin_round(ctl)
-        with tm.phase("train"):
-            be.train(st, sh, self._sel_local(ctl.sel), self.hp)
+        pre, self._pre = self._pre, None
+        if pre is not None:
+            if pre[0] != round_idx or ctl is not None:
+                raise RuntimeError(f"round {pre[0]} was already started by run_round(..., pipeline_next=True); "
+                                   "it has to be the next round, with the engine's own control")
+            ctl = pre[1]                  # control uploaded, training enqueued
+        else:
+            ctl = ctl or self.make_control(round_idx)
+            if hasattr(be, "begin_round"):
+                be.begin_round(ctl)
+            with tm.phase("train"):
+                be.train(st, sh, self._sel_local(ctl.sel), self.hp)
         agg_pos = None
         if ctl.voter_pos >= 0:
             with tm.phase("vote"):
@@ -231,7 +263,16 @@ class FederationEngine:
             self.prefetch_control(ctl.round + 1)       # overlaps with the kernels enqueued above
         # ---- single readback of the round's results (global lists) ------------------------
         if hasattr(be, "readback") and (not evaluate or auc64 is None):
-            a, epochs_all, rejected, auc_all = be.readback(st, agg_pos, evaluate)
+            handle = be.readback_async(st, agg_pos, evaluate)
+            if getattr(self, "_pipeline_next", False) and self._voter_is_decided(self._prefetched[1], ctl.sel):
+                # the next round's upload and training go in behind this round's work, before the host blocks
+                self.commit_staged_data()
+                nxt = self.make_control(ctl.round + 1)
+                be.begin_round(nxt)
+                with tm.phase("train"):
+                    be.train(st, sh, self._sel_local(nxt.sel), self.hp)
+                self._pre = (nxt.round, nxt)
+            a, epochs_all, rejected, auc_all = be.readback_wait(handle)
             if evaluate:
                 metrics = auc_all
         else:
@@ -441,6 +482,8 @@ class FederationEngine:
 
     # ------------------------------------------------------------------ resume (absent in the reference)
     def snapshot(self) -> Dict:
+        if self._pre is not None:
+            raise RuntimeError("a pipelined round is in flight (run_round(..., pipeline_next=True)); finish it first")
         return {"state": self.state.state_dict(), "agg_count_host": list(self.agg_count_host),
                 "py_random": random.getstate(), "np_random": np.random.get_state(),
                 "torch_random": torch.get_rng_state(), "rounds_done": len(self.history),

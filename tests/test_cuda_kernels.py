@@ -54,6 +54,23 @@ def test_train_kernel_matches_oracle(tiny_clients, tmp_path, dev, model_type, up
     assert torch.equal(e_gpu.state.params[1].cpu(), e_ref.state.params[1])
 
 
+@pytest.mark.parametrize("batch", [8, 32])
+def test_train_kernel_other_batch_sizes(tiny_clients, tmp_path, dev, batch):
+    """Batches below 12 rows run on the tensor-core variant with a partly filled M = 16 tile, batches of 13..32
+    rows on the all-FFMA variant; both against the oracle."""
+    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "hybrid", "avg", epoch=2, local_patience=5, batch_size=batch)
+    sel = [0, 3, 4]
+    ctl = RoundControl(0, sel, 0, [1.0] * 3, sel[0], -1)
+    e_gpu.backend.begin_round(ctl)
+    for e in (e_ref, e_gpu):
+        e.backend.train(e.state, e.sh, sel, e.hp)
+    torch.cuda.synchronize()
+    assert e_gpu.state.epochs_run.tolist() == e_ref.state.epochs_run.tolist()
+    assert e_gpu.state.adam_t.tolist() == e_ref.state.adam_t.tolist()
+    assert_close(e_gpu.state.params, e_ref.state.params, 2e-3, 2e-5, f"params, batch {batch}")
+    assert_close(e_gpu.state.adam_v, e_ref.state.adam_v, 5e-3, 1e-9, f"adam v, batch {batch}")
+
+
 def test_train_early_stop_and_partial_batch(tiny_clients, tmp_path, dev):
     e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "hybrid", "avg", epoch=6, local_patience=1, lr_rate=0.05)
     sel = [1, 4]
@@ -237,6 +254,31 @@ def test_full_round_with_tensor_core_scoring(tiny_clients, tmp_path, dev):
         assert res_gpu.aggregator == res_ref.aggregator
         assert_close(e_gpu.state.params, e_ref.state.params, 3e-3, 3e-5, f"params r{r}")
         assert_close(torch.tensor(res_gpu.client_metrics), torch.tensor(res_ref.client_metrics), 0, 2e-3, "auc")
+
+
+def test_pipelined_rounds_match_plain_rounds(tiny_clients, tmp_path, dev):
+    """run_round(..., pipeline_next=True) enqueues the next round's upload + training before it reads its own
+    results back; the sequence of results and the final state must be identical to the plain loop."""
+    engines = []
+    for _ in range(2):
+        cfg = make_cfg(tmp_path, epoch=2, score_precision="tf32x3", num_participants=0.7)
+        random.seed(11); torch.manual_seed(11)
+        engines.append(make_engine(cfg, make_shards(tiny_clients, dev), "hybrid", "mse_avg", "cuda"))
+    plain, piped = engines
+    random.seed(21); torch.manual_seed(21)
+    res_plain = [plain.run_round(r, prefetch_next=True) for r in range(5)]
+    random.seed(21); torch.manual_seed(21)
+    res_piped = [piped.run_round(r, pipeline_next=r < 4) for r in range(5)]
+    assert piped._pre is None
+    for a, b in zip(res_plain, res_piped):
+        assert (a.selected, a.aggregator, a.epochs_run, a.samples) == (b.selected, b.aggregator, b.epochs_run, b.samples)
+        assert a.client_metrics == b.client_metrics
+        assert a.verification == b.verification
+    assert torch.equal(plain.state.params, piped.state.params)
+    assert torch.equal(plain.state.adam_m, piped.state.adam_m)
+    with pytest.raises(RuntimeError):
+        piped.run_round(5, pipeline_next=True)
+        piped.run_round(7)
 
 
 def test_staged_upload_swaps_shards_and_refreshes_residuals(tiny_clients, tmp_path, dev):

@@ -176,3 +176,21 @@ def test_streaming_data_update(tiny_clients, tmp_path):
     eng.update_local_data(train_x=new_train * 2.0)
     assert torch.equal(eng.sh.train.x, new_train * 2.0)
     assert len(eng.run_round(0).client_metrics) == 6
+
+
+def test_next_voter_decidability(tiny_clients, tmp_path):
+    """The pipelined round may build the next control block early only when this round's (still unknown)
+    aggregator cannot change who votes next."""
+    cfg = make_cfg(tmp_path, network_size=6, max_aggregation_threshold=3)
+    eng = make_engine(cfg, make_shards(tiny_clients), "hybrid", "mse_avg", "oracle")
+    cur, nxt = [0, 1, 2], [3, 1, 4]
+    eng.agg_count_host = [0, 0, 0, 0, 0, 0]
+    assert eng._voter_is_decided(nxt, cur)                 # plenty of clients under the quota
+    eng.agg_count_host = [0, 2, 0, 3, 3, 0]
+    assert not eng._voter_is_decided(nxt, cur)             # voter 3 needs client 1, who may reach the quota now
+    eng.agg_count_host = [0, 1, 0, 3, 3, 0]
+    assert eng._voter_is_decided(nxt, cur)                 # one more aggregation leaves client 1 under it
+    eng.agg_count_host = [0, 3, 0, 3, 3, 0]
+    assert eng._voter_is_decided(nxt, cur)                 # nobody can vote, whatever happens
+    eng.agg_count_host = [0, 2, 0, 3, 3, 0]
+    assert eng._voter_is_decided(nxt, [0, 2, 5])           # client 1 is not selected now: its count cannot move
