@@ -9,6 +9,7 @@ O(clients x steps x 40) launches and a host sync per step for the same round
 """
 from __future__ import annotations
 
+import types
 import ctypes as C
 from typing import TYPE_CHECKING, Dict, List, Optional, Sequence
 
@@ -357,6 +358,23 @@ class CudaBackend:
             lat = [host[sh.test.off_host[c]:sh.test.off_host[c + 1]].copy() for c in range(st.n_clients)]
         return self.auc, vals, lat
 
+    def evaluate_side(self, st, sh, model_type: str) -> None:
+        """Evaluation of the round on a side stream, from a snapshot of the parameters taken now (main
+        stream): the caller may enqueue the next round's local training right behind this call -- it only
+        keeps 62 of 148 SMs busy, the evaluation forwards fill the rest.  Results land in ``self.auc``;
+        fetch them with ``readback_async(..., side=True)``."""
+        if getattr(self, "_side", None) is None:
+            self._side = torch.cuda.Stream(device=self.device)
+            self._ev_snap, self._ev_pack = torch.cuda.Event(), torch.cuda.Event()
+            self._eval_params = torch.empty(st.params.shape, dtype=st.params.dtype, device=self.device)
+        main = torch.cuda.current_stream(self.device)
+        self._eval_params.copy_(st.params)
+        self._ev_snap.record(main)
+        with torch.cuda.stream(self._side):
+            self._side.wait_event(self._ev_snap)
+            proxy = types.SimpleNamespace(params=self._eval_params, n_clients=st.n_clients)
+            self.evaluate(proxy, sh, model_type, False, "AUC")
+
     # ------------------------------------------------------------------ gossip
     def gossip(self, st, sh, ctl: RoundControl, spec: MergeSpec, neigh: List[List[int]], rows=None) -> None:
         from ..parallel import topology
@@ -394,10 +412,12 @@ class CudaBackend:
         (aggregator position, epochs_run[N], rejected[N], auc[N] or None)."""
         return self.readback_wait(self.readback_async(st, agg_pos, with_auc))
 
-    def readback_async(self, st, agg_pos: Optional[torch.Tensor], with_auc: bool):
+    def readback_async(self, st, agg_pos: Optional[torch.Tensor], with_auc: bool, side: bool = False):
         """Enqueue the packing of the round's results and their D2H copy; returns a handle for
         ``readback_wait``.  More work (the next round's training) may be enqueued in between: the wait is on
-        an event recorded right behind the copy, not on the stream."""
+        an event recorded right behind the copy, not on the stream.  ``side``: the AUCs come from
+        ``evaluate_side``; what the next training overwrites (epochs, verdicts) is packed on the main stream
+        now, the rest on the side stream behind the evaluation."""
         C_, W = st.n_clients, self.comm.world
         if getattr(self, "_rb_dev", None) is None:
             cmax = C_
@@ -413,16 +433,23 @@ class CudaBackend:
         rb[0:2].copy_(agg_pos if agg_pos is not None else self.agg_pos.new_full((2,), -1))
         rb[2:2 + C_].copy_(st.epochs_run)
         rb[2 + cm:2 + cm + C_].copy_(st.rejected)
-        if with_auc:
-            rb[2 + 2 * cm:2 + 2 * cm + 2 * C_].view(torch.float64).copy_(self.auc[:C_])
-        if self.comm.is_dist:
-            import torch.distributed as dist
-            dist.all_gather_into_tensor(self._rb_all, rb, group=self.comm.group)
-            src = self._rb_all
-        else:
-            src = rb
-        self._rb_pin[:src.numel()].copy_(src, non_blocking=True)
-        self._rb_event.record(torch.cuda.current_stream(self.device))
+        main = torch.cuda.current_stream(self.device)
+        stream = main
+        if side:
+            self._ev_pack.record(main)
+            self._side.wait_event(self._ev_pack)
+            stream = self._side
+        with torch.cuda.stream(stream):
+            if with_auc:
+                rb[2 + 2 * cm:2 + 2 * cm + 2 * C_].view(torch.float64).copy_(self.auc[:C_])
+            if self.comm.is_dist:
+                import torch.distributed as dist
+                dist.all_gather_into_tensor(self._rb_all, rb, group=self.comm.group)
+                src = self._rb_all
+            else:
+                src = rb
+            self._rb_pin[:src.numel()].copy_(src, non_blocking=True)
+            self._rb_event.record(stream)
         return (with_auc, src.numel())
 
     def readback_wait(self, handle):

@@ -256,15 +256,25 @@ class FederationEngine:
             want_latents = cfg.write_latents and self.model_type == "hybrid"
         metrics: List[float] = []
         lat, auc64, auc_dev = None, None, None
+        if getattr(self, "_prefetch_next", False):
+            self.prefetch_control(ctl.round + 1)       # host work, overlaps with the kernels enqueued so far
+        pipelined = (getattr(self, "_pipeline_next", False) and hasattr(be, "readback_async")
+                     and self._voter_is_decided(self._prefetched[1], ctl.sel))
+        # pipelined rounds evaluate on a side stream from a parameter snapshot, concurrently with the next
+        # round's local training (which leaves more than half of the SMs idle)
+        side_eval = (pipelined and evaluate and not want_latents and cfg.metric == "AUC"
+                     and hasattr(be, "evaluate_side"))
         if evaluate:
             with tm.phase("evaluate"):
-                auc_dev, auc64, lat = be.evaluate(st, sh, self.model_type, want_latents, cfg.metric)
-        if getattr(self, "_prefetch_next", False):
-            self.prefetch_control(ctl.round + 1)       # overlaps with the kernels enqueued above
+                if side_eval:
+                    be.evaluate_side(st, sh, self.model_type)
+                else:
+                    auc_dev, auc64, lat = be.evaluate(st, sh, self.model_type, want_latents, cfg.metric)
         # ---- single readback of the round's results (global lists) ------------------------
         if hasattr(be, "readback") and (not evaluate or auc64 is None):
-            handle = be.readback_async(st, agg_pos, evaluate)
-            if getattr(self, "_pipeline_next", False) and self._voter_is_decided(self._prefetched[1], ctl.sel):
+            handle = be.readback_async(st, agg_pos, evaluate, side_eval) if side_eval else \
+                be.readback_async(st, agg_pos, evaluate)
+            if pipelined:
                 # the next round's upload and training go in behind this round's work, before the host blocks
                 self.commit_staged_data()
                 nxt = self.make_control(ctl.round + 1)
