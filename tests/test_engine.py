@@ -194,3 +194,18 @@ def test_next_voter_decidability(tiny_clients, tmp_path):
     assert eng._voter_is_decided(nxt, cur)                 # nobody can vote, whatever happens
     eng.agg_count_host = [0, 2, 0, 3, 3, 0]
     assert eng._voter_is_decided(nxt, [0, 2, 5])           # client 1 is not selected now: its count cannot move
+
+
+def test_pipeline_flag_is_harmless_without_a_device(tiny_clients, tmp_path):
+    """The oracle backend has no asynchronous read-back: pipeline_next must silently run the plain order."""
+    runs = []
+    for piped in (False, True):
+        cfg = make_cfg(tmp_path, epoch=1)
+        eng = make_engine(cfg, make_shards(tiny_clients), "hybrid", "mse_avg", "oracle")
+        random.seed(5); torch.manual_seed(5)
+        res = [eng.run_round(r, pipeline_next=piped and r < 2) for r in range(3)]
+        assert eng._pre is None
+        runs.append((res, eng.state.params.clone()))
+    for a, b in zip(runs[0][0], runs[1][0]):
+        assert (a.selected, a.aggregator, a.client_metrics) == (b.selected, b.aggregator, b.client_metrics)
+    assert torch.equal(runs[0][1], runs[1][1])
