@@ -37,8 +37,8 @@
 namespace fm {
 namespace tc {
 
-constexpr int NT_MM = 288;                 // warps 0-3: epilogue 1 (+ X -> TMEM), warps 4-7: epilogue 2, warp 8: TMA + MMA producer
-constexpr int PRODUCER_WARP = 8;
+constexpr int NT_MM = 320;                 // warps 0-3: epilogue 1 (+ X -> TMEM), 4-7: epilogue 2, 8: MMA issue, 9: TMA / bulk loads
+constexpr int PRODUCER_WARP = 8, LOADER_WARP = 9;
 constexpr int MM_TMEM_COLS = 512;
 constexpr int C_XHI = 0, C_XLO = 128, C_D1 = 256, C_A2LO = 320, C_D2 = 384;
 constexpr int MM_MAX_CHUNKS = 4;
@@ -173,30 +173,12 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned c
         // thread -- not the tensor pipe -- the bottleneck of v1..v4)
         if (elect_one()) {
             // This thread is a single warp with nothing to hide latency behind: every instruction costs ~4+ cycles.
-            // The loop body is therefore instantiated once per buffer parity (descriptors become base + immediate),
-            // the pair sequence is tracked with one look-ahead cursor, and the instrumentation is compiled out
-            // unless the caller asked for it (v6 spent ~700 instructions per pair here and was bound by them).
+            // It therefore does nothing but wait and issue MMAs (the operand loads live on the loader warp below); the
+            // loop body is instantiated once per buffer parity (descriptors become base + immediate) and the
+            // instrumentation is compiled out unless the caller asked for it.  v6 spent ~700 instructions per pair
+            // here, v7 ~650 (loads included), and both were bound by them rather than by the tensor pipe.
             using P0 = std::integral_constant<int, 0>;
             using P1 = std::integral_constant<int, 1>;
-            auto load_w1 = [&](int m, auto WB) {              // w1 image + tables of a pair into buffer WB
-                constexpr int wb = decltype(WB)::value;
-                const unsigned char* img = images + (size_t)m * IMG_BYTES;
-                mbar_expect_tx(&S.bar_w1[wb], W1BYTES);
-                bulk_load(S.w1[wb], img + IMG_W1, 16384, &S.bar_w1[wb]);
-                if (PREC == 3) bulk_load(S.w1lo[wb], img + IMG_W1LO, 16384, &S.bar_w1[wb]);
-            };
-            auto load_w4 = [&](int m, auto WB) {
-                constexpr int wb = decltype(WB)::value;
-                const unsigned char* img = images + (size_t)m * IMG_BYTES;
-                mbar_expect_tx(&S.bar_w4[wb], W4BYTES);
-                bulk_load(S.w4[wb], img + IMG_W4, 16384, &S.bar_w4[wb]);
-                if (PREC == 3) bulk_load(S.w4lo[wb], img + IMG_W4LO, 16384, &S.bar_w4[wb]);
-            };
-            auto load_x = [&](int tile) {
-                mbar_expect_tx(&S.bar_x, XBYTES);
-#pragma unroll
-                for (int kb = 0; kb < 4; ++kb) tma_load_2d(S.x + kb * XBLK, &xmap, kb * 32, tile * TROWS, &S.bar_x);
-            };
             const uint64_t dw1a = smem_desc_sw128(S.w1[0]), dw1b = smem_desc_sw128(S.w1[1]);
             const uint64_t dw1loa = smem_desc_sw128(S.w1lo[0]), dw1lob = smem_desc_sw128(S.w1lo[1]);
             const uint64_t dw4a = smem_desc_sw128(S.w4[0]), dw4b = smem_desc_sw128(S.w4[1]);
@@ -223,27 +205,13 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned c
             long long t_prev = TIMING ? clock64() : 0;
             const bool timing = TIMING && blockIdx.x == 0;
 #define MM_TICK(slot) do { if (TIMING && timing) { const long long now_ = clock64(); t_acc[slot] += now_ - t_prev; t_prev = now_; } } while (0)
-            // look-ahead state: unit of pair g (u0); existence / unit / model of pairs g+1 and g+2
+            // look-ahead state: unit of pair g (u0); existence / unit of pair g+1
             PairCursor cl = first_pair();
-            PairCursor cx = cl;
-            load_x(cx.tile); next_unit(cx);
             int u0 = cl.i;
-            load_w1(cl.m, P0{}); load_w4(cl.m, P0{});
             next_pair(cl);
             bool ok1 = cl.ok;
-            int u1 = cl.i, m1 = cl.m;
-            if (ok1) { load_w1(m1, P1{}); load_w4(m1, P1{}); next_pair(cl); }
-            bool ok2 = ok1 && cl.ok;
-            int u2 = cl.i, m2 = cl.m;
+            int u1 = cl.i;
             int g = 0, ut = 0;
-            // the staging buffer is refilled with the next unit's rows once group A has parked the current tile in
-            // TMEM and group B holds its rows in registers (bar_xfree); checked when that is known to have happened
-            int x_release_pending = 0, x_release_at = 1;
-            auto flush_x_release = [&]() {
-                mbar_wait(&S.bar_xfree, (uint32_t)(x_release_pending & 1));
-                if (cx.ok) { load_x(cx.tile); next_unit(cx); }
-                x_release_pending = -1;
-            };
             mbar_wait(&S.bar_xt, 0u);
             tc_fence_after();
             issue_mma1(P0{}, 0u);
@@ -252,11 +220,7 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned c
                 using PN = std::integral_constant<int, b ^ 1>;
                 const uint32_t ph2 = (uint32_t)((g >> 1) & 1);
                 if (ok1 && u1 != u0) {                          // group A parks the next tile in TMEM as soon as MMA 1 (g) retires
-                    if (x_release_pending >= 0) flush_x_release();      // (one-pair units: the next tile is not requested yet)
-                    MM_TICK(7);
                     ++ut;
-                    x_release_pending = ut;
-                    x_release_at = g + 2;
                     if (TIMING && timing && ut <= 4) dbg[16 + 4 * (ut - 1)] = (unsigned long long)clock64();
                     mbar_wait(&S.bar_xt, (uint32_t)(ut & 1));
                     tc_fence_after();
@@ -266,19 +230,12 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned c
                 // D1[b^1]: epilogue 1 (g-1) is done and MMA 2 (g-1), the reader of the h2 head kept there, was issued before
                 if (ok1) issue_mma1(PN{}, (uint32_t)(((g + 1) >> 1) & 1));
                 MM_TICK(0);
-                if (g >= 1) {                                   // MMA 2 (g-1) retired -> its w4 buffer takes the image of pair g+1
-                    mbar_wait(&S.bar_d2, (uint32_t)(b ^ 1));
-                    if (ok1) load_w4(m1, PN{});
-                }
-                MM_TICK(1);
-                mbar_wait(&S.bar_h2[b], ph2);                   // epilogue 1 (g) done: h2(g) in TMEM, w1 buffer b (tables) free
+                mbar_wait(&S.bar_h2[b], ph2);                   // epilogue 1 (g) done: h2(g) in TMEM
                 MM_TICK(2);
-                if (ok2) load_w1(m2, PB);
                 mbar_wait(&S.bar_w4[b], ph2);
                 MM_TICK(3);
                 if (g >= 1) mbar_wait(&S.bar_d2free, (uint32_t)(b ^ 1));   // epilogue 2 (g-1) holds D2 in registers
                 MM_TICK(4);
-                if (x_release_pending >= 0 && g >= x_release_at) flush_x_release();
                 tc_fence_after();
                 const uint32_t d2 = tmem + C_D2, a2 = tmem + C_D1 + 32 * b, a2lo = tmem + C_A2LO + 32 * b;
                 const uint64_t bw4 = b ? dw4b : dw4a, bw4lo = b ? dw4lob : dw4loa;
@@ -294,8 +251,8 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned c
                 tc_commit(&S.bar_d2);
                 MM_TICK(5);
                 const bool more = ok1;
-                u0 = u1; ok1 = ok2; u1 = u2; m1 = m2;
-                if (ok2) { next_pair(cl); ok2 = cl.ok; u2 = cl.i; m2 = cl.m; }
+                u0 = u1;
+                if (ok1) { next_pair(cl); ok1 = cl.ok; u1 = cl.i; }
                 ++g;
                 return more;
             };
@@ -304,6 +261,69 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned c
                 if (!body(P1{})) break;
             }
             if (TIMING && timing) for (int i = 0; i < 8; ++i) dbg[i] = (unsigned long long)t_acc[i];
+        }
+        __syncwarp();
+    } else if (warp == LOADER_WARP) {
+        // Operand traffic: the x tile of the next unit and the w1 / w4 images two pairs / one pair ahead.  Every buffer
+        // is refilled as soon as the barrier that proves its last reader done has completed; the MMA thread only ever
+        // waits for "landed" barriers.
+        if (elect_one()) {
+            auto load_w1 = [&](int m, int wb) {               // w1 image + tables of a pair
+                const unsigned char* img = images + (size_t)m * IMG_BYTES;
+                mbar_expect_tx(&S.bar_w1[wb], W1BYTES);
+                bulk_load(S.w1[wb], img + IMG_W1, 16384, &S.bar_w1[wb]);
+                if (PREC == 3) bulk_load(S.w1lo[wb], img + IMG_W1LO, 16384, &S.bar_w1[wb]);
+            };
+            auto load_w4 = [&](int m, int wb) {
+                const unsigned char* img = images + (size_t)m * IMG_BYTES;
+                mbar_expect_tx(&S.bar_w4[wb], W4BYTES);
+                bulk_load(S.w4[wb], img + IMG_W4, 16384, &S.bar_w4[wb]);
+                if (PREC == 3) bulk_load(S.w4lo[wb], img + IMG_W4LO, 16384, &S.bar_w4[wb]);
+            };
+            auto load_x = [&](int tile) {
+                mbar_expect_tx(&S.bar_x, XBYTES);
+#pragma unroll
+                for (int kb = 0; kb < 4; ++kb) tma_load_2d(S.x + kb * XBLK, &xmap, kb * 32, tile * TROWS, &S.bar_x);
+            };
+            // look-ahead state: unit of pair g (u0); existence / unit / model of pairs g+1 and g+2
+            PairCursor cl = first_pair();
+            PairCursor cx = cl;
+            load_x(cx.tile); next_unit(cx);
+            int u0 = cl.i;
+            load_w1(cl.m, 0); load_w4(cl.m, 0);
+            next_pair(cl);
+            bool ok1 = cl.ok;
+            int u1 = cl.i, m1 = cl.m;
+            if (ok1) { load_w1(m1, 1); load_w4(m1, 1); next_pair(cl); }
+            bool ok2 = ok1 && cl.ok;
+            int u2 = cl.i, m2 = cl.m;
+            // the staging buffer is refilled with the next unit's rows once group A has parked the current tile in
+            // TMEM and group B holds its rows in registers (bar_xfree); checked when that is known to have happened
+            int ut = 0, x_release_pending = 0, x_release_at = 2;
+            auto flush_x_release = [&]() {
+                mbar_wait(&S.bar_xfree, (uint32_t)(x_release_pending & 1));
+                if (cx.ok) { load_x(cx.tile); next_unit(cx); }
+                x_release_pending = -1;
+            };
+            for (int g = 0;; ++g) {
+                const int b = g & 1;
+                if (ok1 && u1 != u0) {                          // unit boundary ahead: group A needs the next tile staged
+                    if (x_release_pending >= 0) flush_x_release();      // (one-pair units: not requested yet)
+                    ++ut;
+                    x_release_pending = ut;
+                    x_release_at = g + 3;
+                }
+                if (g >= 1) {                                   // MMA 2 (g-1) retired -> its w4 buffer takes the image of pair g+1
+                    mbar_wait(&S.bar_d2, (uint32_t)(b ^ 1));
+                    if (ok1) load_w4(m1, b ^ 1);
+                    if (x_release_pending >= 0 && g >= x_release_at) flush_x_release();   // epilogue 2 (g-1) ran: B is in this unit
+                }
+                mbar_wait(&S.bar_h2[b], (uint32_t)((g >> 1) & 1));   // epilogue 1 (g) done: w1 buffer b (tables) is free
+                if (ok2) load_w1(m2, b);
+                if (!ok1) break;
+                u0 = u1; ok1 = ok2; u1 = u2; m1 = m2;
+                if (ok2) { next_pair(cl); ok2 = cl.ok; u2 = cl.i; m2 = cl.m; }
+            }
         }
         __syncwarp();
     } else {
@@ -370,24 +390,29 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned c
 #pragma unroll
                 for (int j = 0; j < H; ++j) h1[j] = fmaxf(__uint_as_float(v[j]) + T1(T_B1 + j), 0.f);
                 h1[27] = 0.f;
+                // 27 -> 7 -> 27 with packed FMAs (FFMA2): even / odd partial sums, 247 issue slots instead of 385
                 float z[8];
 #pragma unroll
                 for (int i = 0; i < Z; ++i) {
-                    float acc = T1(T_B2 + i);
+                    float2 acc = make_float2(T1(T_B2 + i), 0.f);
 #pragma unroll
                     for (int j4 = 0; j4 < 28; j4 += 4) {
                         const float4 w = T4(T_W2 + i * 28 + j4);
-                        acc = fmaf(h1[j4], w.x, fmaf(h1[j4 + 1], w.y, fmaf(h1[j4 + 2], w.z, fmaf(h1[j4 + 3], w.w, acc))));
+                        acc = ffma2(make_float2(h1[j4], h1[j4 + 1]), make_float2(w.x, w.y), acc);
+                        acc = ffma2(make_float2(h1[j4 + 2], h1[j4 + 3]), make_float2(w.z, w.w), acc);
                     }
-                    z[i] = acc;
+                    z[i] = acc.x + acc.y;
                 }
+                z[7] = 0.f;
 #pragma unroll
                 for (int j = 0; j < H; ++j) {
-                    const float4 wa = T4(T_W3 + j * 8), wb = T4(T_W3 + j * 8 + 4);
-                    float acc = T1(T_B3 + j);
-                    acc = fmaf(z[0], wa.x, fmaf(z[1], wa.y, fmaf(z[2], wa.z, fmaf(z[3], wa.w, acc))));
-                    acc = fmaf(z[4], wb.x, fmaf(z[5], wb.y, fmaf(z[6], wb.z, acc)));
-                    const float hv = fmaxf(acc, 0.f);
+                    const float4 wa = T4(T_W3 + j * 8), wb = T4(T_W3 + j * 8 + 4);     // w3[j][7] is a zero pad
+                    float2 acc = make_float2(T1(T_B3 + j), 0.f);
+                    acc = ffma2(make_float2(z[0], z[1]), make_float2(wa.x, wa.y), acc);
+                    acc = ffma2(make_float2(z[2], z[3]), make_float2(wa.z, wa.w), acc);
+                    acc = ffma2(make_float2(z[4], z[5]), make_float2(wb.x, wb.y), acc);
+                    acc = ffma2(make_float2(z[6], z[7]), make_float2(wb.z, wb.w), acc);
+                    const float hv = fmaxf(acc.x + acc.y, 0.f);
                     if (PREC == 3) { v[j] = trunc_tf32(hv); h1[j] = hv - __uint_as_float(v[j]); }
                     else v[j] = cvt_tf32(hv);
                 }

@@ -106,6 +106,18 @@ __device__ __forceinline__ void tmem_ld64(uint32_t taddr, uint32_t (&v0)[32], ui
                  : "memory");
 }
 
+// packed fp32 FMA (FFMA2 on sm_100): d = a * b + c on both halves, one issue slot
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+    unsigned long long ra, rb, rc, rd;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+    float2 d;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
+}
+
 // byte offset of element (row, k) inside a [rows x 32 floats] K-block with the 128-B swizzle
 __device__ __forceinline__ int sw128(int row, int k) {
     return row * 128 + ((((k >> 2) ^ (row & 7)) << 4) | ((k & 3) << 2));
