@@ -15,7 +15,8 @@
 //     measured in v4, where the producer's MMA-1 issue was the bottleneck of the kernel).
 //   * The fp32 tile also stays in shared memory (double buffered, TMA, 128-B swizzle) for the squared error.
 //   * Models arrive as pre-staged operand images (swizzled UMMA layouts, hi/lo split) that a prep kernel
-//     builds once per round; the producer thread pulls them with bulk async copies: the w1 image is double
+//     builds once per round; a loader warp pulls them with bulk async copies (the MMA-issuing warp only waits and
+//     issues: its instruction stream, not the tensor pipe, was the bottleneck when it also loaded): the w1 image is double
 //     buffered (image k+2 is requested when epilogue 1 of model k is done), the w4 image of model k is
 //     requested when MMA 2 of model k-1 has retired.
 //   * D1 is double buffered in TMEM; epilogue 1 writes the TF32 head of h2 back into the D1 columns it just
