@@ -13,12 +13,14 @@
 //     with tcgen05.st (2 x 128 columns).  GEMM 1 then runs in TS mode (A from TMEM) at the tensor-core floor
 //     (128 x 32 x 8 in ~16 cycles) instead of re-reading 4 KB of A from shared memory per MMA (~66 cycles
 //     measured in v4, where the producer's MMA-1 issue was the bottleneck of the kernel).
-//   * The fp32 tile also stays in shared memory (double buffered, TMA, 128-B swizzle) for the squared error.
-//   * Models arrive as pre-staged operand images (swizzled UMMA layouts, hi/lo split) that a prep kernel
-//     builds once per round; a loader warp pulls them with bulk async copies (the MMA-issuing warp only waits and
-//     issues: its instruction stream, not the tensor pipe, was the bottleneck when it also loaded): the w1 image is double
-//     buffered (image k+2 is requested when epilogue 1 of model k is done), the w4 image of model k is
-//     requested when MMA 2 of model k-1 has retired.
+//   * The fp32 tile passes through ONE shared-memory staging buffer (TMA, 128-B swizzle): the epilogue-1 warps park
+//     it in TMEM, each epilogue-2 thread copies its row into registers for the squared error, and the buffer is
+//     immediately refilled with the next unit's tile.
+//   * Models arrive as pre-staged operand images (swizzled UMMA layouts, hi/lo split) that a prep kernel builds once
+//     per round; a loader warp pulls them with bulk async copies (the MMA-issuing warp only waits and issues: its
+//     instruction stream, not the tensor pipe, was the bottleneck when it also loaded).  Both images are double
+//     buffered: w1 of model k+2 is requested when epilogue 1 of model k is done (its bias / bottleneck tables ride in
+//     the pad rows of that image), w4 of model k+1 when MMA 2 of model k-1 has retired.
 //   * D1 is double buffered in TMEM; epilogue 1 writes the TF32 head of h2 back into the D1 columns it just
 //     read (the tensor pipe runs MMAs in issue order, and MMA 1 (k+2) is issued after MMA 2 (k)), the
 //     remainder of h2 goes to its own double-buffered columns; D2 is single buffered and released by
