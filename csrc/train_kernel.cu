@@ -207,6 +207,39 @@ __device__ __forceinline__ void adam1(float& w, float& m, float& v, float anchor
     w = fmaf(-st.step_size, __fdividef(m, denom), w);
 }
 
+// ---- packed fp32 pairs (FFMA2 / FMUL2 / FADD2 on sm_100): two IEEE operations per issue slot, same rounding ------
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float a, float b) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ f32x2 bc2(float a) { return pk2(a, a); }
+__device__ __forceinline__ float2 up2(f32x2 r) { float2 d; asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(r)); return d; }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) { f32x2 d; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+
+// adam1 on two parameters at once: the same operations in the same order, packed
+__device__ __forceinline__ void adam2(float& w0, float& w1, float& m0, float& m1, float& v0, float& v1, float an0, float an1,
+                                      f32x2 g, const AdamStep& st, float& prox_acc) {
+    f32x2 w = pk2(w0, w1), m = pk2(m0, m1), v = pk2(v0, v1);
+    if (st.mu != 0.f) {
+        const f32x2 dl = sub2(w, pk2(an0, an1));
+        const float2 d = up2(dl);
+        prox_acc = fmaf(d.x, d.x, prox_acc);
+        prox_acc = fmaf(d.y, d.y, prox_acc);
+        g = fma2(bc2(2.f * st.mu), dl, g);
+    }
+    m = fma2(sub2(g, m), bc2(0.1f), m);
+    v = fma2(mul2(bc2(0.001f), g), g, mul2(v, bc2(0.999f)));
+    const float2 vv = up2(v);
+    float sq0, sq1;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq0) : "f"(vv.x));
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq1) : "f"(vv.y));
+    const float2 den = up2(fma2(pk2(sq0, sq1), bc2(st.inv_sqrt_bc2), bc2(1e-8f)));
+    const float2 mm = up2(m);
+    w = fma2(bc2(-st.step_size), pk2(__fdividef(mm.x, den.x), __fdividef(mm.y, den.y)), w);
+    const float2 ww = up2(w);
+    w0 = ww.x; w1 = ww.y; m0 = mm.x; m1 = mm.y; v0 = vv.x; v1 = vv.y;
+}
+
 __device__ __forceinline__ void adam_update(float* __restrict__ Ws, float* __restrict__ Ms, float* __restrict__ Vs,
                                             const float* __restrict__ As, int idx, float g, const AdamStep& st,
                                             float& prox_acc) {
@@ -286,9 +319,9 @@ __device__ __forceinline__ void wgrad_adam_tile(int item, const float* __restric
                                                 float (&m)[16], float (&v)[16], float& prox_acc) {
     const int nt = item / K4, kc = item - nt * K4;
     const int n0 = nt * 4, nvalid = min(4, N - n0);
-    float g[16];
+    f32x2 g[8];                                   // g[q * 2 + h]: row q of the tile, columns 2h, 2h + 1
 #pragma unroll
-    for (int i = 0; i < 16; ++i) g[i] = 0.f;
+    for (int i = 0; i < 8; ++i) g[i] = pk2(0.f, 0.f);
     const float* a = A + 4 * kc;
 #pragma unroll
     for (int b4 = 0; b4 < BT; b4 += 4) {
@@ -296,14 +329,15 @@ __device__ __forceinline__ void wgrad_adam_tile(int item, const float* __restric
         const float4 a1 = *reinterpret_cast<const float4*>(a + (b4 + 1) * AP);
         const float4 a2 = *reinterpret_cast<const float4*>(a + (b4 + 2) * AP);
         const float4 a3 = *reinterpret_cast<const float4*>(a + (b4 + 3) * AP);
+        const f32x2 a0l = pk2(a0.x, a0.y), a0h = pk2(a0.z, a0.w), a1l = pk2(a1.x, a1.y), a1h = pk2(a1.z, a1.w);
+        const f32x2 a2l = pk2(a2.x, a2.y), a2h = pk2(a2.z, a2.w), a3l = pk2(a3.x, a3.y), a3h = pk2(a3.z, a3.w);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             if (q < nvalid) {
                 const float4 gg = *reinterpret_cast<const float4*>(GT + (n0 + q) * BT + b4);
-                g[q * 4 + 0] = fmaf(gg.x, a0.x, fmaf(gg.y, a1.x, fmaf(gg.z, a2.x, fmaf(gg.w, a3.x, g[q * 4 + 0]))));
-                g[q * 4 + 1] = fmaf(gg.x, a0.y, fmaf(gg.y, a1.y, fmaf(gg.z, a2.y, fmaf(gg.w, a3.y, g[q * 4 + 1]))));
-                g[q * 4 + 2] = fmaf(gg.x, a0.z, fmaf(gg.y, a1.z, fmaf(gg.z, a2.z, fmaf(gg.w, a3.z, g[q * 4 + 2]))));
-                g[q * 4 + 3] = fmaf(gg.x, a0.w, fmaf(gg.y, a1.w, fmaf(gg.z, a2.w, fmaf(gg.w, a3.w, g[q * 4 + 3]))));
+                const f32x2 gx = bc2(gg.x), gy = bc2(gg.y), gz = bc2(gg.z), gw = bc2(gg.w);
+                g[q * 2 + 0] = fma2(gx, a0l, fma2(gy, a1l, fma2(gz, a2l, fma2(gw, a3l, g[q * 2 + 0]))));
+                g[q * 2 + 1] = fma2(gx, a0h, fma2(gy, a1h, fma2(gz, a2h, fma2(gw, a3h, g[q * 2 + 1]))));
             }
         }
     }
@@ -314,10 +348,8 @@ __device__ __forceinline__ void wgrad_adam_tile(int item, const float* __restric
             float4 w = *reinterpret_cast<float4*>(Ws + idx);
             float4 an = make_float4(0.f, 0.f, 0.f, 0.f);
             if (st.mu != 0.f) an = *reinterpret_cast<const float4*>(As + idx);
-            adam1(w.x, m[q * 4 + 0], v[q * 4 + 0], an.x, g[q * 4 + 0], st, prox_acc);
-            adam1(w.y, m[q * 4 + 1], v[q * 4 + 1], an.y, g[q * 4 + 1], st, prox_acc);
-            adam1(w.z, m[q * 4 + 2], v[q * 4 + 2], an.z, g[q * 4 + 2], st, prox_acc);
-            adam1(w.w, m[q * 4 + 3], v[q * 4 + 3], an.w, g[q * 4 + 3], st, prox_acc);
+            adam2(w.x, w.y, m[q * 4 + 0], m[q * 4 + 1], v[q * 4 + 0], v[q * 4 + 1], an.x, an.y, g[q * 2 + 0], st, prox_acc);
+            adam2(w.z, w.w, m[q * 4 + 2], m[q * 4 + 3], v[q * 4 + 2], v[q * 4 + 3], an.z, an.w, g[q * 2 + 1], st, prox_acc);
             *reinterpret_cast<float4*>(Ws + idx) = w;
             if (Wlo) *reinterpret_cast<float4*>(Wlo + idx) = make_float4(tf32_lo(w.x), tf32_lo(w.y), tf32_lo(w.z), tf32_lo(w.w));
         }
