@@ -22,4 +22,9 @@ sass: $(LIB)
 
 clean:
 	rm -rf build $(LIB)
-.PHONY: all clean sass
+.PHONY: all clean sass probes
+
+# micro-benchmarks of the tensor-core building blocks (results quoted in profiles/README.md and DESIGN.md)
+probes:
+	$(NVCC) $(ARCH) -O3 -std=c++17 -Icsrc scripts/mma_probe.cu -o build/mma_probe -lcuda
+	$(NVCC) $(ARCH) -O3 -std=c++17 scripts/mma_sync_probe.cu -o build/mma_sync_probe
