@@ -66,7 +66,7 @@ struct MmSmem {
     alignas(1024) unsigned char w1lo[2][LO ? 4 * W1BLK : 1024];
     alignas(1024) unsigned char w4[2][128 * 128];
     alignas(1024) unsigned char w4lo[2][LO ? 128 * 128 : 1024];
-    alignas(8) uint64_t bar_x, bar_xfree, bar_xt, bar_w1[2], bar_w4[2], bar_d1[2], bar_h2[2], bar_d2, bar_d2free;
+    alignas(8) uint64_t bar_x, bar_xfree, bar_xt, bar_w1[2], bar_w4[2], bar_d1[2], bar_h2[2], bar_d2[2], bar_d2free;
     uint32_t tmem_base;
 };
 
@@ -146,7 +146,7 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned c
     if (tid == 0) {
         mbar_init(&S.bar_x, 1); mbar_init(&S.bar_w1[0], 1); mbar_init(&S.bar_w1[1], 1);
         mbar_init(&S.bar_w4[0], 1); mbar_init(&S.bar_w4[1], 1); mbar_init(&S.bar_d1[0], 1); mbar_init(&S.bar_d1[1], 1);
-        mbar_init(&S.bar_d2, 1); mbar_init(&S.bar_h2[0], 128); mbar_init(&S.bar_h2[1], 128);
+        mbar_init(&S.bar_d2[0], 1); mbar_init(&S.bar_d2[1], 1); mbar_init(&S.bar_h2[0], 128); mbar_init(&S.bar_h2[1], 128);
         mbar_init(&S.bar_xfree, 256); mbar_init(&S.bar_xt, 128); mbar_init(&S.bar_d2free, 128);
         fence_mbar_init();
     }
@@ -166,7 +166,9 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned c
     // Pipeline (g = running pair index of this CTA, b = g & 1, ut = running unit index):
     //   tensor pipe order  ... MMA1(g+1) MMA2(g) MMA1(g+2) MMA2(g+1) ...
     //   epilogue 1 (g) starts when MMA1(g) retires, epilogue 2 (g) when MMA2(g) retires; the two run on different warps.
-    // Rule kept throughout: no waiter can fall two phases behind the mbarrier it waits on.
+    // Rule kept throughout: a parity wait only works if the waiter observes completion c of a barrier
+    // before completion c+1 happens.  For every (barrier, waiter) pair below, completion c+1 depends on work that the
+    // waiter itself releases after it has observed c -- by data dependency, not by timing.
     const bool has_work = first_pair().ok;      // false only when every unit of this CTA is an empty chunk
     if (!has_work) {
     } else if (warp == PRODUCER_WARP) {
@@ -251,7 +253,7 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned c
                         mma_ts(d2, a2lo + ks * 8, bd, IDESC2, 1u);
                     }
                 }
-                tc_commit(&S.bar_d2);
+                tc_commit(&S.bar_d2[b]);       // one barrier per parity: see the loader's wait
                 MM_TICK(5);
                 const bool more = ok1;
                 u0 = u1;
@@ -310,16 +312,18 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned c
             };
             for (int g = 0;; ++g) {
                 const int b = g & 1;
+                if (g >= 1) {                                   // MMA 2 (g-1) retired -> its w4 buffer takes the image of pair g+1
+                    // bar_d2 alternates with the pair parity: the next completion of THIS barrier is MMA 2 (g+1), which
+                    // needs the image requested right below -- so this thread cannot miss a phase, whatever the timing
+                    mbar_wait(&S.bar_d2[b ^ 1], (uint32_t)(((g - 1) >> 1) & 1));
+                    if (ok1) load_w4(m1, b ^ 1);
+                    if (x_release_pending >= 0 && g >= x_release_at) flush_x_release();   // epilogue 2 (g-2) ran: B is in this unit
+                }
                 if (ok1 && u1 != u0) {                          // unit boundary ahead: group A needs the next tile staged
-                    if (x_release_pending >= 0) flush_x_release();      // (one-pair units: not requested yet)
+                    if (x_release_pending >= 0) flush_x_release();      // (units shorter than three pairs: not requested yet)
                     ++ut;
                     x_release_pending = ut;
                     x_release_at = g + 3;
-                }
-                if (g >= 1) {                                   // MMA 2 (g-1) retired -> its w4 buffer takes the image of pair g+1
-                    mbar_wait(&S.bar_d2, (uint32_t)(b ^ 1));
-                    if (ok1) load_w4(m1, b ^ 1);
-                    if (x_release_pending >= 0 && g >= x_release_at) flush_x_release();   // epilogue 2 (g-1) ran: B is in this unit
                 }
                 mbar_wait(&S.bar_h2[b], (uint32_t)((g >> 1) & 1));   // epilogue 1 (g) done: w1 buffer b (tables) is free
                 if (ok2) load_w1(m2, b);
@@ -468,7 +472,7 @@ score_multi_tc_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned c
                     fresh = false;
                 }
                 if (timing) { const long long t1 = clock64(); tb[0] += t1 - t0; t0 = t1; }
-                mbar_wait(&S.bar_d2, (uint32_t)(g & 1));
+                mbar_wait(&S.bar_d2[g & 1], (uint32_t)((g >> 1) & 1));
                 tc_fence_after();
                 if (timing) { const long long t1 = clock64(); tb[1] += t1 - t0; t0 = t1; }
                 float sse = 0.f;
