@@ -15,7 +15,7 @@ from typing import Optional
 
 _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REPO_ROOT = os.path.dirname(_PKG)
-LIB_PATH = os.path.join(_PKG, "_C", "libfedmse_b200.so")
+LIB_PATH = os.environ.get("FEDMSE_B200_LIB") or os.path.join(_PKG, "_C", "libfedmse_b200.so")   # override: experiments
 _lib: Optional[C.CDLL] = None
 
 c_f32p = C.POINTER(C.c_float)
