@@ -310,6 +310,44 @@ __device__ __forceinline__ void wgrad_adam(int item0, const float* __restrict__ 
 }
 
 
+// ---- the "small" role of the update phase: W2, W3 and every bias on 64 threads -------------------------------
+// Measured: these two warps (one per SM sub-partition, nobody to hide latency behind) were the critical path of the
+// phase -- 3.0 k cycles on their own -- because the three per-layer loops ran strictly one after the other: every
+// Adam store to the weight array orders the next section's loads behind it.  Here all gradients are formed first
+// (reads only, independent chains), then all weights / moments are loaded, updated and stored.
+template <int BT>
+__device__ __forceinline__ float4 wgrad_quad(const float* __restrict__ gt, const float* __restrict__ a, int AP) {
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);        // g[c] = sum_b gt[b] * a[b][c]
+#pragma unroll
+    for (int b4 = 0; b4 < BT; b4 += 4) {
+        const float4 gg = *reinterpret_cast<const float4*>(gt + b4);
+        const float4 a0 = *reinterpret_cast<const float4*>(a + (b4 + 0) * AP);
+        const float4 a1 = *reinterpret_cast<const float4*>(a + (b4 + 1) * AP);
+        const float4 a2 = *reinterpret_cast<const float4*>(a + (b4 + 2) * AP);
+        const float4 a3 = *reinterpret_cast<const float4*>(a + (b4 + 3) * AP);
+        g.x = fmaf(gg.x, a0.x, fmaf(gg.y, a1.x, fmaf(gg.z, a2.x, fmaf(gg.w, a3.x, g.x))));
+        g.y = fmaf(gg.x, a0.y, fmaf(gg.y, a1.y, fmaf(gg.z, a2.y, fmaf(gg.w, a3.y, g.y))));
+        g.z = fmaf(gg.x, a0.z, fmaf(gg.y, a1.z, fmaf(gg.z, a2.z, fmaf(gg.w, a3.z, g.z))));
+        g.w = fmaf(gg.x, a0.w, fmaf(gg.y, a1.w, fmaf(gg.z, a2.w, fmaf(gg.w, a3.w, g.w))));
+    }
+    return g;
+}
+template <int BT>
+__device__ __forceinline__ float row_sum(const float* __restrict__ gt) {
+    float acc = 0.f;
+#pragma unroll
+    for (int b4 = 0; b4 < BT; b4 += 4) {
+        const float4 gg = *reinterpret_cast<const float4*>(gt + b4);
+        acc += (gg.x + gg.y) + (gg.z + gg.w);
+    }
+    return acc;
+}
+template <int BT, int N>
+__device__ __forceinline__ float4 bias_quad(const float* __restrict__ GT, int n0) {
+    return make_float4(n0 + 0 < N ? row_sum<BT>(GT + (n0 + 0) * BT) : 0.f, n0 + 1 < N ? row_sum<BT>(GT + (n0 + 1) * BT) : 0.f,
+                       n0 + 2 < N ? row_sum<BT>(GT + (n0 + 2) * BT) : 0.f, n0 + 3 < N ? row_sum<BT>(GT + (n0 + 3) * BT) : 0.f);
+}
+
 // Weight gradient + Adam for a 4(n) x 4(k) register tile of one big matrix (W1 or W4).  The thread owns
 // these 16 parameters for the whole kernel: their Adam moments stay in registers (m, v), the activations
 // are read once per tile instead of once per output feature, and the weights are touched once per step.
@@ -804,19 +842,51 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
                     if (tid - ROLE_W4 < W4_TILES)
                         wgrad_adam_tile<BT, D, 7>(tid - ROLE_W4, S.dxT, S.h2, SM::HP, S_W4, W4P, S.W, MMA ? S.Wlo : nullptr, As, st, tm, tv, prox_acc);
                 } else {
-                    constexpr int NS = NT - ROLE_SMALL;
+                    static_assert(NT - ROLE_SMALL == 64 && H * 2 + 7 <= 64 && Z * 7 + 2 <= 64 && H + D <= 3 * 64, "small-role item map");
                     const int t0 = tid - ROLE_SMALL;
-                    wgrad_adam<BT, H, Z, 2, NS>(t0, S.dp2T, S.z, SM::ZP, S_W3, W3P, S_B3, S.W, S.M, S.V, As, st, prox_acc);
-                    wgrad_adam<BT, Z, H, 7, NS>(t0, S.dzT, S.h1, SM::HP, S_W2, W2P, S_B2, S.W, S.M, S.V, As, st, prox_acc);
-                    // biases of the two big layers (their weight tiles live in registers of other threads)
-                    for (int n = t0; n < H + D; n += NS) {
-                        const bool first = n < H;
-                        const float* gt = first ? S.dp1T + n * BT : S.dxT + (n - H) * BT;
-                        float gsum = 0.f;
-#pragma unroll
-                        for (int bb = 0; bb < BT; ++bb) gsum += gt[bb];
-                        adam_update(S.W, S.M, S.V, As, first ? S_B1 + n : S_B4 + (n - H), gsum, st, prox_acc);
+                    // -- gradients of this thread's W3 (+ b3) item and W2 (+ b2) item
+                    float4 gA = make_float4(0.f, 0.f, 0.f, 0.f), gB = gA;
+                    int iA = -1, iB = -1;
+                    if (t0 < H * 2) { const int n = t0 >> 1, kc = t0 & 1; gA = wgrad_quad<BT>(S.dp2T + n * BT, S.z + 4 * kc, SM::ZP); iA = S_W3 + n * W3P + 4 * kc; }
+                    else if (t0 < H * 2 + 7) { const int n0 = (t0 - H * 2) * 4; gA = bias_quad<BT, H>(S.dp2T, n0); iA = S_B3 + n0; }
+                    if (t0 < Z * 7) { const int n = t0 / 7, kc = t0 - 7 * n; gB = wgrad_quad<BT>(S.dzT + n * BT, S.h1 + 4 * kc, SM::HP); iB = S_W2 + n * W2P + 4 * kc; }
+                    else if (t0 < Z * 7 + 2) { const int n0 = (t0 - Z * 7) * 4; gB = bias_quad<BT, Z>(S.dzT, n0); iB = S_B2 + n0; }
+                    // -- loads, Adam, stores (distinct addresses; grouped so that no load waits behind a store)
+                    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    const int jA = iA < 0 ? 0 : iA, jB = iB < 0 ? 0 : iB;
+                    float4 wA = *reinterpret_cast<float4*>(S.W + jA), mA = *reinterpret_cast<float4*>(S.M + jA), vA = *reinterpret_cast<float4*>(S.V + jA);
+                    float4 wB = *reinterpret_cast<float4*>(S.W + jB), mB = *reinterpret_cast<float4*>(S.M + jB), vB = *reinterpret_cast<float4*>(S.V + jB);
+                    float4 aA = z4, aB = z4;
+                    if (prox) { aA = *reinterpret_cast<const float4*>(As + jA); aB = *reinterpret_cast<const float4*>(As + jB); }
+                    if (iA >= 0) {
+                        adam1(wA.x, mA.x, vA.x, aA.x, gA.x, st, prox_acc); adam1(wA.y, mA.y, vA.y, aA.y, gA.y, st, prox_acc);
+                        adam1(wA.z, mA.z, vA.z, aA.z, gA.z, st, prox_acc); adam1(wA.w, mA.w, vA.w, aA.w, gA.w, st, prox_acc);
                     }
+                    if (iB >= 0) {
+                        adam1(wB.x, mB.x, vB.x, aB.x, gB.x, st, prox_acc); adam1(wB.y, mB.y, vB.y, aB.y, gB.y, st, prox_acc);
+                        adam1(wB.z, mB.z, vB.z, aB.z, gB.z, st, prox_acc); adam1(wB.w, mB.w, vB.w, aB.w, gB.w, st, prox_acc);
+                    }
+                    if (iA >= 0) { *reinterpret_cast<float4*>(S.W + iA) = wA; *reinterpret_cast<float4*>(S.M + iA) = mA; *reinterpret_cast<float4*>(S.V + iA) = vA; }
+                    if (iB >= 0) { *reinterpret_cast<float4*>(S.W + iB) = wB; *reinterpret_cast<float4*>(S.M + iB) = mB; *reinterpret_cast<float4*>(S.V + iB) = vB; }
+                    // -- up to three biases of the two big layers as a second, short stage (keeps the register peak down)
+                    int iC[3];
+                    float gC[3], wC[3], mC[3], vC[3], aC[3];
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) {
+                        const int n = t0 + 64 * i;
+                        iC[i] = -1; gC[i] = 0.f;
+                        if (n < H) { gC[i] = row_sum<BT>(S.dp1T + n * BT); iC[i] = S_B1 + n; }
+                        else if (n < H + D) { gC[i] = row_sum<BT>(S.dxT + (n - H) * BT); iC[i] = S_B4 + (n - H); }
+                    }
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) {
+                        const int j = iC[i] < 0 ? 0 : iC[i];
+                        wC[i] = S.W[j]; mC[i] = S.M[j]; vC[i] = S.V[j]; aC[i] = prox ? As[j] : 0.f;
+                    }
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) if (iC[i] >= 0) adam1(wC[i], mC[i], vC[i], aC[i], gC[i], st, prox_acc);
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) if (iC[i] >= 0) { S.W[iC[i]] = wC[i]; S.M[iC[i]] = mC[i]; S.V[iC[i]] = vC[i]; }
                 }
                 if (prox) loss_acc = fmaf(a.fedprox_mu, prox_acc, loss_acc);
             }
