@@ -31,5 +31,5 @@ print("mma.sync tf32 -> HMMA.1688.F32.TF32, ldmatrix -> LDSM, setmaxnreg -> USET
 for f, c in counts.items():
     name = subprocess.run(["c++filt", f], capture_output=True, text=True).stdout.strip()
     sel = {k: v for k, v in c.items() if k.startswith(("UTC", "UTMA", "UBLK", "LDTM", "STTM", "SYNCS", "RED", "HMMA", "LDSM", "USETMAXREG", "LDG.E.STRONG"))
-           or k in ("FFMA", "LDS.128", "BAR", "SHFL", "MUFU")}
+           or k in ("FFMA", "FFMA2", "FMUL2", "FADD2", "LDS.128", "BAR", "SHFL", "MUFU")}
     print(f"{name[:120]}\n    {sum(c.values())} instructions: " + ", ".join(f"{k} {v}" for k, v in sorted(sel.items(), key=lambda kv: -kv[1])))
