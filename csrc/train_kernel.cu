@@ -787,6 +787,16 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
                     *reinterpret_cast<float2*>(pp + 8) = make_float2(c1.sum(0), c1.sum(1));
                     *reinterpret_cast<float2*>(pp + 8 * 32) = make_float2(c0.sum(2), c0.sum(3));
                     *reinterpret_cast<float2*>(pp + 8 * 32 + 8) = make_float2(c1.sum(2), c1.sum(3));
+                } else if (tid - 256 < D) {
+                    // idle in this phase: the output-layer bias gradient is complete (dxT) and nobody reads b4 before the
+                    // next step, so its Adam update leaves the two "small" warps that bound the update phase (one bias
+                    // per thread on warps 8-11: short enough to hide behind the MMAs of warps 0-7)
+                    AdamStep st;
+                    st.step_size = S.sctab[2 * (ts & 31)]; st.inv_sqrt_bc2 = S.sctab[2 * (ts & 31) + 1]; st.mu = a.fedprox_mu;
+                    float prox_b4 = 0.f;
+                    const int n = tid - 256;
+                    adam_update(S.W, S.M, S.V, As, S_B4 + n, row_sum<BT>(S.dxT + n * BT), st, prox_b4);
+                    if (prox) loss_acc = fmaf(a.fedprox_mu, prox_b4, loss_acc);
                 }
             } else {
                 layer_dgrad<BT, D, H, 4, true>(S.dxT, S.W + S_W4, W4P, S.h2, SM::HP, S.dp2T);
@@ -868,15 +878,19 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
                     }
                     if (iA >= 0) { *reinterpret_cast<float4*>(S.W + iA) = wA; *reinterpret_cast<float4*>(S.M + iA) = mA; *reinterpret_cast<float4*>(S.V + iA) = vA; }
                     if (iB >= 0) { *reinterpret_cast<float4*>(S.W + iB) = wB; *reinterpret_cast<float4*>(S.M + iB) = mB; *reinterpret_cast<float4*>(S.V + iB) = vB; }
-                    // -- up to three biases of the two big layers as a second, short stage (keeps the register peak down)
+                    // -- biases of the two big layers as a second, short stage (keeps the register peak down); with the
+                    //    tensor-core variant b4 was already updated by idle warps of the data-gradient phase
+                    constexpr int NC = MMA ? 1 : 3;
                     int iC[3];
                     float gC[3], wC[3], mC[3], vC[3], aC[3];
 #pragma unroll
                     for (int i = 0; i < 3; ++i) {
                         const int n = t0 + 64 * i;
                         iC[i] = -1; gC[i] = 0.f;
-                        if (n < H) { gC[i] = row_sum<BT>(S.dp1T + n * BT); iC[i] = S_B1 + n; }
-                        else if (n < H + D) { gC[i] = row_sum<BT>(S.dxT + (n - H) * BT); iC[i] = S_B4 + (n - H); }
+                        if (i < NC) {
+                            if (n < H) { gC[i] = row_sum<BT>(S.dp1T + n * BT); iC[i] = S_B1 + n; }
+                            else if (!MMA && n < H + D) { gC[i] = row_sum<BT>(S.dxT + (n - H) * BT); iC[i] = S_B4 + (n - H); }
+                        }
                     }
 #pragma unroll
                     for (int i = 0; i < 3; ++i) {
