@@ -33,11 +33,66 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 REF_DIR = os.path.join(HERE, "_ref")
 
 
+REF_SRC = os.environ.get("FEDMSE_REFERENCE_SRC", "/root/reference")
+_REF_PKGS = ("Model", "Trainer", "Evaluator", "DataLoader", "Utils")
+
+
+def _installed() -> bool:
+    return all(os.path.isfile(os.path.join(REF_DIR, p, "__init__.py")) for p in _REF_PKGS)
+
+
+def ensure_installed(verbose: bool = False) -> str:
+    """Idempotent offline install of the unmodified reference into ``baseline/_ref``.
+
+    Order: (1) already there -> nothing to do; (2) ``baseline/install_reference.sh`` (the pip route recorded in
+    DESIGN.md section 5); (3) if pip fails, a verbatim file copy of the reference's python packages.  Returns ''
+    on success, else the reason.  ``__graft_entry__.build()`` and ``bench.py --impl reference`` both call this, so a
+    fresh checkout (``baseline/_ref`` is git-ignored) gets the reference arm without a manual step."""
+    if _installed():
+        return ""
+    src = os.path.join(REF_SRC, "src")
+    if not os.path.isdir(os.path.join(src, "Trainer")):
+        return f"baseline/_ref missing and no reference source at {REF_SRC}"
+    import subprocess
+    why = ""
+    try:
+        r = subprocess.run(["bash", os.path.join(HERE, "install_reference.sh"), REF_SRC], capture_output=True,
+                           text=True, timeout=600)
+        if r.returncode != 0:
+            why = (r.stderr or r.stdout).strip().splitlines()[-1:] or ["pip install failed"]
+            why = str(why[0])[:200]
+        if verbose:
+            print(r.stdout[-2000:], r.stderr[-2000:])
+    except Exception as e:                                   # no bash / pip / timeout
+        why = repr(e)[:200]
+    if not _installed():                                     # fallback: plain copy of the same files
+        try:
+            os.makedirs(REF_DIR, exist_ok=True)
+            for pkg in _REF_PKGS:
+                dst = os.path.join(REF_DIR, pkg)
+                os.makedirs(dst, exist_ok=True)
+                for f in os.listdir(os.path.join(src, pkg)):
+                    if f.endswith(".py") and f != "spliter.py":      # spliter.py is a C comment block, not python
+                        shutil.copyfile(os.path.join(src, pkg, f), os.path.join(dst, f))
+            shutil.copyfile(os.path.join(src, "main.py"), os.path.join(REF_DIR, "fedmse_reference_main.py"))
+            with open(os.path.join(REF_DIR, "INSTALL_NOTE.txt"), "w") as fh:
+                fh.write(f"plain copy of {src} (pip route failed: {why})\n")
+        except Exception as e:
+            return f"baseline/_ref install failed: {why}; copy failed: {e!r}"
+    return "" if _installed() else f"baseline/_ref install failed: {why}"
+
+
 def available() -> str:
-    """'' when the reference install is usable, else the reason."""
-    if not os.path.isdir(os.path.join(REF_DIR, "Trainer")):
-        return "baseline/_ref missing (run baseline/install_reference.sh)"
-    return ""
+    """'' when the reference install is usable (installing it first if needed), else the reason."""
+    if int(os.environ.get("LOCAL_RANK", "0")) != 0 and not _installed():
+        # torchrun: local rank 0 installs, the others wait for it (or for its verdict that it cannot)
+        src_ok = os.path.isdir(os.path.join(REF_SRC, "src", "Trainer"))
+        t0 = time.time()
+        while src_ok and not _installed() and time.time() - t0 < 180:
+            time.sleep(1.0)
+        time.sleep(1.0)
+        return "" if _installed() else "baseline/_ref missing (local rank 0 could not install it)"
+    return ensure_installed()
 
 
 def _import_ref():
