@@ -925,7 +925,10 @@ __global__ void __launch_bounds__(NT, 1) train_clients_kernel(const FmTrainArgs 
         }
         epochs_done = e + 1;
         bool stop = false;
-        if (valid_loss < min_valid) {      // uniform across the block: every thread holds the same value
+        if (nbv == 0) {
+            // no validation rows = the reference's run(train_loader, valid_loader=None): all epochs, no early
+            // stop, no best-epoch snapshot (client_trainer.py:387 guards the whole block with `if valid_loader`)
+        } else if (valid_loss < min_valid) {      // uniform across the block: every thread holds the same value
             min_valid = valid_loss; worse = 0;
             float* gb = a.best + (size_t)c * P_PAD;
             for (int p = tid; p < NP; p += NT) gb[p] = S.W[sidx(p)];

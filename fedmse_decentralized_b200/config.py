@@ -62,7 +62,8 @@ class ExperimentConfig:
     data_root: Optional[str] = None       # overrides the scenario's data_path
     synthetic_clients: int = 0            # >0: ignore config_file, generate this many clients
     synthetic_spec: str = "nbaiot"        # "nbaiot" | "kitsune"
-    score_precision: str = "fp32"         # "fp32" (exact FFMA) | "tf32" (tcgen05 scoring forward)
+    score_precision: str = "fp32"         # "fp32" (exact FFMA) | "tf32" | "tf32x3" | "bf16x3" (tcgen05 scoring forwards)
+    fusion_rows: int = 512                # fusion_avg: dev rows used for the KDE / JS-distance weights
     log_level: str = "INFO"
 
     def __post_init__(self):
@@ -76,7 +77,7 @@ class ExperimentConfig:
         if self.verification_method not in ("val", "dev"):
             raise ValueError("verification_method must be 'val' or 'dev'")
         for u in self.update_types:
-            if u not in ("avg", "fedprox", "mse_avg"):
+            if u not in ("avg", "fedprox", "mse_avg", "fusion_avg"):
                 raise ValueError(f"unknown update type {u!r}")
         for m in self.model_types:
             if m not in ("hybrid", "autoencoder"):

@@ -114,6 +114,18 @@ class OracleBackend:
                 out[pos] = oracle.chunked_mse(st.params[g - sh.first_client], sh.dev, self.layout, 0)
         return out
 
+    def fusion_scores(self, st: FederationState, sh: ShardStore, ctl: RoundControl, max_rows: int
+                      ) -> torch.Tensor:
+        """``fusion_avg``: JS distance between the KDE densities of the dev rows and of each selected model's
+        reconstruction of them (``utils.similarity.fusion_distances``); owned positions only, like the MSE."""
+        from ..utils.similarity import fusion_distances
+        out = torch.zeros(len(ctl.sel), dtype=torch.float32, device=st.device)
+        own = [(pos, g - sh.first_client) for pos, g in enumerate(ctl.sel) if self._owned(sh, g)]
+        if own:
+            d = fusion_distances(st.params[[c for _, c in own]], sh.dev, self.layout, max_rows)
+            out[[pos for pos, _ in own]] = d
+        return out
+
     def merge(self, st: FederationState, sh: ShardStore, ctl: RoundControl, spec: MergeSpec,
               mse: Optional[torch.Tensor], agg_pos: torch.Tensor, rows: Optional[torch.Tensor] = None
               ) -> torch.Tensor:
@@ -124,7 +136,8 @@ class OracleBackend:
         if a < 0:
             return theta
         n = len(ctl.sel)
-        w = oracle.merge_weights(spec.update_type, mse, n, a, spec.compat_alias, st.device)
+        kind = "mse_avg" if spec.update_type == "fusion_avg" else spec.update_type   # weights = (1/d_j) normalised
+        w = oracle.merge_weights(kind, mse, n, a, spec.compat_alias, st.device)
         if rows is None:
             rows = st.params[[g - sh.first_client for g in ctl.sel]]
         theta = oracle.weighted_reduce(rows, range(n), w)
@@ -203,7 +216,11 @@ class OracleBackend:
             c = g - sh.first_client
             cand = [g] + [j for j in neigh[g] if j != g]
             V = sh.valid.rows(g)
-            if spec.update_type == "mse_avg":
+            if spec.update_type == "fusion_avg":
+                from ..utils.similarity import fusion_distances
+                dist_ = fusion_distances(src[[j - base for j in cand]], V, self.layout)
+                w = oracle.merge_weights("mse_avg", dist_, len(cand), device=st.device)
+            elif spec.update_type == "mse_avg":
                 mse = torch.stack([oracle.chunked_mse(src[j - base], V, self.layout, 0) for j in cand])
                 w = oracle.merge_weights("mse_avg", mse, len(cand), device=st.device)
             else:

@@ -284,10 +284,27 @@ class CudaBackend:
             return self._publish(self.mse, n, 1)
         return self.mse[:n]
 
+    def fusion_scores(self, st, sh, ctl: RoundControl, max_rows: int) -> torch.Tensor:
+        """``fusion_avg`` weights (the reference's orphaned KDE / Jensen-Shannon similarity): batched
+        torch GEMM + logsumexp on the device (a library path by design: O(n_sel x rows^2 x 115) on <= 512 rows);
+        the distances then ride the same board exchange and merge kernel as the MSE scores."""
+        from ..utils.similarity import fusion_distances
+        n = len(ctl.sel)
+        f, C_ = sh.first_client, st.n_clients
+        own = [(pos, g - f) for pos, g in enumerate(ctl.sel) if f <= g < f + C_]
+        self.mse.zero_()
+        if own:
+            d = fusion_distances(st.params[[c for _, c in own]], sh.dev, self.layout, max_rows)
+            self.mse[torch.tensor([pos for pos, _ in own], device=self.device)] = d
+        if self.exchanges_scores:
+            return self._publish(self.mse, n, 1)
+        return self.mse[:n]
+
     def merge(self, st, sh, ctl: RoundControl, spec: MergeSpec, mse, agg_pos, rows=None) -> torch.Tensor:
         n = len(ctl.sel)
         a = _lib.FmMergeArgs(_ptr(self.peer_table), self.comm.world, self.comm.rank, sh.n_global,
-                             _ptr(self.ctl_sel), n, _ptr(mse), 1 if spec.update_type == "mse_avg" else 0,
+                             _ptr(self.ctl_sel), n, _ptr(mse),
+                             1 if spec.update_type in ("mse_avg", "fusion_avg") else 0,
                              1 if spec.compat_alias else 0, _ptr(agg_pos), _ptr(st.agg_count), _ptr(self.theta),
                              _ptr(self.weights), 0, 0, 0, 0)
         if self.exchanges_scores:

@@ -102,6 +102,8 @@ def train_client(params: torch.Tensor, m: torch.Tensor, v: torch.Tensor, t: int,
                 vb += 1
         valid_loss = vt / vb if vb else float("nan")
         log.append((train_loss, valid_loss))
+        if vb == 0:
+            continue          # run(train_loader, valid_loader=None): all epochs, no early stop, nothing saved
         if valid_loss < min_valid:
             min_valid, worse = valid_loss, 0
             best.copy_(w)

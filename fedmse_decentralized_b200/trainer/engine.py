@@ -241,6 +241,10 @@ class FederationEngine:
                     mse = be.merge_scores(st, sh, ctl)
                     if not getattr(be, "exchanges_scores", False):
                         mse = cm.sum_(mse)
+                elif self.update_type == "fusion_avg":
+                    mse = be.fusion_scores(st, sh, ctl, self.cfg.fusion_rows)
+                    if not getattr(be, "exchanges_scores", False):
+                        mse = cm.sum_(mse)
                 rows = None
                 if cm.is_dist and not getattr(be, "reads_peers", False):
                     rows = cm.gather_rows(st.params, ctl.sel, self.first)

@@ -78,3 +78,54 @@ def fusion_weights(dev_kde_scores, generated_sets, device=None) -> np.ndarray:
     d = np.array([similarity_score(dev_kde_scores, g, device) for g in generated_sets])
     w = 1.0 / (d + 1e-12)
     return w / w.sum()
+
+
+# --------------------------------------------------------------------------- fusion_avg as a live merge rule
+def _js_distance_from_logs(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """``jensenshannon(exp(a), exp(b))`` for log-score vectors, batched over leading dims of ``b``.
+
+    scipy normalises both vectors to sum 1 first, so only ``softmax`` of the log-scores matters; computing it
+    as a softmax keeps 115-dimensional KDE log-densities (hundreds of nats below zero) from underflowing."""
+    p = torch.softmax(a, dim=-1)
+    q = torch.softmax(b, dim=-1)
+    m = 0.5 * (p + q)
+
+    def rel(x, y):
+        t = torch.where(x > 0, x * (torch.log(x.clamp_min(1e-300)) - torch.log(y.clamp_min(1e-300))),
+                        torch.zeros_like(x))
+        return t.sum(-1)
+
+    return torch.sqrt((0.5 * rel(p, m) + 0.5 * rel(q, m)).clamp_min(0))
+
+
+def _kde_self_log_density_t(X: torch.Tensor) -> torch.Tensor:
+    """Batched ``kde_self_log_density`` on tensors ``[..., n, d]`` (float64, Scott bandwidth)."""
+    n, d = X.shape[-2], X.shape[-1]
+    h = scott_bandwidth(n, d)
+    log_norm = -0.5 * d * math.log(2 * math.pi) - d * math.log(h) - math.log(n)
+    sq = (X * X).sum(-1)
+    d2 = (sq[..., :, None] + sq[..., None, :] - 2.0 * X @ X.transpose(-1, -2)).clamp_min_(0)
+    return torch.logsumexp(-0.5 * d2 / (h * h), dim=-1) + log_norm
+
+
+def fusion_distances(rows: torch.Tensor, dev: torch.Tensor, layout, max_rows: int = 512,
+                     model_block: int = 16) -> torch.Tensor:
+    """Per-model ``similarity_score`` for the ``fusion_avg`` merge rule, on the tensors' device.
+
+    The source of ``GlobalAggregator.fusion_avg`` was deleted from the reference; what survives is its weight
+    function (``src/Utils/utils.py:10-24``) and the names in the leftover bytecode.  Here the
+    "generated data set" of client j is the dev set as *reconstructed by client j's autoencoder* (same number
+    of points as the dev set, which ``jensenshannon`` needs), and the score is the JS distance between the KDE
+    self-densities of the dev rows and of that reconstruction.  ``max_rows`` caps the O(n^2 d) pairwise work by
+    using the first rows of the (already shuffled) dev matrix.  Returns ``[len(rows)]`` float32 distances; the
+    merge weight is ``(1/d_j) / sum_k (1/d_k)`` (``fusion_weights``)."""
+    from ..ops import oracle
+    D = layout.dim
+    X = dev[:max_rows, :D].to(torch.float32)
+    ref = _kde_self_log_density_t(X.to(torch.float64))
+    out = torch.empty(rows.shape[0], dtype=torch.float32, device=rows.device)
+    for s in range(0, rows.shape[0], model_block):
+        rec = torch.stack([oracle.forward(r, X, layout)[1] for r in rows[s:s + model_block]])
+        dens = _kde_self_log_density_t(rec.to(torch.float64))
+        out[s:s + model_block] = _js_distance_from_logs(ref, dens).to(torch.float32) + 1e-12
+    return out

@@ -209,3 +209,27 @@ def test_pipeline_flag_is_harmless_without_a_device(tiny_clients, tmp_path):
     for a, b in zip(runs[0][0], runs[1][0]):
         assert (a.selected, a.aggregator, a.client_metrics) == (b.selected, b.aggregator, b.client_metrics)
     assert torch.equal(runs[0][1], runs[1][1])
+
+
+def test_fusion_avg_is_a_selectable_merge_rule(tiny_clients, tmp_path):
+    """The historical 4th merge rule: weights = normalised inverse JS distance (utils.similarity)."""
+    from fedmse_decentralized_b200.ops import oracle
+    from fedmse_decentralized_b200.utils.similarity import fusion_distances
+    sh = make_shards(tiny_clients)
+    cfg = make_cfg(tmp_path, update_types=["fusion_avg"], fusion_rows=64)
+    eng = make_engine(cfg, sh, "hybrid", "fusion_avg")
+    ctl = eng.make_control(0)
+    eng.backend.train(eng.state, sh, eng._sel_local(ctl.sel), eng.hp)
+    before = eng.state.params.clone()
+    scores = eng.backend.vote_scores(eng.state, sh, ctl, eng.spec)
+    agg = eng.backend.elect(eng.state, scores, ctl, eng.spec)
+    d = eng.backend.fusion_scores(eng.state, sh, ctl, 64)
+    theta = eng.backend.merge(eng.state, sh, ctl, eng.spec, d, agg)
+    w = (1.0 / d) / (1.0 / d).sum()
+    want = sum(w[k] * before[g] for k, g in enumerate(ctl.sel))
+    assert_close(theta, want, rtol=1e-5, atol=1e-6, what="fusion_avg theta")
+    assert float(w.min()) > 0 and abs(float(w.sum()) - 1) < 1e-5
+    # and it runs as a full round through the engine
+    eng2 = make_engine(cfg, sh, "hybrid", "fusion_avg")
+    r = eng2.run_round(0)
+    assert r.aggregator >= 0 and len(r.client_metrics) == 6

@@ -42,3 +42,27 @@ def test_similarity_against_reference_module(reference_modules):
     s = kde_self_log_density(A)
     B = rng.normal(size=(60, 4)) * 1.7
     assert abs(RU.similarity_score(s, B) - similarity_score(s, B)) < 1e-10
+
+
+def test_fusion_distances_match_scipy_sklearn():
+    """fusion_avg weight function on tensors == the reference formula (sklearn KDE + scipy JS distance)
+    applied to each model's reconstruction of the dev rows (src/Utils/utils.py:10-24)."""
+    import torch
+    from scipy.spatial.distance import jensenshannon
+    from sklearn.neighbors import KernelDensity
+    from fedmse_decentralized_b200.layout import ParamLayout
+    from fedmse_decentralized_b200.models import init_packed_models
+    from fedmse_decentralized_b200.ops import oracle
+    from fedmse_decentralized_b200.utils.similarity import fusion_distances
+    torch.manual_seed(0)
+    lay = ParamLayout(12, 6, 3)              # low dimension: exp(log-density) stays representable for scipy
+    rows = init_packed_models(3, "hybrid", lay, 5.0)
+    dev = torch.randn(40, 128)
+    d = fusion_distances(rows, dev, lay, max_rows=40)
+    X = dev[:, :12].numpy().astype(np.float64)
+    ref = KernelDensity(kernel="gaussian", bandwidth="scott").fit(X).score_samples(X)
+    for j in range(3):
+        rec = oracle.forward(rows[j], dev[:, :12], lay)[1].numpy().astype(np.float64)
+        s = KernelDensity(kernel="gaussian", bandwidth="scott").fit(rec).score_samples(rec)
+        want = jensenshannon(np.exp(ref), np.exp(s))
+        assert abs(float(d[j]) - want) < 1e-5 * max(1.0, want), (j, float(d[j]), want)
