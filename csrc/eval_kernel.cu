@@ -6,6 +6,11 @@
 // so the AUC is computed here exactly in integers: sort (score, label) pairs in shared memory with a
 // bitonic network, prefix-count the negatives, and for every tie group add
 // positives * (2 * negatives_below + negatives_in_group); AUC = U2 / (2 n+ n-) in double.
+//
+// Capacity: up to 16,384 test rows per client (npad = next power of two, 8 B per key, <= 200 KB) the keys live
+// in shared memory.  Larger test sets (raw N-BaIoT devices put hundreds of thousands of abnormal rows in the test
+// set, Configuration/nba-iot-training.json) use the GLOBAL variant: keys in a caller-provided global scratch
+// (L2-resident), sorted as 8,192-key shared-memory chunks + global compare-exchange passes for the wide strides.
 #include <float.h>
 #include "common.cuh"
 #include "../include/fedmse_b200.h"
@@ -23,8 +28,28 @@ __device__ __forceinline__ uint32_t float_key(float f) {   // order-preserving f
     return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
+constexpr int AUC_CHUNK = 8192;        // keys per shared-memory chunk of the global variant (64 KB)
+
+// compare-exchange network steps j = j_hi, j_hi/2, ..., 1 of merge size k on a shared-memory chunk whose first
+// key has global index `base` (the sort direction depends on the global index)
+__device__ __forceinline__ void bitonic_steps_smem(unsigned long long* sk, int cnt, int base, int k, int j_hi) {
+    for (int j = j_hi; j > 0; j >>= 1) {
+        for (int i = threadIdx.x; i < cnt; i += ANT) {
+            const int ixj = i ^ j;
+            if (ixj > i) {
+                const unsigned long long x = sk[i], y = sk[ixj];
+                const bool up = ((base + i) & k) == 0;
+                if ((x > y) == up) { sk[i] = y; sk[ixj] = x; }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+template <bool GLOBAL>
 __global__ void __launch_bounds__(ANT, 1) auc_kernel(const FmAucArgs a, int npad) {
-    extern __shared__ __align__(16) unsigned long long keys[];   // [npad]
+    extern __shared__ __align__(16) unsigned long long skeys[];   // [npad] (or one AUC_CHUNK when GLOBAL)
+    unsigned long long* keys = GLOBAL ? a.keys_scratch + (size_t)blockIdx.x * npad : skeys;
     __shared__ double red[34];
     __shared__ int chunk_neg[ANT];
     __shared__ float mu[8], isd[8];
@@ -68,17 +93,38 @@ __global__ void __launch_bounds__(ANT, 1) auc_kernel(const FmAucArgs a, int npad
     const long long n_neg = (long long)n - n_pos;
     __syncthreads();
     // ---- bitonic sort of npad keys ----
-    for (int k = 2; k <= npad; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = tid; i < npad; i += ANT) {
-                const int ixj = i ^ j;
-                if (ixj > i) {
-                    const unsigned long long x = keys[i], y = keys[ixj];
-                    const bool up = (i & k) == 0;
-                    if ((x > y) == up) { keys[i] = y; keys[ixj] = x; }
-                }
-            }
+    if (!GLOBAL) {
+        for (int k = 2; k <= npad; k <<= 1) bitonic_steps_smem(keys, npad, 0, k, k >> 1);
+    } else {
+        __threadfence_block();
+        // (A) every chunk completely sorted in shared memory (all merge sizes up to the chunk)
+        for (int b = 0; b < npad; b += AUC_CHUNK) {
+            for (int i = tid; i < AUC_CHUNK; i += ANT) skeys[i] = keys[b + i];
             __syncthreads();
+            for (int k = 2; k <= AUC_CHUNK; k <<= 1) bitonic_steps_smem(skeys, AUC_CHUNK, b, k, k >> 1);
+            for (int i = tid; i < AUC_CHUNK; i += ANT) keys[b + i] = skeys[i];
+            __syncthreads();
+        }
+        // (B) wider merges: strides >= AUC_CHUNK in global memory, the rest of each merge per chunk in smem
+        for (int k = 2 * AUC_CHUNK; k <= npad; k <<= 1) {
+            for (int j = k >> 1; j >= AUC_CHUNK; j >>= 1) {
+                for (int i = tid; i < npad; i += ANT) {
+                    const int ixj = i ^ j;
+                    if (ixj > i) {
+                        const unsigned long long x = keys[i], y = keys[ixj];
+                        const bool up = (i & k) == 0;
+                        if ((x > y) == up) { keys[i] = y; keys[ixj] = x; }
+                    }
+                }
+                __syncthreads();
+            }
+            for (int b = 0; b < npad; b += AUC_CHUNK) {
+                for (int i = tid; i < AUC_CHUNK; i += ANT) skeys[i] = keys[b + i];
+                __syncthreads();
+                bitonic_steps_smem(skeys, AUC_CHUNK, b, k, AUC_CHUNK >> 1);
+                for (int i = tid; i < AUC_CHUNK; i += ANT) keys[b + i] = skeys[i];
+                __syncthreads();
+            }
         }
     }
     // ---- negatives prefix per contiguous chunk ----
@@ -120,9 +166,25 @@ extern "C" int fm_auc(const FmAucArgs* args, void* stream) {
     int npad = 2;
     while (npad < args->max_rows) npad <<= 1;
     const size_t smem = (size_t)npad * sizeof(unsigned long long);
-    if (smem > 200 * 1024) return (int)cudaErrorInvalidValue;   // > 25,600 test rows per client: caller falls back
-    cudaError_t err = cudaFuncSetAttribute(auc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (err != cudaSuccess) return (int)err;
-    auc_kernel<<<args->n_local, ANT, smem, (cudaStream_t)stream>>>(*args, npad);
+    cudaError_t err;
+    if (smem <= 200 * 1024) {                                    // <= 16,384 test rows per client 
+        err = cudaFuncSetAttribute(auc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (err != cudaSuccess) return (int)err;
+        auc_kernel<false><<<args->n_local, ANT, smem, (cudaStream_t)stream>>>(*args, npad);
+    } else {
+        // keys in global scratch: the caller provides n_local * fm_auc_scratch_keys(max_rows) 8-byte words
+        if (args->keys_scratch == nullptr || npad < 2 * AUC_CHUNK) return (int)cudaErrorInvalidValue;
+        const size_t csm = (size_t)AUC_CHUNK * sizeof(unsigned long long);
+        err = cudaFuncSetAttribute(auc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csm);
+        if (err != cudaSuccess) return (int)err;
+        auc_kernel<true><<<args->n_local, ANT, csm, (cudaStream_t)stream>>>(*args, npad);
+    }
     return (int)cudaGetLastError();
+}
+
+// 8-byte key slots per client the global-memory variant needs (0 = the shared-memory variant serves max_rows)
+extern "C" int64_t fm_auc_scratch_keys(int32_t max_rows) {
+    int npad = 2;
+    while (npad < max_rows) npad <<= 1;
+    return (size_t)npad * sizeof(unsigned long long) <= 200 * 1024 ? 0 : (int64_t)npad;
 }

@@ -87,7 +87,7 @@ class FmVerifyArgs(C.Structure):
 class FmAucArgs(C.Structure):
     _fields_ = [("mode", C.c_int32), ("n_local", C.c_int32), ("test_sse", c_vp), ("test_lat", c_vp),
                 ("labels", c_vp), ("test_off", c_vp), ("train_lat", c_vp), ("train_off", c_vp),
-                ("scores_out", c_vp), ("auc", c_vp), ("max_rows", C.c_int32)]
+                ("scores_out", c_vp), ("auc", c_vp), ("max_rows", C.c_int32), ("keys_scratch", c_vp)]
 
 
 class FmGossipArgs(C.Structure):
@@ -175,6 +175,8 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)
         fn.argtypes = argt
         fn.restype = C.c_int
+    lib.fm_auc_scratch_keys.argtypes = [C.c_int32]
+    lib.fm_auc_scratch_keys.restype = C.c_int64
     lib.fm_vote_scores_static_error.argtypes = []
     lib.fm_vote_scores_static_error.restype = C.c_char_p
     lib.fm_error_string.argtypes = [C.c_int]

@@ -360,7 +360,8 @@ class CudaBackend:
         want_scores = metric != "AUC"
         a = _lib.FmAucArgs(1 if hybrid else 0, st.n_clients, _ptr(self.test_sse), _ptr(self.test_lat),
                            _ptr(sh.test.y), _ptr(sh.test.off), _ptr(self.train_lat), _ptr(sh.train.off),
-                           _ptr(self.scores_out) if want_scores else 0, _ptr(self.auc), sh.test.max_count())
+                           _ptr(self.scores_out) if want_scores else 0, _ptr(self.auc), sh.test.max_count(),
+                           _ptr(self._auc_scratch(st.n_clients, sh.test.max_count())))
         _lib.check(self.lib.fm_auc(C.byref(a), self._stream()), "auc")
         self.launches += 1
         vals = None
@@ -374,6 +375,17 @@ class CudaBackend:
             host = self.test_lat[:, :7].cpu().numpy().astype("float32")
             lat = [host[sh.test.off_host[c]:sh.test.off_host[c + 1]].copy() for c in range(st.n_clients)]
         return self.auc, vals, lat
+
+    def _auc_scratch(self, n_local: int, max_rows: int) -> Optional[torch.Tensor]:
+        """Global key scratch of the AUC kernel for test sets beyond its shared-memory capacity (16,384 rows per
+        client); None below that."""
+        per = int(self.lib.fm_auc_scratch_keys(max_rows))
+        if per == 0:
+            return None
+        need = per * max(1, n_local)
+        if getattr(self, "_auc_keys", None) is None or self._auc_keys.numel() < need:
+            self._auc_keys = torch.empty(need, dtype=torch.int64, device=self.device)
+        return self._auc_keys
 
     def evaluate_side(self, st, sh, model_type: str) -> None:
         """Evaluation of the round on a side stream, from a snapshot of the parameters taken now (main

@@ -106,8 +106,11 @@ class ClientTrainer:
         else:
             self.adam_t, best, log_ = oracle.train_client(self.params, self.adam_m, self.adam_v, self.adam_t,
                                                           self.anchor, xt, xv, self.layout, hp)
+        if valid_loader is None:
+            log_ = []                     # the reference appends to training_tracking only when it validated (:405)
         self.training_tracking = log_
-        artefacts.save_client_model(self.save_dir, self.layout.unpack(best))
+        if valid_loader is not None:      # the reference saves model.cpt only inside its validation block (:387-411)
+            artefacts.save_client_model(self.save_dir, self.layout.unpack(best))
         artefacts.save_tracking(self.save_dir, log_)
         self._sync_module()
         return log_

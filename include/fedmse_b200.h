@@ -236,7 +236,9 @@ int fm_verify_update(const FmVerifyArgs* args, void* stream);
  * One CTA per local client.  mode 0 (autoencoder): score = sse / D.  mode 1 (hybrid):
  * score = || (z - mean(z_train)) / std(z_train) ||_2 with population std, 0 -> 1.
  * Non-finite scores are mapped like numpy.nan_to_num.  AUC is the tie-aware Mann-Whitney
- * statistic computed exactly in integers after an in-shared-memory bitonic sort. */
+ * statistic computed exactly in integers after a bitonic sort: in shared memory up to 16,384 test rows
+ * per client; above that in `keys_scratch` (n_local * fm_auc_scratch_keys(max_rows) 8-byte words of
+ * global memory, required then -- cudaErrorInvalidValue without it). */
 typedef struct FmAucArgs {
     int32_t mode; int32_t n_local;
     const float* test_sse; const float* test_lat; const float* labels; const int32_t* test_off;
@@ -244,8 +246,10 @@ typedef struct FmAucArgs {
     float* scores_out;  /* [test rows] or NULL */
     double* auc;        /* [n_local] */
     int32_t max_rows;   /* max test rows of any client (sizes shared memory) */
+    unsigned long long* keys_scratch;   /* NULL unless fm_auc_scratch_keys(max_rows) > 0 */
 } FmAucArgs;
 int fm_auc(const FmAucArgs* args, void* stream);
+int64_t fm_auc_scratch_keys(int32_t max_rows);
 
 /* ---- gossip merge (per-client T2; reference API client_trainer.py:141-172) ---------------
  * One CTA per selected local client i: candidates = nbr_idx[nbr_off[i] .. nbr_off[i+1]) (self

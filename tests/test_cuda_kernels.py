@@ -135,6 +135,33 @@ def test_auc_kernel_ties_and_nonfinite(dev):
     assert abs(float(out[0]) - want) < 1e-12
 
 
+def test_auc_kernel_large_test_sets_use_global_scratch(dev):
+    """More than 16,384 test rows per client (raw N-BaIoT devices, Configuration/nba-iot-training.json): the keys
+    are sorted in global scratch instead of shared memory; two clients of different sizes, with ties."""
+    import ctypes as C
+    from fedmse_decentralized_b200.ops import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(3)
+    sizes = [40000, 17001]
+    per = int(lib.fm_auc_scratch_keys(max(sizes)))
+    assert per == 65536 and int(lib.fm_auc_scratch_keys(16384)) == 0
+    sse = torch.cat([torch.randn(sizes[0], generator=g).abs() * 115.0,
+                     torch.randint(0, 50, (sizes[1],), generator=g).float() * 115.0])
+    y = (torch.rand(sum(sizes), generator=g) > 0.7).float()
+    off_h = [0, sizes[0], sum(sizes)]
+    want = [oracle.auc_from_scores(sse[off_h[c]:off_h[c + 1]] / 115.0, y[off_h[c]:off_h[c + 1]]) for c in range(2)]
+    off = torch.tensor(off_h, dtype=torch.int32, device=dev)
+    out = torch.zeros(2, dtype=torch.float64, device=dev)
+    sse_d, y_d = sse.to(dev), y.to(dev)
+    a = _lib.FmAucArgs(0, 2, sse_d.data_ptr(), 0, y_d.data_ptr(), off.data_ptr(), 0, 0, 0, out.data_ptr(), max(sizes), 0)
+    assert lib.fm_auc(C.byref(a), torch.cuda.current_stream().cuda_stream) != 0      # scratch is required here
+    scratch = torch.empty(2 * per, dtype=torch.int64, device=dev)
+    a.keys_scratch = scratch.data_ptr()
+    _lib.check(lib.fm_auc(C.byref(a), torch.cuda.current_stream().cuda_stream))
+    for c in range(2):
+        assert abs(float(out[c]) - want[c]) < 1e-12, (c, float(out[c]), want[c])
+
+
 @pytest.mark.parametrize("update_type,compat", [("avg", True), ("mse_avg", True), ("mse_avg", False),
                                                 ("fedprox", True)])
 def test_full_round_matches_oracle(tiny_clients, tmp_path, dev, update_type, compat):
