@@ -134,7 +134,8 @@ def run_ours(args):
     cfg = ExperimentConfig(num_participants=args.participation, epoch=args.epochs, lr_rate=1e-3, shrink_lambda=5,
                            network_size=n_global, batch_size=12, backend="cuda", write_latents=False,
                            save_client_models=False, reference_compat=True,
-                           score_precision=args.score_precision)
+                           score_precision=args.score_precision, aggregation=args.aggregation,
+                           topology=args.topology, topology_k=args.topology_k, topology_seed=args.seed)
     eng = FederationEngine(cfg, sh, args.model, args.update, comm=comm, names_global=[c.name for c in prepared])
     setup_s = time.time() - t0
     result_bytes = 8 * cnt + 4 * cnt * 2 + 8   # AUC (f64) + epochs_run + rejected (i32) + aggregator
@@ -201,7 +202,12 @@ def run_ours(args):
             "data": "synthetic", "impl": "ours",
             "rounds_per_sec": args.steps / (ms / 1e3),
             "config": {"model": f"SAE-CEN 115-27-7 ({args.model}) + {args.update}",
-                       "scenario": "N-BaIoT-shaped synthetic, reference round loop (elect/merge/broadcast/verify/evaluate)",
+                       "scenario": ("N-BaIoT-shaped synthetic, reference round loop (elect/merge/broadcast/verify/evaluate)"
+                                    if args.aggregation == "elected" else
+                                    f"N-BaIoT-shaped synthetic, decentralized gossip: every selected client merges its "
+                                    f"{args.topology} neighbours (k={args.topology_k}) weighted by MSE on its own validation "
+                                    f"rows, verifies, all clients evaluated (BASELINE.json config 4)"),
+                       "aggregation": args.aggregation, "topology": args.topology if args.aggregation == "gossip" else None,
                        "clients": n_global, "clients_per_gpu": args.clients_per_gpu,
                        "global_batch": 12, "seq_len": 115, "epochs": args.epochs, "local_patience": 1,
                        "participation": args.participation, "lr": 1e-3, "shrink_lambda": 5,
@@ -283,7 +289,9 @@ def run_reference(args):
             "config": {"model": f"SAE-CEN 115-27-7 ({args.model}) + {args.update}", "clients": n_global,
                        "clients_per_gpu": args.clients_per_gpu, "global_batch": 12, "seq_len": 115,
                        "epochs": args.epochs, "local_patience": 1, "participation": args.participation,
-                       "parallelism": f"reference loop, clients block-partitioned, NCCL all_gather of models, dp{comm.world}"},
+                       "parallelism": f"reference loop, clients block-partitioned, NCCL all_gather of models, dp{comm.world}",
+                       "aggregation": "elected (the reference's only round loop: its gossip API, client_trainer.py:141-172, "
+                                      "is never called by main.py and has no verification or topology)"},
             "e2e": {"value": samples / (float(mx[1]) / 1e3), "unit": "samples/s",
                     "what": "the reference's loop is end to end by construction (per-batch H2D from pinned "
                             "DataLoaders, .item() every step)"},
@@ -304,6 +312,11 @@ def main():
     ap.add_argument("--model", default="hybrid", choices=["hybrid", "autoencoder"])
     ap.add_argument("--update", default="mse_avg", choices=["avg", "fedprox", "mse_avg"])
     ap.add_argument("--seed", type=int, default=1234)
+    ap.add_argument("--aggregation", default="elected", choices=["elected", "gossip"],
+                    help="elected = the reference's round loop (default, what --impl reference runs); gossip = "
+                         "decentralized neighbour aggregation (BASELINE.json config 4)")
+    ap.add_argument("--topology", default="random-k", choices=["full", "ring", "random-k"])
+    ap.add_argument("--topology-k", type=int, default=4)
     ap.add_argument("--score-precision", default="tf32x3", choices=["fp32", "tf32", "tf32x3"],
                     help="scoring forwards: exact FFMA kernel, single-pass TF32 or error-compensated 3xTF32 on tcgen05")
     args = ap.parse_args()

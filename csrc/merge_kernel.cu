@@ -207,8 +207,10 @@ __device__ __forceinline__ void verify_decide_and_apply(float* params_c, float* 
 
 __global__ void __launch_bounds__(VNT) verify_kernel(const FmVerifyArgs a) {
     __shared__ double red[34];
+    // multi-GPU: every rank is done reading the pre-merge slabs and score boards (waited for even when nothing was
+    // elected: merge_kernel signals in that case too, and the wait keeps the boards' write-after-read order)
+    wait_arrivals(a.arrive, a.expect);
     if (a.agg_pos[0] < 0) return;
-    wait_arrivals(a.arrive, a.expect);    // multi-GPU: every rank is done reading the pre-merge slabs
     const int c = blockIdx.x, tid = threadIdx.x;
     const int g = a.first_client + c;
     float* params_c = a.params + (size_t)c * P_PAD;

@@ -96,7 +96,12 @@ class FmGossipArgs(C.Structure):
                 ("rejected", c_vp), ("n_local", C.c_int32), ("first_client", C.c_int32),
                 ("sel_local", c_vp), ("n_sel", C.c_int32), ("nbr_off", c_vp), ("nbr_idx", c_vp),
                 ("x_valid", c_vp), ("valid_off", c_vp), ("mode", C.c_int32), ("thr_change", C.c_float),
-                ("thr_perf", C.c_float)]
+                ("thr_perf", C.c_float), ("topo_kind", C.c_int32), ("topo_k", C.c_int32), ("round", C.c_int32),
+                ("topo_seed", C.c_uint64), ("snap_parity", C.c_int32), ("snap_stride", C.c_int64),
+                ("arrive", c_vp), ("expect", C.c_uint32)]
+
+
+TOPO_KIND = {"csr": 0, "full": 1, "ring": 2, "random-k": 3, "random_k": 3, "random": 3}
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -160,6 +165,8 @@ def load() -> C.CDLL:
         ("fm_verify_update", [C.POINTER(FmVerifyArgs), c_vp]),
         ("fm_auc", [C.POINTER(FmAucArgs), c_vp]),
         ("fm_gossip", [C.POINTER(FmGossipArgs), c_vp]),
+        ("fm_gossip_publish", [c_vp, c_vp, C.c_int64, c_vp, C.c_int32, c_vp, c_vp]),
+        ("fm_random_neighbour", [C.c_uint64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
         ("fm_weighted_rows", [c_vp, c_vp, C.c_int32, c_vp, C.c_int64, c_vp, C.c_uint32, c_vp, C.c_int32, C.c_int32,
                               c_vp, c_vp]),
         ("fm_slice_reduce", [c_vp, C.c_int32, C.c_int32, c_vp, C.c_int64, c_vp, C.c_uint32, c_vp, C.c_int32, c_vp, c_vp]),

@@ -318,11 +318,6 @@ class CudaBackend:
         self.launches += 1
         return self.theta
 
-    def _barrier_token(self) -> torch.Tensor:
-        if not hasattr(self, "_tok"):
-            self._tok = torch.zeros(1, dtype=torch.float32, device=self.device)
-        return self._tok
-
     # ------------------------------------------------------------------ T3
     def verify_update(self, st, sh, ctl: RoundControl, spec: MergeSpec, theta, agg_pos) -> None:
         if spec.verification_method == "dev":
@@ -405,34 +400,57 @@ class CudaBackend:
             self.evaluate(proxy, sh, model_type, False, "AUC")
 
     # ------------------------------------------------------------------ gossip
-    def gossip(self, st, sh, ctl: RoundControl, spec: MergeSpec, neigh: List[List[int]], rows=None) -> None:
+    device_topology = True     # full / ring / random-k graphs are generated inside the gossip kernel
+
+    def gossip(self, st, sh, ctl: RoundControl, spec: MergeSpec, neigh, rows=None, topo=None) -> None:
+        """One launch per rank: every selected client merges {itself} + its in-neighbours and gates the result.
+
+        ``topo = (kind, k, seed)`` with kind in full / ring / random-k: the kernel generates the graph itself
+        (nothing is built or uploaded on the host); otherwise ``neigh`` (list of neighbour lists) is uploaded as a
+        CSR table once per distinct object.  Cross-GPU ordering uses the snapshot-parity protocol of
+        ``csrc/gossip_kernel.cu`` (peer-mapped arrival counters), no NCCL call."""
         from ..parallel import topology
         from ..parallel.symmetric import SymmetricSlab
+        if spec.update_type == "fusion_avg":
+            raise NotImplementedError("fusion_avg weights are an elected-mode merge rule on the CUDA backend "
+                                      "(use backend='oracle' for gossip + fusion_avg)")
+        comm = self.comm
         if self.snap_slab is None:
+            rows_max = self.param_slab.nbytes // (4 * self.layout.padded)
             with torch.cuda.device(self.device):
-                self.snap_slab = SymmetricSlab(st.n_clients, self.layout.padded, self.comm,
-                                               rows_max=self.param_slab.nbytes // (4 * self.layout.padded))
+                self.snap_slab = SymmetricSlab(2 * rows_max, self.layout.padded, comm, rows_max=2 * rows_max)
             self._slabs.append(self.snap_slab)
-        if getattr(self, "_nbr_src", None) is not neigh:     # keep a reference: identity, not id()
-            off, idx = topology.to_csr(neigh, include_self=True)
-            self._nbr = (off.to(self.device), idx.to(self.device))
-            self._nbr_src = neigh
-        self.snap_slab.tensor.copy_(st.params)
-        if self.comm.is_dist:
-            self.comm.sum_(self._barrier_token())          # all snapshots complete before anyone reads
+            self._snap_stride = rows_max * self.layout.padded
+            self._gossip_seq = 0
+            self._gossip_done = torch.zeros(1, dtype=torch.int32, device=self.device)
+        kind, k, seed, off_p, idx_p = 0, 0, 0, 0, 0
+        if topo is not None and _lib.TOPO_KIND.get(topo[0], 0) != 0:
+            kind, k, seed = _lib.TOPO_KIND[topo[0]], int(topo[1]), int(topo[2])
+        else:
+            if getattr(self, "_nbr_src", None) is not neigh:     # keep a reference: identity, not id()
+                off, idx = topology.to_csr(neigh, include_self=True)
+                self._nbr = (off.to(self.device), idx.to(self.device))
+                self._nbr_src = neigh
+            off_p, idx_p = _ptr(self._nbr[0]), _ptr(self._nbr[1])
+        parity = self._gossip_seq & 1
+        self._gossip_seq += 1
+        snap = self.snap_slab.ptr + 4 * parity * self._snap_stride
+        _lib.check(self.lib.fm_gossip_publish(_ptr(st.params), snap, st.n_clients * self.layout.padded,
+                                              _ptr(self.ctl_slab.table) if comm.is_dist else 0, comm.world,
+                                              _ptr(self._gossip_done), self._stream()), "gossip_publish")
+        arrive, expect = (self.ctl_arrive_ptr + 4 * 3, comm.world * self._gossip_seq) if comm.is_dist else (0, 0)
         n = self.n_sel_local
-        if n:
-            a = _lib.FmGossipArgs(_ptr(self.snap_slab.table), self.comm.world, self.comm.rank, sh.n_global,
+        if n or comm.is_dist:
+            a = _lib.FmGossipArgs(_ptr(self.snap_slab.table), comm.world, comm.rank, sh.n_global,
                                   _ptr(st.params), _ptr(st.anchor), _ptr(st.hist), _ptr(st.hist_perf),
                                   _ptr(st.hist_valid), _ptr(st.rejected), st.n_clients, sh.first_client,
-                                  _ptr(self.ctl_sel_local), n, _ptr(self._nbr[0]), _ptr(self._nbr[1]),
+                                  _ptr(self.ctl_sel_local), n, off_p, idx_p,
                                   _ptr(sh.valid.x), _ptr(sh.valid.off),
                                   1 if spec.update_type == "mse_avg" else 0, spec.verification_threshold,
-                                  spec.performance_threshold)
+                                  spec.performance_threshold, kind, k, ctl.round, seed & (2**64 - 1), parity,
+                                  self._snap_stride, arrive, expect)
             _lib.check(self.lib.fm_gossip(C.byref(a), self._stream()), "gossip")
-            self.launches += 1
-        if self.comm.is_dist:
-            self.comm.sum_(self._barrier_token())          # peers done reading before the next snapshot
+        self.launches += 2
 
     # ------------------------------------------------------------------ one read-back per round
     def readback(self, st, agg_pos: Optional[torch.Tensor], with_auc: bool):
@@ -498,3 +516,13 @@ class CudaBackend:
 
     def synchronize(self) -> None:
         torch.cuda.synchronize(self.device)
+
+    def close(self) -> None:
+        """Release the peer-mapped slabs (raw cudaMalloc + IPC mappings: torch's allocator cannot reclaim them).
+        Collective on multi-GPU runs (each slab barriers before it is freed).  The state tensors that alias the
+        parameter slab must not be used afterwards."""
+        torch.cuda.synchronize(self.device)
+        for slab in self._slabs:
+            slab.close()
+        self._slabs.clear()
+        self.param_slab = self.snap_slab = None

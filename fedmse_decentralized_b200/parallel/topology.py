@@ -33,14 +33,43 @@ def ring(n: int, hops: int = 1) -> List[List[int]]:
     return out
 
 
+_M64 = (1 << 64) - 1
+
+
+def _splitmix64(x: int) -> int:
+    x = (x + 0x9E3779B97F4A7C15) & _M64
+    x = ((x ^ (x >> 30)) * 0xBF58476D1CE4E5B9) & _M64
+    x = ((x ^ (x >> 27)) * 0x94D049BB133111EB) & _M64
+    return x ^ (x >> 31)
+
+
+def random_neighbour(seed: int, round_idx: int, g: int, j: int, attempt: int, n: int) -> int:
+    """Draw ``attempt`` of neighbour slot ``j`` of client ``g`` in round ``round_idx`` (uniform over the other
+    ``n - 1`` clients).  Bit-for-bit the device function of ``csrc/gossip_kernel.cu`` (``fm_random_neighbour``):
+    the gossip kernel generates its random-k graph from ``(seed, round)`` alone, nothing is uploaded."""
+    h = _splitmix64((seed & _M64) ^ ((0xD1B54A32D192ED03 * (round_idx + 1)) & _M64))
+    h = _splitmix64(h ^ ((0x9E3779B97F4A7C15 * (g + 1)) & _M64))
+    h = _splitmix64(h ^ ((j << 32) | attempt))
+    c = h % (n - 1)
+    return c + (1 if c >= g else 0)
+
+
 def random_k(n: int, k: int, seed: int = 0, round_idx: int = 0) -> List[List[int]]:
-    """Each client draws ``k`` distinct random in-neighbours (fresh per round)."""
+    """Each client draws ``k`` distinct random in-neighbours (fresh per round); a slot that repeats an earlier
+    pick is redrawn with the next ``attempt``."""
     k = min(k, n - 1)
-    rng = np.random.default_rng([seed, round_idx])
     out = []
     for i in range(n):
-        cand = rng.choice(n - 1, size=k, replace=False)
-        out.append([int(c + (c >= i)) for c in cand])
+        nb: List[int] = []
+        for j in range(k):
+            attempt = 0
+            while True:
+                c = random_neighbour(seed, round_idx, i, j, attempt, n)
+                if c not in nb:
+                    nb.append(c)
+                    break
+                attempt += 1
+        out.append(nb)
     return out
 
 

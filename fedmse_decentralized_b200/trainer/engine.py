@@ -150,9 +150,10 @@ class FederationEngine:
             return
         n_sel = max(1, int(self.cfg.num_participants * self.N))
         sel = random.sample(range(self.N), n_sel)
-        need = (n_sel - 1) + (n_sel if self.update_type == "mse_avg" else 0)
-        while len(self._rand_fifo) < need:
-            self._rand_fifo.append(torch.rand(1).item())
+        if self.cfg.aggregation != "gossip":          # gossip has no vote: no tie-break draws
+            need = (n_sel - 1) + (n_sel if self.update_type == "mse_avg" else 0)
+            while len(self._rand_fifo) < need:
+                self._rand_fifo.append(torch.rand(1).item())
         self._prefetched = (round_idx, sel)
 
     def make_control(self, round_idx: int) -> RoundControl:
@@ -163,6 +164,8 @@ class FederationEngine:
             self._prefetched = None
         else:
             sel = random.sample(range(self.N), n_sel)
+        if cfg.aggregation == "gossip":               # no election: every selected client merges its neighbourhood
+            return RoundControl(round_idx, sel, -1, [1.0] * n_sel, sel[0], -1)
         quota = cfg.max_aggregation_threshold
         voter_pos, jitter = -1, [1.0] * n_sel
         for k in range(n_sel):
@@ -211,10 +214,8 @@ class FederationEngine:
         data, if any, is committed first).  The next call picks up from there.  Results are identical to
         the unpipelined sequence; if the next voter cannot be determined yet (quota nearly exhausted) the
         call silently falls back to the plain order."""
-        self._prefetch_next = (prefetch_next or pipeline_next) and ctl is None and self.cfg.aggregation != "gossip"
+        self._prefetch_next = (prefetch_next or pipeline_next) and ctl is None
         self._pipeline_next = pipeline_next and self._prefetch_next
-        if self.cfg.aggregation == "gossip":
-            return self._run_round_gossip(round_idx, ctl, evaluate, want_latents)
         be, st, sh, cm, tm = self.backend, self.state, self.sh, self.comm, self.timer
         pre, self._pre = self._pre, None
         if pre is not None:
@@ -229,7 +230,9 @@ class FederationEngine:
             with tm.phase("train"):
                 be.train(st, sh, self._sel_local(ctl.sel), self.hp)
         agg_pos = None
-        if ctl.voter_pos >= 0:
+        if self.cfg.aggregation == "gossip":
+            self._gossip_phase(ctl)
+        elif ctl.voter_pos >= 0:
             with tm.phase("vote"):
                 scores = be.vote_scores(st, sh, ctl, self.spec)
                 if not getattr(be, "exchanges_scores", False):     # CUDA multi-GPU exchanges in-kernel (P2P boards)
@@ -263,7 +266,7 @@ class FederationEngine:
         if getattr(self, "_prefetch_next", False):
             self.prefetch_control(ctl.round + 1)       # host work, overlaps with the kernels enqueued so far
         pipelined = (getattr(self, "_pipeline_next", False) and hasattr(be, "readback_async")
-                     and self._voter_is_decided(self._prefetched[1], ctl.sel))
+                     and (cfg.aggregation == "gossip" or self._voter_is_decided(self._prefetched[1], ctl.sel)))
         # pipelined rounds evaluate on a side stream from a parameter snapshot, concurrently with the next
         # round's local training (which leaves more than half of the SMs idle)
         side_eval = (pipelined and evaluate and not want_latents and cfg.metric == "AUC"
@@ -342,32 +345,27 @@ class FederationEngine:
 
     # ------------------------------------------------------------------ gossip round
     def neighbours(self, round_idx: int) -> List[List[int]]:
+        """Host copy of the round's gossip graph (the CUDA backend generates the same graph in its kernel)."""
         cfg = self.cfg
         if cfg.topology.startswith("random") or self._neigh_cache is None:
             self._neigh_cache = topology.build(cfg.topology, self.N, cfg.topology_k,
                                                cfg.topology_seed, round_idx)
         return self._neigh_cache
 
-    def _run_round_gossip(self, round_idx, ctl, evaluate, want_latents) -> RoundResult:
-        be, st, sh, cm, tm = self.backend, self.state, self.sh, self.comm, self.timer
-        if ctl is None:
-            n_sel = max(1, int(self.cfg.num_participants * self.N))
-            sel = random.sample(range(self.N), n_sel)
-            ctl = RoundControl(round_idx, sel, -1, [1.0] * n_sel, sel[0], -1)
-        if hasattr(be, "begin_round"):
-            be.begin_round(ctl)
-        with tm.phase("train"):
-            be.train(st, sh, self._sel_local(ctl.sel), self.hp)
+    def _gossip_phase(self, ctl: RoundControl) -> None:
+        be, st, sh, cm, tm, cfg = self.backend, self.state, self.sh, self.comm, self.timer, self.cfg
         with tm.phase("gossip"):
-            neigh = self.neighbours(round_idx)
             be_gossip = getattr(be, "gossip", None)
             if be_gossip is None:
                 raise RuntimeError(f"backend {be.name} has no gossip op")
-            rows = None
-            if cm.is_dist and not getattr(be, "reads_peers", False):
-                rows = cm.gather_rows(st.params, list(range(self.N)), self.first)
-            be_gossip(st, sh, ctl, self.spec, neigh, rows)
-        return self._finish_round(ctl, None, evaluate, want_latents)
+            if getattr(be, "device_topology", False):
+                be_gossip(st, sh, ctl, self.spec, None, None,
+                          topo=(cfg.topology, cfg.topology_k, cfg.topology_seed))
+            else:
+                rows = None
+                if cm.is_dist and not getattr(be, "reads_peers", False):
+                    rows = cm.gather_rows(st.params, list(range(self.N)), self.first)
+                be_gossip(st, sh, ctl, self.spec, self.neighbours(ctl.round), rows)
 
     # ------------------------------------------------------------------ full experiment for one combination
     def fit(self, stop: Optional[GlobalStop] = None, write: bool = True) -> List[RoundResult]:
@@ -493,6 +491,17 @@ class FederationEngine:
             touched.append(sh.valid.x)
         if touched and hasattr(self.backend, "data_updated"):
             self.backend.data_updated(*touched)
+
+    def close(self) -> None:
+        """Free backend resources that outlive python garbage collection (peer-mapped slabs).  Collective when
+        distributed.  The engine is unusable afterwards."""
+        if self._pre is not None:
+            self.backend.synchronize()
+            self._pre = None
+        be_close = getattr(self.backend, "close", None)
+        if be_close is not None:
+            self.state.params = None          # aliases the parameter slab
+            be_close()
 
     # ------------------------------------------------------------------ resume (absent in the reference)
     def snapshot(self) -> Dict:

@@ -89,10 +89,13 @@ def run_experiment(cfg: ExperimentConfig, comm: Optional[Comm] = None) -> Dict[s
                 eng = FederationEngine(cfg, sh, model_type, update_type, run=run, comm=comm,
                                        names_global=names)
                 stop = shared_stop if cfg.reference_compat else GlobalStop(cfg.global_patience)
-                eng.fit(stop)
-                best[model_type][update_type] = max(best[model_type][update_type], eng.final_best())
-                log.info("phase timings (ms): %s",
-                         {p: round(v["mean_ms"], 3) for p, v in eng.timer.summary().items()})
+                try:
+                    eng.fit(stop)
+                    best[model_type][update_type] = max(best[model_type][update_type], eng.final_best())
+                    log.info("phase timings (ms): %s",
+                             {p: round(v["mean_ms"], 3) for p, v in eng.timer.summary().items()})
+                finally:
+                    eng.close()          # peer-mapped slabs are raw device memory: free them per combination
                 del eng, sh
                 if device.type == "cuda":
                     torch.cuda.empty_cache()

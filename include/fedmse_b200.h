@@ -252,22 +252,38 @@ int fm_auc(const FmAucArgs* args, void* stream);
 int64_t fm_auc_scratch_keys(int32_t max_rows);
 
 /* ---- gossip merge (per-client T2; reference API client_trainer.py:141-172) ---------------
- * One CTA per selected local client i: candidates = nbr_idx[nbr_off[i] .. nbr_off[i+1]) (self
- * first); weight_j = 1/MSE(model_j on client i's validation rows) normalised (mode 1) or
- * uniform (mode 0); theta_i = sum w_j model_j read through peer_slabs; then the verification
- * gate of fm_verify_update on client i's own validation rows.  Reads `src` slabs, writes
- * `params` (must be distinct buffers: synchronous gossip). */
+ * One CTA per selected local client i: candidates = {i} + in-neighbours of i under the topology;
+ * weight_j = 1/MSE(model_j on client i's validation rows) (mode 1) or 1 (mode 0), normalised;
+ * theta_i = sum w_j model_j, every model fetched ONCE into shared memory (unicast bulk copies through
+ * `peer_src`, i.e. NVLink for remote owners) and used for both the score and the reduction; then the
+ * verification gate of fm_verify_update on client i's own validation rows.  Reads snapshot buffer
+ * `snap_parity` of the `peer_src` slabs, writes `params` (distinct buffers: synchronous gossip).
+ * Topology: FM_TOPO_FULL / FM_TOPO_RING (topo_k/2 hops each side) / FM_TOPO_RANDOM_K (topo_k distinct
+ * draws of fm_random_neighbour(seed, round, i, slot, attempt, n)) are generated in the kernel;
+ * FM_TOPO_CSR reads nbr_off/nbr_idx (global ids, self listed first).
+ * Multi-GPU: `arrive` = this rank's arrive[3] counter, complete when >= expect (fm_gossip_publish of
+ * every rank); a rank without selected clients still launches one waiting CTA (n_sel = 0). */
+enum { FM_TOPO_CSR = 0, FM_TOPO_FULL = 1, FM_TOPO_RING = 2, FM_TOPO_RANDOM_K = 3 };
 typedef struct FmGossipArgs {
     const float* const* peer_src;   /* [world] snapshot slabs to read */
     int32_t world; int32_t rank; int32_t n_global;
     float* params; float* anchor; float* hist; float* hist_perf; int32_t* hist_valid; int32_t* rejected;
     int32_t n_local; int32_t first_client;
     const int32_t* sel_local; int32_t n_sel;
-    const int32_t* nbr_off; const int32_t* nbr_idx;  /* CSR over global ids, indexed by global id */
+    const int32_t* nbr_off; const int32_t* nbr_idx;  /* FM_TOPO_CSR only: CSR over global ids, indexed by global id */
     const float* x_valid; const int32_t* valid_off;
     int32_t mode; float thr_change; float thr_perf;
+    int32_t topo_kind; int32_t topo_k; int32_t round; uint64_t topo_seed;
+    int32_t snap_parity; int64_t snap_stride;        /* floats between the two snapshot buffers of a slab */
+    const uint32_t* arrive; uint32_t expect;         /* NULL on one GPU */
 } FmGossipArgs;
 int fm_gossip(const FmGossipArgs* args, void* stream);
+/* params[n_floats] -> snapshot; then (peer_ctl != NULL) signal arrive[3] of every rank's control block once the
+ * whole copy is visible.  done_counter: one zeroed uint32 of scratch owned by the caller. */
+int fm_gossip_publish(const float* params, float* snapshot, int64_t n_floats, float* const* peer_ctl,
+                      int32_t world, uint32_t* done_counter, void* stream);
+/* the random-k draw, for hosts that need the same graph (parallel/topology.py restates it in python) */
+int32_t fm_random_neighbour(uint64_t seed, int32_t round, int32_t g, int32_t j, int32_t attempt, int32_t n);
 
 /* ---- wide-model weighted reduction across GPUs by in-kernel peer loads (no NCCL) ------------
  * (BASELINE.json config 5; the reference's merge for a model of any size: client_trainer.py:107-130.)

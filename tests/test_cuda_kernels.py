@@ -201,9 +201,13 @@ def test_vote_scores_and_election(tiny_clients, tmp_path, dev):
     assert a_gpu.tolist() == a_ref.tolist() and a_ref[0] != best
 
 
-def test_gossip_matches_oracle(tiny_clients, tmp_path, dev):
-    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "hybrid", "mse_avg", aggregation="gossip",
-                         topology="ring", num_participants=1.0, epoch=1)
+@pytest.mark.parametrize("topology,upd", [("ring", "mse_avg"), ("random-k", "mse_avg"), ("full", "mse_avg"),
+                                          ("random-k", "avg")])
+def test_gossip_matches_oracle(tiny_clients, tmp_path, dev, topology, upd):
+    """Fused gossip kernel (device-generated graph, one fetch per neighbour row) against the torch oracle that
+    walks the host copy of the same graph."""
+    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "hybrid", upd, aggregation="gossip",
+                         topology=topology, topology_k=3, topology_seed=11, num_participants=1.0, epoch=1)
     for r in range(2):
         random.seed(7 + r)
         sel = random.sample(range(6), 6)
@@ -213,6 +217,30 @@ def test_gossip_matches_oracle(tiny_clients, tmp_path, dev):
         assert_close(e_gpu.state.params, e_ref.state.params, 3e-3, 3e-5, f"gossip params r{r}")
         assert e_gpu.state.rejected.tolist() == e_ref.state.rejected.tolist()
         assert_close(torch.tensor(res_gpu.client_metrics), torch.tensor(res_ref.client_metrics), 0, 2e-3, "auc")
+
+
+def test_gossip_csr_table_equals_device_topology(tiny_clients, tmp_path, dev):
+    """An uploaded CSR table of the same ring gives bit-identical parameters to the in-kernel ring."""
+    from fedmse_decentralized_b200.parallel import topology
+    outs = []
+    for use_table in (False, True):
+        cfg = make_cfg(tmp_path, aggregation="gossip", topology="ring", num_participants=1.0, epoch=1)
+        eng = make_engine(cfg, make_shards(tiny_clients, dev), "hybrid", "mse_avg", "cuda", seed=3)
+        if use_table:
+            eng.backend.device_topology = False
+        eng.run_round(0)
+        outs.append(eng.state.params.clone())
+    assert torch.equal(outs[0], outs[1])
+
+
+def test_gossip_pipelined_rounds_are_bit_identical(tiny_clients, tmp_path, dev):
+    res = []
+    for pipe in (False, True):
+        cfg = make_cfg(tmp_path, aggregation="gossip", topology="random-k", topology_k=2, num_participants=0.7, epoch=1)
+        eng = make_engine(cfg, make_shards(tiny_clients, dev), "hybrid", "mse_avg", "cuda", seed=3)
+        out = [eng.run_round(r, pipeline_next=pipe and r < 3) for r in range(4)]
+        res.append(([o.client_metrics for o in out], eng.state.params.clone(), [o.selected for o in out]))
+    assert res[0][2] == res[1][2] and res[0][0] == res[1][0] and torch.equal(res[0][1], res[1][1])
 
 
 @pytest.mark.parametrize("precision,rtol", [("tf32", 2e-2), ("tf32x3", 2e-4)])

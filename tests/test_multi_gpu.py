@@ -21,26 +21,44 @@ from fedmse_decentralized_b200.parallel import init_distributed, shutdown
 from fedmse_decentralized_b200.trainer import FederationEngine, build_shards
 comm = init_distributed()
 assert comm.device.type == "cuda"
+E = os.environ
+n_clients, n_rounds, pipe = int(E.get("FM_CLIENTS", "9")), int(E.get("FM_ROUNDS", "3")), E.get("FM_PIPE", "0") == "1"
 spec = SyntheticSpec(n_normal=300, n_abnormal=220, n_test_normal=50, jitter_rows=8)
-clients, dev = prepare_from_raw(make_clients(9, spec, seed=4), True, seed=2)
+clients, dev = prepare_from_raw(make_clients(n_clients, spec, seed=4), True, seed=2)
 sh, names = build_shards(clients, dev, comm, comm.device)
 random.seed(1); np.random.seed(1); torch.manual_seed(1)
-cfg = ExperimentConfig(epoch=2, num_rounds=3, network_size=9, backend="cuda", output_root=os.environ["FM_OUT"],
-                       aggregation=os.environ.get("FM_AGG", "elected"), topology="ring", num_participants=0.7,
+cfg = ExperimentConfig(epoch=2, num_rounds=n_rounds, network_size=n_clients, backend="cuda", output_root=E["FM_OUT"],
+                       aggregation=E.get("FM_AGG", "elected"), topology=E.get("FM_TOPO", "ring"), topology_k=3,
+                       num_participants=float(E.get("FM_PART", "0.7")), score_precision=E.get("FM_PREC", "fp32"),
                        write_latents=False, save_client_models=False)
-eng = FederationEngine(cfg, sh, "hybrid", os.environ.get("FM_UPD", "mse_avg"), comm=comm, names_global=names)
-out = [eng.run_round(r) for r in range(3)]
+eng = FederationEngine(cfg, sh, "hybrid", E.get("FM_UPD", "mse_avg"), comm=comm, names_global=names)
+out = []
+if pipe:      # the bench's loop: pipelined rounds with fresh local rows staged from pinned host memory every round
+    f, c = sh.first_client, sh.n_clients
+    pin_t = sh.train.x.cpu().pin_memory()
+    pin_v = sh.valid.x[sh.valid.off_host[f]:sh.valid.off_host[f + c]].cpu().pin_memory()
+    for r in range(n_rounds):
+        last = r + 1 == n_rounds
+        if not last:
+            eng.stage_next_data(pin_t, pin_v)
+        out.append(eng.run_round(r, prefetch_next=True, pipeline_next=not last))
+        if not last:
+            eng.commit_staged_data()
+else:
+    out = [eng.run_round(r) for r in range(n_rounds)]
 torch.cuda.synchronize()
 if comm.rank == 0:
     print("RESULT " + json.dumps({"metrics": [r.client_metrics for r in out], "agg": [r.aggregator for r in out],
                                   "ver": [[v["is_verified"] for v in r.verification] for r in out],
                                   "epochs": [sorted(r.epochs_run.items()) for r in out]}))
+eng.close()
 shutdown()
 '''
 
 
-def _run(world, tmp_path, agg, upd="mse_avg"):
-    env = dict(os.environ, FM_ROOT=ROOT, FM_OUT=str(tmp_path), FM_AGG=agg, FM_UPD=upd, MASTER_ADDR="127.0.0.1")
+def _run(world, tmp_path, agg, upd="mse_avg", **env_extra):
+    env = dict(os.environ, FM_ROOT=ROOT, FM_OUT=str(tmp_path), FM_AGG=agg, FM_UPD=upd, MASTER_ADDR="127.0.0.1",
+               **{k: str(v) for k, v in env_extra.items()})
     script = tmp_path / "worker_gpu.py"
     script.write_text(WORKER)
     if world == 1:
@@ -54,17 +72,48 @@ def _run(world, tmp_path, agg, upd="mse_avg"):
     return json.loads(line[7:])
 
 
-@pytest.mark.parametrize("agg,upd", [("elected", "mse_avg"), ("elected", "avg"), ("gossip", "mse_avg")])
-def test_n_gpus_match_one_gpu(tmp_path, agg, upd):
+def _world():
     n = torch.cuda.device_count()
     if n < 2:
         pytest.skip("needs >= 2 GPUs")
-    world = 2 if n < 4 else (4 if n < 8 else 8)
-    one = _run(1, tmp_path, agg, upd)
-    many = _run(world, tmp_path, agg, upd)
+    return 2 if n < 4 else (4 if n < 8 else 8)
+
+
+def _same(one, many, n_clients):
     assert one["agg"] == many["agg"] and one["ver"] == many["ver"] and one["epochs"] == many["epochs"]
     for a, b in zip(one["metrics"], many["metrics"]):
-        assert len(a) == 9 and max(abs(x - y) for x, y in zip(a, b)) < 1e-6
+        assert len(a) == n_clients and max(abs(x - y) for x, y in zip(a, b)) < 1e-6
+
+
+@pytest.mark.parametrize("agg,upd", [("elected", "mse_avg"), ("elected", "avg"), ("gossip", "mse_avg")])
+def test_n_gpus_match_one_gpu(tmp_path, agg, upd):
+    world = _world()
+    _same(_run(1, tmp_path, agg, upd), _run(world, tmp_path, agg, upd), 9)
+
+
+def test_n_gpus_match_one_gpu_gossip_random_k(tmp_path):
+    """Gossip over a per-round random-k graph generated inside the kernel: same graph, same result on N GPUs."""
+    world = _world()
+    kw = dict(FM_TOPO="random-k", FM_ROUNDS=4, FM_CLIENTS=17)
+    _same(_run(1, tmp_path, "gossip", **kw), _run(world, tmp_path, "gossip", **kw), 17)
+
+
+def test_n_gpus_match_one_gpu_quota_exhaustion(tmp_path):
+    """10 clients x 16 rounds at 50 % participation: aggregation quotas (3 per client) run out, so rounds without a
+    voter and the pipelined loop's `next voter undecided` fallback are exercised on both sides."""
+    world = _world()
+    kw = dict(FM_CLIENTS=10, FM_ROUNDS=16, FM_PART=0.5, FM_PIPE=1)
+    one, many = _run(1, tmp_path, "elected", **kw), _run(world, tmp_path, "elected", **kw)
+    _same(one, many, 10)
+    assert -1 in one["agg"] or len(set(one["agg"])) >= 6
+
+
+@pytest.mark.parametrize("agg", ["elected", "gossip"])
+def test_n_gpus_match_one_gpu_pipelined_staged_64_clients(tmp_path, agg):
+    """The bench's loop (pipelined rounds + staged uploads, tcgen05 scoring) on 64 clients x 6 rounds."""
+    world = _world()
+    kw = dict(FM_CLIENTS=64, FM_ROUNDS=6, FM_PART=0.5, FM_PIPE=1, FM_PREC="tf32x3", FM_TOPO="random-k")
+    _same(_run(1, tmp_path, agg, **kw), _run(world, tmp_path, agg, **kw), 64)
 
 
 def test_p2p_weighted_allreduce_matches_nccl(tmp_path):

@@ -66,3 +66,18 @@ def test_fusion_distances_match_scipy_sklearn():
         s = KernelDensity(kernel="gaussian", bandwidth="scott").fit(rec).score_samples(rec)
         want = jensenshannon(np.exp(ref), np.exp(s))
         assert abs(float(d[j]) - want) < 1e-5 * max(1.0, want), (j, float(d[j]), want)
+
+
+def test_random_k_hash_matches_the_device_function():
+    """parallel/topology.py restates the gossip kernel's neighbour hash bit for bit (host side of the C ABI)."""
+    from fedmse_decentralized_b200.ops import _lib
+    from fedmse_decentralized_b200.parallel import topology
+    if not _lib.is_available():
+        pytest.skip("library not built")
+    lib = _lib.load()
+    for seed, rnd, g, j, att, n in [(0, 0, 0, 0, 0, 2), (11, 3, 5, 2, 1, 1000), (2**63 + 5, 17, 999, 63, 4, 1000),
+                                    (7, 1, 3, 0, 0, 6)]:
+        assert topology.random_neighbour(seed, rnd, g, j, att, n) == lib.fm_random_neighbour(seed, rnd, g, j, att, n)
+    nb = topology.random_k(50, 4, seed=1, round_idx=2)
+    assert all(len(set(r)) == 4 and i not in r for i, r in enumerate(nb))
+    assert nb != topology.random_k(50, 4, seed=1, round_idx=3)
