@@ -122,7 +122,13 @@ class ReferenceFederation:
         import pandas as pd
         dev_parts = []
         bs = cfg["batch_size"]
+        seed0 = int(cfg.get("seed", 1234))
         for i, cl in enumerate(raw_clients):     # src/main.py:131-207
+            # numpy's global generator drives DataFrame.sample as in the reference; it is re-seeded per client so
+            # that the shuffles of a client are the same on every rank (ranks only shuffle the abnormal rows of the
+            # clients they own, which would otherwise shift the stream of all later clients and give every rank a
+            # different replica of the validation / dev data)
+            np.random.seed((seed0 * 1000003 + i) % (2 ** 32))
             normal = pd.DataFrame(cl.normal).sample(frac=1).reset_index(drop=True)
             n = len(normal)
             n_tr, n_va, n_dv = int(0.4 * n), int(0.1 * n), int(0.4 * n)
@@ -146,6 +152,7 @@ class ReferenceFederation:
                 info["valid_loader"] = DataLoader(RDL.IoTDataset(p_va, l_va), batch_size=bs, pin_memory=True)
                 info["test_loader"] = DataLoader(test_ds, batch_size=bs, pin_memory=True)
             self.client_info.append(info)
+        np.random.seed((seed0 * 1000003 + 999983) % (2 ** 32))
         min_len = min(len(c["dev_normal_dataset"]) for c in self.client_info)     # src/main.py:214-223
         dev = pd.concat([c["dev_normal_dataset"].sample(n=min_len) for c in self.client_info], axis=0)
         processed_dev, _ = RDL.IoTDataProccessor(scaler="standard").fit_transform(dev)

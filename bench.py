@@ -102,31 +102,30 @@ def seed_all(seed):
     random.seed(seed); np.random.seed(seed); torch.manual_seed(seed)
 
 
-def run_ours(args):
+def build_engine(args, comm, n_global, first, cnt):
+    """Synthetic scenario -> device shards -> engine, for the block of clients [first, first + cnt) of ``comm``'s rank.
+    Every shuffle is keyed by (seed, client), so the replicated validation shards and the pooled dev matrix are
+    identical on every rank and for every partition of the clients over ranks."""
     import numpy as np
-    import torch
     from fedmse_decentralized_b200 import ExperimentConfig
     from fedmse_decentralized_b200.data import ShardStore, prepare_client, pool_dev_set
     from fedmse_decentralized_b200.data.shards import Segmented
     from fedmse_decentralized_b200.trainer import FederationEngine
-
-    comm, n_global, first, cnt = build_world(args)
-    dev = comm.device
     owned = range(first, first + cnt)
-    t0 = time.time()
     raw = synth(n_global, owned, args.seed)
     seed_all(args.seed)
-    rng = np.random.default_rng(args.seed)
     prepared = []
     for i, cl in enumerate(raw):
+        rng = np.random.default_rng([args.seed, 7, i])
         normal = cl.normal[rng.permutation(len(cl.normal))]
         abn = cl.abnormal[rng.permutation(len(cl.abnormal))] if i in owned else cl.abnormal
         prepared.append(prepare_client(cl.name, normal, abn, cl.test_normal if i in owned else None, True))
-    devset = pool_dev_set(prepared, sampler=lambda a, n: a[rng.permutation(len(a))[:n]])
+    rng_dev = np.random.default_rng([args.seed, 8])
+    devset = pool_dev_set(prepared, sampler=lambda a, n: a[rng_dev.permutation(len(a))[:n]])
     local = prepared[first:first + cnt]
     sh_host = ShardStore.build(local, devset, first_client=first, n_global=n_global)
     sh_host.valid = Segmented.from_list([c.valid for c in prepared])
-    sh = sh_host.to(dev)
+    sh = sh_host.to(comm.device)
     # pinned host copies of what an IoT gateway would deliver fresh every round (local training data)
     pin_train = sh_host.train.x.pin_memory()
     v0, v1 = sh_host.valid.off_host[first], sh_host.valid.off_host[first + cnt]
@@ -137,6 +136,79 @@ def run_ours(args):
                            score_precision=args.score_precision, aggregation=args.aggregation,
                            topology=args.topology, topology_k=args.topology_k, topology_seed=args.seed)
     eng = FederationEngine(cfg, sh, args.model, args.update, comm=comm, names_global=[c.name for c in prepared])
+    return eng, sh, pin_train, pin_valid
+
+
+def bench_loop(eng, pin_train, pin_valid, n_rounds, r0=0):
+    """The bench's round loop: pipelined rounds with every round's local rows staged from pinned host memory."""
+    out = []
+    eng.stage_next_data(pin_train, pin_valid)
+    eng.commit_staged_data()
+    for r in range(r0, r0 + n_rounds):
+        last = r + 1 == r0 + n_rounds
+        if not last:
+            eng.stage_next_data(pin_train, pin_valid)
+        out.append(eng.run_round(r, prefetch_next=True, pipeline_next=not last))
+        if not last:
+            eng.commit_staged_data()
+    return out
+
+
+def run_check(args, comm, n_global, first, cnt):
+    """--check: the SAME global scenario (clients_per_gpu x N clients) for ``--check-rounds`` rounds through the
+    bench's pipelined loop (staged uploads included), once on the N ranks and once on rank 0's GPU alone; the two runs
+    must agree on aggregator ids, epochs run, verification verdicts and every client's AUC (1e-6).  Prints one JSON
+    line; exit status 1 on a mismatch.  This anchors the multi-GPU path at the benchmark's scale."""
+    import torch
+    from fedmse_decentralized_b200.parallel import Comm
+    R = args.check_rounds
+    eng, sh, pt, pv = build_engine(args, comm, n_global, first, cnt)
+    multi = bench_loop(eng, pt, pv, R)
+    torch.cuda.synchronize(comm.device)
+    eng.close()
+    comm.barrier()
+    verdict = None
+    if comm.rank == 0:
+        solo = Comm(rank=0, world=1, device=comm.device)
+        eng1, sh1, pt1, pv1 = build_engine(args, solo, n_global, 0, n_global)
+        single = bench_loop(eng1, pt1, pv1, R)
+        torch.cuda.synchronize(comm.device)
+        bad = []
+        worst = 0.0
+        for r, (a, b) in enumerate(zip(multi, single)):
+            if a.selected != b.selected: bad.append(f"round {r}: selection differs")
+            if a.aggregator != b.aggregator: bad.append(f"round {r}: aggregator {a.aggregator} vs {b.aggregator}")
+            if a.epochs_run != b.epochs_run: bad.append(f"round {r}: epochs run differ")
+            if [v["is_verified"] for v in a.verification] != [v["is_verified"] for v in b.verification]:
+                bad.append(f"round {r}: verification verdicts differ")
+            d = max(abs(x - y) for x, y in zip(a.client_metrics, b.client_metrics))
+            worst = max(worst, d)
+            if not d < 1e-6: bad.append(f"round {r}: max |AUC difference| {d:.3e}")
+        verdict = {"check": "pass" if not bad else "FAIL", "n_gpus": comm.world, "clients": n_global, "rounds": R,
+                   "aggregation": args.aggregation, "score_precision": args.score_precision,
+                   "max_abs_auc_diff": worst, "aggregators": [a.aggregator for a in multi],
+                   "auc_mean_per_round": [sum(a.client_metrics) / len(a.client_metrics) for a in multi],
+                   "auc_min_per_round": [min(a.client_metrics) for a in multi], "mismatches": bad[:10]}
+        print(json.dumps(verdict))
+    comm.barrier()
+    if verdict is not None and verdict["check"] != "pass":
+        sys.exit(1)
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    from fedmse_decentralized_b200 import ExperimentConfig
+    from fedmse_decentralized_b200.data import ShardStore, prepare_client, pool_dev_set
+    from fedmse_decentralized_b200.data.shards import Segmented
+    from fedmse_decentralized_b200.trainer import FederationEngine
+
+    comm, n_global, first, cnt = build_world(args)
+    dev = comm.device
+    t0 = time.time()
+    if args.check:
+        return run_check(args, comm, n_global, first, cnt)
+    eng, sh, pin_train, pin_valid = build_engine(args, comm, n_global, first, cnt)
     setup_s = time.time() - t0
     result_bytes = 8 * cnt + 4 * cnt * 2 + 8   # AUC (f64) + epochs_run + rejected (i32) + aggregator
 
@@ -198,7 +270,12 @@ def run_ours(args):
             "dtype": {"fp32": "fp32 (training GEMMs: error-compensated 3xTF32 mma.sync, fp32 accumulate; rest FFMA)",
                       "tf32": "fp32 training (3xTF32 GEMMs) + tf32 scoring forwards",
                       "tf32x3": "fp32 (parameters, Adam, accumulation in fp32; GEMMs as error-compensated 3xTF32: training "
-                                "on mma.sync, scoring forwards on tcgen05; ~1e-6 relative to fp32 FFMA)"}[args.score_precision],
+                                "on mma.sync, scoring forwards on tcgen05; GPU tests hold scores to 2e-4 and trained "
+                                "parameters to 2e-3 relative of the fp32 oracle)",
+                      "fp16x3": "fp32 (parameters, Adam, accumulation in fp32; training GEMMs error-compensated 3xTF32 on "
+                                "mma.sync; MSE-weight scoring on tcgen05 kind::f16 with fp16 head+remainder operands, three "
+                                "products per GEMM; other scoring forwards 3xTF32 on tcgen05; GPU tests hold the MSE to 1e-4 "
+                                "relative of the fp32 oracle)"}[args.score_precision],
             "data": "synthetic", "impl": "ours",
             "rounds_per_sec": args.steps / (ms / 1e3),
             "config": {"model": f"SAE-CEN 115-27-7 ({args.model}) + {args.update}",
@@ -248,7 +325,8 @@ def run_reference(args):
     raw = synth(n_global, owned, args.seed)
     seed_all(args.seed)
     cfg = {"model_type": args.model, "update_type": args.update, "epoch": args.epochs, "batch_size": 12,
-           "lr_rate": 1e-3, "shrink_lambda": 5, "patience": 1, "num_participants": args.participation}
+           "lr_rate": 1e-3, "shrink_lambda": 5, "patience": 1, "num_participants": args.participation,
+           "seed": args.seed}
     fed = ref_harness.ReferenceFederation(raw, owned, cfg, comm.world, comm.rank, dev)
 
     def sync_all():
@@ -317,7 +395,10 @@ def main():
                          "decentralized neighbour aggregation (BASELINE.json config 4)")
     ap.add_argument("--topology", default="random-k", choices=["full", "ring", "random-k"])
     ap.add_argument("--topology-k", type=int, default=4)
-    ap.add_argument("--score-precision", default="tf32x3", choices=["fp32", "tf32", "tf32x3"],
+    ap.add_argument("--check", action="store_true",
+                    help="no timing: run the scenario on the N ranks and on one GPU and assert equal results")
+    ap.add_argument("--check-rounds", type=int, default=3)
+    ap.add_argument("--score-precision", default="tf32x3", choices=["fp32", "tf32", "tf32x3", "fp16x3"],
                     help="scoring forwards: exact FFMA kernel, single-pass TF32 or error-compensated 3xTF32 on tcgen05")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)   # timing rule: at least 3 warm-up steps, both arms

@@ -1,0 +1,600 @@
+// MSE-weight scoring of many models on ONE shared matrix (the pooled dev set), second generation:
+// every layer on the tensor core, fp16 hi/lo operands, per-model MSE finished inside the kernel.
+//
+// Reference: fed_mse_avg, src/Trainer/client_trainer.py:115-130 -- a full-batch forward of every selected model on
+// the dev matrix, s_j = 1 / MSE_j.  The work is n_models x rows row-forwards, quadratic in the client count (the dev
+// set is pooled from all clients), so it is the one phase of a round whose per-GPU cost grows with the number of
+// GPUs; score_multi_tc.cu (3xTF32) spent 1.6 k tensor cycles and 1.6 k CUDA-core cycles per (128-row tile, model).
+//
+// What changed against score_multi_tc.cu:
+//  * fp16 hi/lo instead of 3xTF32.  Every operand is split as v = hi + lo with hi = fp16(v), lo = fp16(v - hi)
+//    (22 mantissa bits together, |v| clamped to the fp16 range first) and every GEMM is the three products
+//    hi*hi + hi*lo + lo*hi with fp32 accumulation in TMEM: kind::f16 runs at twice the TF32 rate and K = 16 per
+//    instruction, so a pair costs 24 + 6 + 6 MMAs (~0.86 k tensor cycles) instead of 45 + 12 (~1.5 k).
+//  * The 27 -> 7 -> 27 bottleneck left the CUDA cores.  There is no activation between the two inner layers, so
+//    h2 = relu(W3 (W2 h1 + b2) + b3) = relu(W32 h1 + b32) with W32 = W3 W2 (27 x 27, rank 7) and b32 = W3 b2 + b3,
+//    formed once per model by the prep kernel: ONE extra small GEMM (M128 N32 K32) between the two big ones.
+//  * Biases ride in the GEMMs: the parked tile gets a constant-one column (k = 115), W1 carries b1 in that column
+//    and a pass-through row that makes h1[27] = 1, W32 carries b32 in column 27 and passes the one on, W4 carries
+//    b4 in column 27.  The epilogues between the GEMMs are ReLU + fp16 split only, no tables, no FMAs.
+//  * X (hi/lo) is double buffered in TMEM, so the next tile is parked while the current one is still being read.
+//  * No [models x rows] SSE matrix: each epilogue warp writes one partial sum per (model, tile); after a grid-wide
+//    barrier the CTAs reduce them in a fixed order to the per-model MSE (deterministic, replaces chunk_mean).
+//
+// TMEM map (512 columns): X[u&1] hi 128u..+63, lo +64..+127 | D1/h1[b] 256+32b | D1b/h2[b] 320+32b | D2 384..511.
+// Warp roles: 0-3 epilogues 1a/1b + tile parking, 4-7 epilogue 2 (squared error), 8 MMA issue, 9 weight images,
+// 10 X tiles (TMA).
+//
+// Tensor-pipe issue order in steady state:  ... MMA1(g+2)  MMA1b(g+1)  MMA2(g)  MMA1(g+3) ...
+// TMA multicast is not used; the operand images and the dev matrix live in this GPU's memory.
+#include <cuda_fp16.h>
+#include <type_traits>
+#include "tc_common.cuh"
+#include "../include/fedmse_b200.h"
+
+namespace fm {
+namespace tcf {
+
+using namespace fm::tc;
+
+constexpr int NT_F = 352;
+constexpr int MMA_WARP = 8, WLOAD_WARP = 9, XLOAD_WARP = 10;
+constexpr int F_TMEM_COLS = 512;
+constexpr int C_X = 0, C_XLO = 64, C_D1 = 256, C_D1B = 320, C_D2 = 384;     // X buffer u at 128 * u
+// operand image of one model (bytes).  K-major, 128-B swizzle, 64 fp16 per 128-B row (short K is zero padded).
+constexpr int W1_BYTES = 2 * 4096;          // [32 n][128 k]  = two K-blocks of 32 rows x 128 B
+constexpr int W32_BYTES = 4096;             // [32 n][32 k]   (k 32..63 zero)
+constexpr int W4_BYTES = 128 * 128;         // [128 n][32 k]  (k 32..63 zero)
+constexpr int IMG_W1 = 0, IMG_W1LO = IMG_W1 + W1_BYTES, IMG_W32 = IMG_W1LO + W1_BYTES, IMG_W32LO = IMG_W32 + W32_BYTES,
+              IMG_W4 = IMG_W32LO + W32_BYTES, IMG_W4LO = IMG_W4 + W4_BYTES, IMG_F_BYTES = IMG_W4LO + W4_BYTES;   // 57,344
+static_assert(IMG_F_BYTES <= FM_TC_IMAGE_BYTES, "the f16 image must fit the image slot of the header");
+constexpr float F16_MAX = 65504.f;
+
+struct FSmem {
+    alignas(1024) unsigned char x[4 * XBLK];                 // fp32 staging of one 128-row tile (TMA, 128-B swizzle)
+    alignas(1024) unsigned char w1[2][2 * W1_BYTES];         // hi | lo
+    alignas(1024) unsigned char w32[2][2 * W32_BYTES];
+    alignas(1024) unsigned char w4[2][2 * W4_BYTES];
+    alignas(8) uint64_t bar_x, bar_xfree, bar_xt[2], bar_w1[2], bar_w32[2], bar_w4[2], bar_d1[2], bar_h1[2], bar_d1b[2],
+        bar_h2[2], bar_d2[2], bar_d2free;
+    uint32_t tmem_base;
+    double red[12];
+};
+
+// byte offset of fp16 element (row, k) inside a [rows x 64 fp16] K-block with the 128-B swizzle
+__host__ __device__ __forceinline__ int sw128h(int row, int k) {
+    return row * 128 + ((((k >> 3) ^ (row & 7)) << 4) | ((k & 7) << 1));
+}
+__host__ __device__ constexpr uint32_t idesc_f16(int M, int N) {       // D = F32, A = B = F16, both K-major, dense
+    return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void mma_ts_f16(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, {%5, %5, %5, %5}, p;\n\t}\n"
+                 ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accum), "r"(0u) : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+                 "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};\n"
+                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}\n"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+// (a, b) -> packed fp16 heads (a in the low half: element k of an A row sits in bits [15:0] of column k / 2 when k is
+// even) and packed fp16 remainders
+template <bool SWAP>
+__device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
+    const __half2 h = SWAP ? __floats2half2_rn(b, a) : __floats2half2_rn(a, b);
+    const float2 f = __half22float2(h);
+    const __half2 l = SWAP ? __floats2half2_rn(b - f.x, a - f.y) : __floats2half2_rn(a - f.x, b - f.y);
+    hi = *reinterpret_cast<const uint32_t*>(&h);
+    lo = *reinterpret_cast<const uint32_t*>(&l);
+}
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+    unsigned long long ra, rb, rd;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+    float2 d;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
+}
+
+struct PairCursor {
+    int i, m, m0, m1, tile, ord;      // unit slot i of this CTA, model m in [m0, m1), ordinal of the (non-empty) unit
+    bool ok;
+};
+
+// ---- prep: one CTA per slot; owned slots get a dense index and an operand image ----------------
+__global__ void __launch_bounds__(256) prep_images_f16_kernel(const float* __restrict__ slab, const int* __restrict__ slot_client,
+                                                              int first_client, int n_local, int n_slots,
+                                                              unsigned char* __restrict__ images, int* __restrict__ owned_slots,
+                                                              int* __restrict__ n_owned) {
+    __shared__ int s_idx;
+    __shared__ float w2s[Z * H], w3s[H * Z], b2s[8], b3s[32];
+    const int slot = blockIdx.x, tid = threadIdx.x;
+    const int c = (slot_client ? slot_client[slot] : first_client + slot) - first_client;
+    if (c < 0 || c >= n_local) return;
+    if (tid == 0) { s_idx = atomicAdd(n_owned, 1); owned_slots[s_idx] = slot; }
+    const float* row = slab + (size_t)c * P_PAD;
+    for (int i = tid; i < Z * H; i += 256) { w2s[i] = row[OFF_W2 + i]; w3s[i] = row[OFF_W3 + i]; }
+    if (tid < Z) b2s[tid] = row[OFF_B2 + tid];
+    if (tid < H) b3s[tid] = row[OFF_B3 + tid];
+    __syncthreads();
+    unsigned char* img = images + (size_t)s_idx * FM_TC_IMAGE_BYTES;
+    for (int i = tid; i < IMG_F_BYTES / 16; i += 256) reinterpret_cast<uint4*>(img)[i] = make_uint4(0, 0, 0, 0);
+    __syncthreads();
+    auto put = [&](int off_hi, int off_lo, int off, float v) {
+        v = fminf(fmaxf(v, -F16_MAX), F16_MAX);
+        const __half h = __float2half_rn(v);
+        *reinterpret_cast<__half*>(img + off_hi + off) = h;
+        *reinterpret_cast<__half*>(img + off_lo + off) = __float2half_rn(v - __half2float(h));
+    };
+    for (int p = tid; p < NP; p += 256) {
+        const float v = row[p];
+        if (p < OFF_B1) { const int n = p / D, k = p - n * D; put(IMG_W1, IMG_W1LO, (k >> 6) * 4096 + sw128h(n, k & 63), v); }
+        else if (p < OFF_W2) put(IMG_W1, IMG_W1LO, 4096 + sw128h(p - OFF_B1, 115 & 63), v);     // b1 rides in column 115 (x[115] == 1)
+        else if (p >= OFF_W4 && p < OFF_B4) { const int q = p - OFF_W4, d = q / H, j = q - d * H; put(IMG_W4, IMG_W4LO, sw128h(d, j), v); }
+        else if (p >= OFF_B4) put(IMG_W4, IMG_W4LO, sw128h(p - OFF_B4, 27), v);                 // b4 rides in column 27 (h2[27] == 1)
+    }
+    if (tid == 0) {
+        put(IMG_W1, IMG_W1LO, 4096 + sw128h(27, 115 & 63), 1.f);      // h1[27] = relu(1 * x[115]) = 1
+        put(IMG_W32, IMG_W32LO, sw128h(27, 27), 1.f);                 // h2[27] = relu(1 * h1[27]) = 1
+    }
+    // W32 = W3 W2 (27 x 27), b32 = W3 b2 + b3 in column 27
+    for (int e = tid; e < H * (H + 1); e += 256) {
+        const int n = e / (H + 1), k = e - n * (H + 1);
+        float acc = k < H ? 0.f : b3s[n];
+#pragma unroll
+        for (int i = 0; i < Z; ++i) acc = fmaf(w3s[n * Z + i], k < H ? w2s[i * H + k] : b2s[i], acc);
+        put(IMG_W32, IMG_W32LO, sw128h(n, k), acc);
+    }
+}
+
+template <bool SWAP>
+__global__ void __launch_bounds__(NT_F, 1)
+score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned char* __restrict__ images,
+                       const int* __restrict__ owned_slots, const int* __restrict__ n_owned_ptr, int x_rows, int n_chunks,
+                       float* __restrict__ partial, float* __restrict__ out_mse, unsigned* __restrict__ gbar,
+                       unsigned long long* __restrict__ dbg) {
+    extern __shared__ __align__(1024) unsigned char smem_dyn[];
+    FSmem& S = *reinterpret_cast<FSmem*>(smem_dyn);
+    if ((smem_u32(smem_dyn) & 1023u) != 0u) __trap();         // 128-B swizzle needs a 1024-B aligned base
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n_models = *n_owned_ptr;
+    if (n_models <= 0) return;                                // uniform over the grid
+    const int n_tiles = (x_rows + TROWS - 1) / TROWS;
+    const int n_units = n_tiles * n_chunks;
+    const int my_units = (int)blockIdx.x < n_units ? (n_units - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+    auto next_unit = [&](PairCursor& c) {
+        for (;;) {
+            if (++c.i >= my_units) { c.ok = false; return; }
+            const int u = (int)blockIdx.x + c.i * (int)gridDim.x, ch = u % n_chunks;
+            c.tile = u / n_chunks;
+            c.m = c.m0 = ch * n_models / n_chunks;          // n_models <= FM_MAX_SEL, n_chunks <= 4: no overflow
+            c.m1 = (ch + 1) * n_models / n_chunks;
+            if (c.m < c.m1) { ++c.ord; c.ok = true; return; }
+        }
+    };
+    auto first_pair = [&]() { PairCursor c; c.i = -1; c.m = c.m0 = c.m1 = 0; c.tile = 0; c.ord = -1; c.ok = false; next_unit(c); return c; };
+    auto next_pair = [&](PairCursor& c) { if (++c.m >= c.m1) next_unit(c); };
+
+    if (tid == 0) {
+        mbar_init(&S.bar_x, 1); mbar_init(&S.bar_xfree, 256); mbar_init(&S.bar_d2free, 128);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&S.bar_xt[b], 128); mbar_init(&S.bar_w1[b], 1); mbar_init(&S.bar_w32[b], 1); mbar_init(&S.bar_w4[b], 1);
+            mbar_init(&S.bar_d1[b], 1); mbar_init(&S.bar_d1b[b], 1); mbar_init(&S.bar_d2[b], 1);
+            mbar_init(&S.bar_h1[b], 128); mbar_init(&S.bar_h2[b], 128);
+        }
+        fence_mbar_init();
+    }
+    if (warp == MMA_WARP) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)), "r"(F_TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = S.tmem_base;
+    constexpr uint32_t IDESC_N32 = idesc_f16(128, 32), IDESC_N128 = idesc_f16(128, 128);
+
+    // total pairs of this CTA and, per role, a walk over them in the same order
+    const bool has_work = first_pair().ok;
+    if (!has_work) {
+    } else if (warp == MMA_WARP) {
+        if (elect_one()) {
+            const uint64_t dw1[2] = {smem_desc_sw128(S.w1[0]), smem_desc_sw128(S.w1[1])};
+            const uint64_t dw32[2] = {smem_desc_sw128(S.w32[0]), smem_desc_sw128(S.w32[1])};
+            const uint64_t dw4[2] = {smem_desc_sw128(S.w4[0]), smem_desc_sw128(S.w4[1])};
+            // Three issue stages walk the pairs in order: q1 / q1b / q2 = next pair of MMA1 / MMA1b / MMA2.  A stage is
+            // issued as soon as its inputs are there (non-blocking barrier tests), so the steady-state order
+            // ... MMA1(g+2) MMA1b(g+1) MMA2(g) ... emerges by itself and a unit boundary (MMA1 of the next unit waits
+            // for its tile) never blocks the MMAs that the tile's arrival depends on -- units of any length are safe.
+            // Buffer reuse is covered by issue order (the tensor pipe executes in order): MMA1(q) overwrites D1[q&1]
+            // only after MMA1b(q-2), its last reader, was issued (q1 <= q1b + 1); MMA1b(q) overwrites D1b[q&1] only
+            // after MMA2(q-2) was issued (q1b <= q2 + 1); MMA2 waits for epilogue 2 to have copied D2 out.
+            // Parity safety: every barrier tested here completes its next phase only after work that this thread
+            // issues after having seen the current one.
+            PairCursor c1 = first_pair();
+            int q1 = 0, q1b = 0, q2 = 0, unit1 = -1;
+            int n_pairs = 0;
+            { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; next_pair(t); } }
+            auto ready1 = [&]() -> bool {
+                if (q1 >= n_pairs || q1 > q1b + 1) return false;
+                if (!mbar_test(&S.bar_w1[q1 & 1], (uint32_t)((q1 >> 1) & 1))) return false;
+                if (c1.ord != unit1 && !mbar_test(&S.bar_xt[c1.ord & 1], (uint32_t)((c1.ord >> 1) & 1))) return false;
+                return true;
+            };
+            auto issue1 = [&]() {                       // MMA1(q1): D1[b] = X[u] . W1^T  (3 x 8 k-steps)
+                const int b = q1 & 1, ub = c1.ord & 1;
+                unit1 = c1.ord;
+                tc_fence_after();
+                const uint32_t d1 = tmem + C_D1 + 32 * b, xh = tmem + 128 * ub + C_X, xl = tmem + 128 * ub + C_XLO;
+#pragma unroll
+                for (int kk = 0; kk < 8; ++kk) {
+                    const uint64_t bh = dw1[b] + (uint64_t)(((kk >> 2) * 4096 + (kk & 3) * 32) >> 4);
+                    const uint64_t bl = bh + (uint64_t)(W1_BYTES >> 4);
+                    mma_ts_f16(d1, xh + kk * 8, bh, IDESC_N32, kk ? 1u : 0u);
+                    mma_ts_f16(d1, xh + kk * 8, bl, IDESC_N32, 1u);
+                    mma_ts_f16(d1, xl + kk * 8, bh, IDESC_N32, 1u);
+                }
+                tc_commit(&S.bar_d1[b]);
+                next_pair(c1);
+                ++q1;
+            };
+            auto ready1b = [&]() -> bool {
+                if (q1b >= q1 || q1b > q2 + 1) return false;
+                const uint32_t ph = (uint32_t)((q1b >> 1) & 1);
+                return mbar_test(&S.bar_h1[q1b & 1], ph) && mbar_test(&S.bar_w32[q1b & 1], ph);
+            };
+            auto issue1b = [&]() {                      // MMA1b(q1b): D1b[b] = h1[b] . W32^T  (3 x 2 k-steps)
+                const int b = q1b & 1;
+                tc_fence_after();
+                const uint32_t d = tmem + C_D1B + 32 * b, ah = tmem + C_D1 + 32 * b, al = ah + 16;
+#pragma unroll
+                for (int ks = 0; ks < 2; ++ks) {
+                    const uint64_t bh = dw32[b] + (uint64_t)((ks * 32) >> 4), bl = bh + (uint64_t)(W32_BYTES >> 4);
+                    mma_ts_f16(d, ah + ks * 8, bh, IDESC_N32, ks ? 1u : 0u);
+                    mma_ts_f16(d, ah + ks * 8, bl, IDESC_N32, 1u);
+                    mma_ts_f16(d, al + ks * 8, bh, IDESC_N32, 1u);
+                }
+                tc_commit(&S.bar_d1b[b]);
+                ++q1b;
+            };
+            auto ready2 = [&]() -> bool {
+                if (q2 >= q1b) return false;
+                const uint32_t ph = (uint32_t)((q2 >> 1) & 1);
+                if (!mbar_test(&S.bar_h2[q2 & 1], ph) || !mbar_test(&S.bar_w4[q2 & 1], ph)) return false;
+                return q2 == 0 || mbar_test(&S.bar_d2free, (uint32_t)((q2 - 1) & 1));   // epilogue 2 (q2 - 1) holds D2 in registers
+            };
+            auto issue2 = [&]() {                       // MMA2(q2): D2 = h2[b] . W4^T  (3 x 2 k-steps)
+                const int b = q2 & 1;
+                tc_fence_after();
+                const uint32_t d = tmem + C_D2, ah = tmem + C_D1B + 32 * b, al = ah + 16;
+#pragma unroll
+                for (int ks = 0; ks < 2; ++ks) {
+                    const uint64_t bh = dw4[b] + (uint64_t)((ks * 32) >> 4), bl = bh + (uint64_t)(W4_BYTES >> 4);
+                    mma_ts_f16(d, ah + ks * 8, bh, IDESC_N128, ks ? 1u : 0u);
+                    mma_ts_f16(d, ah + ks * 8, bl, IDESC_N128, 1u);
+                    mma_ts_f16(d, al + ks * 8, bh, IDESC_N128, 1u);
+                }
+                tc_commit(&S.bar_d2[b]);
+                ++q2;
+            };
+            while (q2 < n_pairs) {
+                if (ready2()) issue2();                 // oldest work first: it frees the most downstream buffers
+                if (ready1b()) issue1b();
+                if (ready1()) issue1();
+            }
+        }
+        __syncwarp();
+    } else if (warp == WLOAD_WARP) {
+        // Weight images, in the order the tensor pipe frees their buffers: after MMA1(q) retires w1(q+2) is requested,
+        // after MMA1b(q) w32(q+2), after MMA2(q) w4(q+2).  Every wait below is on an MMA that the issuing thread can
+        // reach with images requested earlier in this sequence, and the next completion of each parity barrier needs
+        // the image requested right after the wait (no phase can be missed).
+        if (elect_one()) {
+            int n_pairs = 0;
+            { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; next_pair(t); } }
+            PairCursor cw1 = first_pair(), cw32 = cw1, cw4 = cw1;       // model of the NEXT image to request, per kind
+            int l1 = 0, l32 = 0, l4 = 0;
+            auto load_w1 = [&]() {
+                const unsigned char* img = images + (size_t)cw1.m * FM_TC_IMAGE_BYTES;
+                const int b = l1 & 1;
+                mbar_expect_tx(&S.bar_w1[b], 2 * W1_BYTES);
+                bulk_load(S.w1[b], img + IMG_W1, 2 * W1_BYTES, &S.bar_w1[b]);
+                next_pair(cw1); ++l1;
+            };
+            auto load_w32 = [&]() {
+                const unsigned char* img = images + (size_t)cw32.m * FM_TC_IMAGE_BYTES;
+                const int b = l32 & 1;
+                mbar_expect_tx(&S.bar_w32[b], 2 * W32_BYTES);
+                bulk_load(S.w32[b], img + IMG_W32, 2 * W32_BYTES, &S.bar_w32[b]);
+                next_pair(cw32); ++l32;
+            };
+            auto load_w4 = [&]() {
+                const unsigned char* img = images + (size_t)cw4.m * FM_TC_IMAGE_BYTES;
+                const int b = l4 & 1;
+                mbar_expect_tx(&S.bar_w4[b], 2 * W4_BYTES);
+                bulk_load(S.w4[b], img + IMG_W4, 2 * W4_BYTES, &S.bar_w4[b]);
+                next_pair(cw4); ++l4;
+            };
+            for (int q = 0; q < 2 && q < n_pairs; ++q) { load_w1(); load_w32(); load_w4(); }
+            auto after1 = [&](int q) { if (q + 2 < n_pairs) { mbar_wait(&S.bar_d1[q & 1], (uint32_t)((q >> 1) & 1)); load_w1(); } };
+            auto after1b = [&](int q) { if (q + 2 < n_pairs) { mbar_wait(&S.bar_d1b[q & 1], (uint32_t)((q >> 1) & 1)); load_w32(); } };
+            auto after2 = [&](int q) { if (q + 2 < n_pairs) { mbar_wait(&S.bar_d2[q & 1], (uint32_t)((q >> 1) & 1)); load_w4(); } };
+            after1(0);
+            if (n_pairs > 1) after1(1);
+            after1b(0);
+            for (int g = 0; g < n_pairs; ++g) {
+                if (g + 2 < n_pairs) after1(g + 2);
+                if (g + 1 < n_pairs) after1b(g + 1);
+                after2(g);
+            }
+        }
+        __syncwarp();
+    } else if (warp == XLOAD_WARP) {
+        // fp32 tiles of the units, one ahead: the staging buffer is refilled once the parking warps and the
+        // squared-error warps both have their copy of the current tile (bar_xfree)
+        if (elect_one()) {
+            PairCursor cx = first_pair();
+            int ut = 0;
+            for (;;) {
+                mbar_expect_tx(&S.bar_x, 4u * XBLK);
+#pragma unroll
+                for (int kb = 0; kb < 4; ++kb) tma_load_2d(S.x + kb * XBLK, &xmap, kb * 32, cx.tile * TROWS, &S.bar_x);
+                next_unit(cx);
+                if (!cx.ok) break;
+                mbar_wait(&S.bar_xfree, (uint32_t)(ut & 1));
+                ++ut;
+            }
+        }
+        __syncwarp();
+    } else if (warp < 4) {
+        // ---- group A: parks tiles in TMEM, epilogues 1a (h1) and 1b (h2) of every pair ----
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 128;" ::);
+        const int r = warp * 32 + lane;
+        const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+        uint32_t v[32], hi[16], lo[16];
+        auto park_x = [&](int ut) {                   // fp32 tile -> fp16 head + remainder, one row per thread, k = 115 := 1
+            mbar_wait(&S.bar_x, (uint32_t)(ut & 1));
+            const uint32_t xb_t = lane_base + 128 * (ut & 1);
+#pragma unroll
+            for (int cb = 0; cb < 4; ++cb) {
+                const unsigned char* xb = S.x + cb * XBLK + r * 128;
+#pragma unroll
+                for (int q4 = 0; q4 < 8; ++q4) {
+                    float4 xv = *reinterpret_cast<const float4*>(xb + ((q4 ^ (r & 7)) << 4));
+                    xv.x = fminf(fmaxf(xv.x, -F16_MAX), F16_MAX); xv.y = fminf(fmaxf(xv.y, -F16_MAX), F16_MAX);
+                    xv.z = fminf(fmaxf(xv.z, -F16_MAX), F16_MAX); xv.w = fminf(fmaxf(xv.w, -F16_MAX), F16_MAX);
+                    if (cb == 3 && q4 == 4) xv.w = 1.f;                    // k = 96 + 16 + 3 = 115: the bias column
+                    split2<SWAP>(xv.x, xv.y, hi[q4 * 2], lo[q4 * 2]);
+                    split2<SWAP>(xv.z, xv.w, hi[q4 * 2 + 1], lo[q4 * 2 + 1]);
+                }
+                tmem_st16(xb_t + C_X + cb * 16, hi);
+                tmem_st16(xb_t + C_XLO + cb * 16, lo);
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            mbar_arrive(&S.bar_xt[ut & 1]);
+            mbar_arrive(&S.bar_xfree);
+        };
+        auto relu_split = [&](uint32_t col, uint64_t* bar_in, uint64_t* bar_out, uint32_t ph) {
+            mbar_wait(bar_in, ph);
+            tc_fence_after();
+            tmem_ld32(lane_base + col, v);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const float a = fminf(fmaxf(__uint_as_float(v[2 * j]), 0.f), F16_MAX);
+                const float b = fminf(fmaxf(__uint_as_float(v[2 * j + 1]), 0.f), F16_MAX);
+                split2<SWAP>(a, b, hi[j], lo[j]);
+            }
+            tmem_st16(lane_base + col, hi);            // in place: the fp16 operand replaces the fp32 accumulator it came from
+            tmem_st16(lane_base + col + 16, lo);
+            tmem_st_wait();
+            tc_fence_before();
+            mbar_arrive(bar_out);
+        };
+        auto e1 = [&](int q) { relu_split(C_D1 + 32 * (q & 1), &S.bar_d1[q & 1], &S.bar_h1[q & 1], (uint32_t)((q >> 1) & 1)); };
+        auto e1b = [&](int q) { relu_split(C_D1B + 32 * (q & 1), &S.bar_d1b[q & 1], &S.bar_h2[q & 1], (uint32_t)((q >> 1) & 1)); };
+        int n_pairs = 0, n_units_ne = 0;
+        { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; n_units_ne = t.ord + 1; next_pair(t); } }
+        // Three kinds of work, each taken in order as soon as its input is there (warp-uniform non-blocking tests):
+        //   e1(qe1)    when MMA1(qe1) has retired,   e1b(qe1b)  when MMA1b(qe1b) has retired,
+        //   park(unit) when the unit's fp32 tile has landed in the staging buffer AND its TMEM buffer (unit & 1) is free:
+        //              its last reader was MMA1 of the last pair of unit - 2, whose retirement this warp has seen once
+        //              the next e1 pair belongs to unit - 1 or later.
+        // A fixed order would deadlock on units shorter than three pairs (the next tile only lands after the
+        // squared-error warps entered the current unit, which needs e1b of its first pair).
+        PairCursor ce1 = first_pair();                // pair e1 handles next
+        int qe1 = 0, qe1b = 0, parked = 0;
+        auto uniform = [&](bool ok) -> bool { return __all_sync(0xffffffffu, ok) != 0; };
+        while (qe1b < n_pairs) {
+            bool did = false;
+            if (parked < n_units_ne && (qe1 >= n_pairs || ce1.ord >= parked - 1) &&
+                uniform(mbar_test(&S.bar_x, (uint32_t)(parked & 1)))) {
+                park_x(parked);
+                ++parked;
+                did = true;
+            }
+            if (qe1 < n_pairs && uniform(mbar_test(&S.bar_d1[qe1 & 1], (uint32_t)((qe1 >> 1) & 1)))) {
+                e1(qe1);
+                next_pair(ce1);
+                ++qe1;
+                did = true;
+            }
+            if (qe1b < qe1 && uniform(mbar_test(&S.bar_d1b[qe1b & 1], (uint32_t)((qe1b >> 1) & 1)))) {
+                e1b(qe1b);
+                ++qe1b;
+                did = true;
+            }
+            if (!did) __nanosleep(20);
+        }
+    } else {
+        // ---- group B: epilogue 2 (squared error against the row kept in registers), partial sums ----
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 208;" ::);
+        const int wq = warp & 3;
+        const int r = wq * 32 + lane;
+        const uint32_t lane_base = tmem + ((uint32_t)(wq * 32) << 16);
+        uint32_t v0[32], v1[32];
+        float2 nx[58];                              // -x of this thread's row (116 floats), for the whole unit
+        PairCursor c = first_pair();
+        int g = 0, ut = 0;
+        bool fresh = true;
+        while (c.ok) {
+            if (fresh) {
+                mbar_wait(&S.bar_x, (uint32_t)(ut & 1));
+#pragma unroll
+                for (int q = 0; q < 29; ++q) {
+                    const float4 xv = *reinterpret_cast<const float4*>(S.x + (q >> 3) * XBLK + r * 128 + (((q & 7) ^ (r & 7)) << 4));
+                    nx[q * 2] = make_float2(-xv.x, -xv.y);
+                    nx[q * 2 + 1] = make_float2(-xv.z, q == 28 ? 0.f : -xv.w);        // element 115 is padding (D2[115] == 0)
+                }
+                mbar_arrive(&S.bar_xfree);
+                fresh = false;
+            }
+            mbar_wait(&S.bar_d2[g & 1], (uint32_t)((g >> 1) & 1));
+            tc_fence_after();
+            float2 acc = make_float2(0.f, 0.f);
+            auto acc_block = [&](const uint32_t (&v)[32], int cb) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const int d2 = cb * 16 + j;       // float2 index
+                    if (d2 < 58) {
+                        const float2 e = fadd2(make_float2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])), nx[d2]);
+                        acc = ffma2(e, e, acc);
+                    }
+                }
+            };
+            tmem_ld64(lane_base + C_D2, v0, v1);
+            acc_block(v0, 0); acc_block(v1, 1);
+            tmem_ld64(lane_base + C_D2 + 64, v0, v1);
+            tc_fence_before();
+            mbar_arrive(&S.bar_d2free);               // D2 is in registers: MMA2 of the next pair may overwrite it
+            acc_block(v0, 2); acc_block(v1, 3);
+            const int row = c.tile * TROWS + r;
+            float sse = row < x_rows ? acc.x + acc.y : 0.f;
+            sse = warp_sum(sse);
+            if (lane == 0) partial[((size_t)c.m * n_tiles + c.tile) * 4 + wq] = sse;
+            PairCursor cn = c;
+            next_pair(cn);
+            if (!cn.ok || cn.i != c.i) { ++ut; fresh = true; }
+            c = cn;
+            ++g;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == MMA_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(F_TMEM_COLS));
+
+    // ---- grid-wide barrier (the grid never exceeds the SM count and a CTA fills an SM: all CTAs are resident), then
+    //      the per-model MSE from the partial sums in a fixed order ----
+    if (tid == 0) {
+        __threadfence();
+        const unsigned gen = *reinterpret_cast<volatile unsigned*>(gbar + 1);
+        const unsigned old = atomicAdd(gbar, 1u);
+        if (old == gridDim.x - 1) {
+            *reinterpret_cast<volatile unsigned*>(gbar) = 0u;
+            __threadfence();
+            atomicAdd(gbar + 1, 1u);
+        } else {
+            while (*reinterpret_cast<volatile unsigned*>(gbar + 1) == gen) __nanosleep(32);
+        }
+        __threadfence();
+    }
+    __syncthreads();
+    for (int m = blockIdx.x; m < n_models; m += gridDim.x) {
+        const float* pm = partial + (size_t)m * n_tiles * 4;
+        double s = 0.0;
+        for (int i = tid; i < n_tiles * 4; i += NT_F) s += (double)__ldcg(pm + i);
+        s = warp_sum(s);
+        if (lane == 0) S.red[warp] = s;
+        __syncthreads();
+        if (tid == 0) {
+            double t = 0.0;
+            for (int w = 0; w < NT_F / 32; ++w) t += S.red[w];
+            out_mse[owned_slots[m]] = (float)(t / ((double)x_rows * (double)D));
+        }
+        __syncthreads();
+    }
+    (void)dbg;
+}
+
+}  // namespace tcf
+}  // namespace fm
+
+namespace {
+typedef CUresult (*EncodeTiledFn3)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+int encode_x_map_f(CUtensorMap* map, const float* base, int64_t rows) {
+    static EncodeTiledFn3 fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            return (int)cudaErrorNotSupported;
+        fn = reinterpret_cast<EncodeTiledFn3>(p);
+    }
+    const cuuint64_t gdim[2] = {(cuuint64_t)fm::XP, (cuuint64_t)rows};
+    const cuuint64_t gstride[1] = {(cuuint64_t)fm::XP * sizeof(float)};
+    const cuuint32_t box[2] = {32u, (cuuint32_t)fm::tc::TROWS};
+    const cuuint32_t estride[2] = {1u, 1u};
+    return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride, box, estride,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+}
+}  // namespace
+
+extern "C" int64_t fm_score_fused_scratch_floats(int64_t x_rows, int32_t n_models) {
+    const int64_t n_tiles = (x_rows + fm::tc::TROWS - 1) / fm::tc::TROWS;
+    return n_tiles * 4 * (int64_t)(n_models > 0 ? n_models : 1);
+}
+
+extern "C" int fm_score_fused_f16(const FmFusedScoreArgs* a, void* stream) {
+    using namespace fm;
+    using namespace fm::tc;
+    using namespace fm::tcf;
+    if (a->n_slots <= 0 || a->x_rows <= 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t err = cudaMemsetAsync(a->n_owned, 0, sizeof(int), st);
+    if (err != cudaSuccess) return (int)err;
+    prep_images_f16_kernel<<<a->n_slots, 256, 0, st>>>(a->slab, a->slot_client, a->first_client, a->n_local, a->n_slots,
+                                                       a->images, a->owned_slots, a->n_owned);
+    CUtensorMap map;
+    int rc = encode_x_map_f(&map, a->X, a->x_rows);
+    if (rc) return rc;
+    static int sms = 0;
+    if (!sms) { int dev; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    const size_t smem = sizeof(FSmem);
+    static int swap_halves = -1;
+    if (swap_halves < 0) { const char* e = getenv("FM_F16_SWAP"); swap_halves = (e && e[0] == '1') ? 1 : 0; }
+    auto kern = swap_halves ? score_fused_f16_kernel<true> : score_fused_f16_kernel<false>;
+    err = cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return (int)err;
+    // chunks of models per tile: balance the units over the SMs (same cost model as score_multi_tc.cu)
+    const int n_tiles = (int)((a->x_rows + TROWS - 1) / TROWS);
+    const int m_est = a->n_slots < a->n_local ? a->n_slots : (a->n_local > 0 ? a->n_local : 1);
+    int n_chunks = 1;
+    double best = 1e30;
+    for (int c = 1; c <= 4 && c <= (m_est > 0 ? m_est : 1); ++c) {
+        const long long units = (long long)n_tiles * c;
+        const long long g = units < sms ? units : sms;
+        const double cost = (double)((units + g - 1) / g) * ((double)m_est / c + 4.0);
+        if (cost < best * 0.98) { best = cost; n_chunks = c; }
+    }
+    const long long units = (long long)n_tiles * n_chunks;
+    const int grid = (int)(units < sms ? units : sms);
+    kern<<<grid, NT_F, smem, st>>>(map, a->images, a->owned_slots, a->n_owned, (int)a->x_rows, n_chunks, a->partial,
+                                   a->out_mse, a->grid_barrier, a->dbg_cycles);
+    return (int)cudaGetLastError();
+}

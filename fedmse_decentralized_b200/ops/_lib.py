@@ -46,6 +46,12 @@ class FmMultiScoreArgs(C.Structure):
                 ("dbg_cycles", c_vp)]
 
 
+class FmFusedScoreArgs(C.Structure):
+    _fields_ = [("slab", c_vp), ("slot_client", c_vp), ("n_slots", C.c_int32), ("first_client", C.c_int32),
+                ("n_local", C.c_int32), ("X", c_vp), ("x_rows", C.c_int64), ("images", c_vp), ("owned_slots", c_vp),
+                ("n_owned", c_vp), ("partial", c_vp), ("out_mse", c_vp), ("grid_barrier", c_vp), ("dbg_cycles", c_vp)]
+
+
 TC_IMAGE_BYTES = 65536
 
 
@@ -154,6 +160,7 @@ def load() -> C.CDLL:
         ("fm_score_rows_tc", [C.POINTER(FmScoreArgs), C.c_int64, C.c_int32, c_vp, c_vp]),
         ("fm_split_residual", [c_vp, c_vp, C.c_int64, c_vp]),
         ("fm_score_multi_tc", [C.POINTER(FmMultiScoreArgs), c_vp]),
+        ("fm_score_fused_f16", [C.POINTER(FmFusedScoreArgs), c_vp]),
         ("fm_vote_normalise", [c_vp, C.c_int32, c_vp, c_vp]),
         ("fm_chunk_mean", [c_vp, C.c_int32, C.c_int32, C.c_int32, c_vp, c_vp, C.c_int32, C.c_int32,
                            C.c_int32, c_vp, c_vp]),
@@ -182,6 +189,8 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)
         fn.argtypes = argt
         fn.restype = C.c_int
+    lib.fm_score_fused_scratch_floats.argtypes = [C.c_int64, C.c_int32]
+    lib.fm_score_fused_scratch_floats.restype = C.c_int64
     lib.fm_auc_scratch_keys.argtypes = [C.c_int32]
     lib.fm_auc_scratch_keys.restype = C.c_int64
     lib.fm_vote_scores_static_error.argtypes = []

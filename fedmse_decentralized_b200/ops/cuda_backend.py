@@ -46,13 +46,16 @@ class CudaBackend:
     reads_peers = True   # merge / gossip kernels read other ranks' slabs themselves
 
     def __init__(self, layout: ParamLayout, device, score_precision: str = "fp32"):
-        if score_precision not in ("fp32", "tf32", "tf32x3"):
-            raise ValueError("score_precision must be 'fp32', 'tf32' or 'tf32x3'")
+        if score_precision not in ("fp32", "tf32", "tf32x3", "fp16x3"):
+            raise ValueError("score_precision must be 'fp32', 'tf32', 'tf32x3' or 'fp16x3'")
         # scoring forwards of merge / verify / evaluate: exact FFMA kernel, or the tcgen05 kernel (single
         # TF32 pass or error-compensated 3xTF32).  Vote scoring always uses the exact kernel: the election
         # is an argmin over nearly equal scores.
         self.score_precision = score_precision
-        self.tc = {"fp32": 0, "tf32": 1, "tf32x3": 3}[score_precision]
+        # "fp16x3": the MSE-weight scoring of the merge runs on the fused fp16 hi/lo kernel (csrc/score_fused_f16.cu,
+        # fp32-grade like 3xTF32 at twice the tensor rate); verification / evaluation forwards stay on 3xTF32.
+        self.tc = {"fp32": 0, "tf32": 1, "tf32x3": 3, "fp16x3": 3}[score_precision]
+        self.fused_f16 = score_precision == "fp16x3"
         self.tile = 128 if self.tc else TILE
         if (layout.dim, layout.hidden, layout.latent) != (115, 27, 7):
             raise ValueError("the sm_100a kernels are specialised for the 115-27-7 autoencoder; "
@@ -257,8 +260,36 @@ class CudaBackend:
         return self.agg_pos
 
     # ------------------------------------------------------------------ T2 merge
+    def _merge_scores_fused(self, st, sh, ctl: RoundControl) -> torch.Tensor:
+        """prep + ONE kernel: fp16 hi/lo tcgen05 forward of every locally owned selected model over the dev matrix,
+        per-model MSE finished in the kernel (no SSE matrix, no chunk_mean)."""
+        n, R = len(ctl.sel), self.dev_rows
+        if getattr(self, "_images", None) is None:
+            self._images = torch.empty(max(1, st.n_clients) * _lib.TC_IMAGE_BYTES, dtype=torch.uint8,
+                                       device=self.device)
+            self._owned = torch.zeros(max(1, sh.n_global) + 1, dtype=torch.int32, device=self.device)
+        if getattr(self, "_fused_partial", None) is None:
+            need = int(self.lib.fm_score_fused_scratch_floats(R, max(1, st.n_clients)))
+            self._fused_partial = torch.empty(need, dtype=torch.float32, device=self.device)
+            self._fused_gbar = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self.mse.zero_()
+        a = _lib.FmFusedScoreArgs(_ptr(st.params), _ptr(self.ctl_sel), n, sh.first_client, st.n_clients,
+                                  _ptr(sh.dev), R, _ptr(self._images), _ptr(self._owned[1:]), _ptr(self._owned[:1]),
+                                  _ptr(self._fused_partial), _ptr(self.mse), _ptr(self._fused_gbar),
+                                  _ptr(getattr(self, "mm_cycles", None)))
+        _lib.check(self.lib.fm_score_fused_f16(C.byref(a), self._stream()), "score_fused_f16")
+        self.launches += 2
+        if self.exchanges_scores:
+            return self._publish(self.mse, n, 1)
+        return self.mse[:n]
+
     def merge_scores(self, st, sh, ctl: RoundControl) -> torch.Tensor:
         n, R = len(ctl.sel), self.dev_rows
+        if self.fused_f16:
+            if getattr(self, "_dev_absmax", None) is None:       # static matrix: checked once
+                self._dev_absmax = float(sh.dev.abs().max()) if sh.dev.numel() else 0.0
+            if self._dev_absmax <= 1.0e4:                        # fp16 head + remainder cover |x| < 1.3e5 exactly enough
+                return self._merge_scores_fused(st, sh, ctl)
         if self.merge_sse is None or self.merge_sse.numel() < n * R:
             self.merge_sse = torch.zeros(n * R, dtype=torch.float32, device=self.device)
         if self.tc:

@@ -114,6 +114,27 @@ typedef struct FmMultiScoreArgs {
 } FmMultiScoreArgs;
 int fm_score_multi_tc(const FmMultiScoreArgs* args, void* stream);
 
+/* ---- MSE-weight scoring, second generation: every layer on tcgen05 with fp16 hi/lo operands ------------
+ * Same job as fm_score_multi_tc (reference: fed_mse_avg, client_trainer.py:115-130) but (1) fp16 head + fp16
+ * remainder operands, three products per GEMM, fp32 accumulation (kind::f16, twice the TF32 rate; relative error
+ * ~1e-6 like 3xTF32; operands are clamped to +-65504 first, so data beyond ~1.3e5 in magnitude loses accuracy --
+ * callers with such data use fm_score_multi_tc); (2) the 27->7->27 bottleneck as one fused 27x27 GEMM
+ * (W32 = W3 W2, no activation between the two inner layers) and all biases folded into the GEMMs;
+ * (3) out_mse[slot] = mean squared error of the slot's model over all x_rows x 115 elements is finished in the
+ * kernel (per-(model, tile) partial sums reduced in a fixed order behind a grid-wide barrier): no SSE matrix,
+ * no fm_chunk_mean.  Slots owned by other ranks are left untouched.
+ * Scratch (caller): images >= owned * FM_TC_IMAGE_BYTES bytes, owned_slots[n_slots], n_owned[1],
+ * partial[fm_score_fused_scratch_floats(x_rows, owned)] floats, grid_barrier[2] uint32 zeroed once. */
+typedef struct FmFusedScoreArgs {
+    const float* slab; const int32_t* slot_client; int32_t n_slots; int32_t first_client; int32_t n_local;
+    const float* X; int64_t x_rows;
+    unsigned char* images; int32_t* owned_slots; int32_t* n_owned;
+    float* partial; float* out_mse; uint32_t* grid_barrier;
+    unsigned long long* dbg_cycles;
+} FmFusedScoreArgs;
+int fm_score_fused_f16(const FmFusedScoreArgs* args, void* stream);
+int64_t fm_score_fused_scratch_floats(int64_t x_rows, int32_t n_models);
+
 /* Column-normalise a vote matrix: out = (V - mean) / (unbiased std + 1e-8)
  * (reference: client_trainer.py:221-223).  V and out are [rows][FM_XP]; out is caller scratch. */
 int fm_vote_normalise(const float* V, int32_t rows, float* out, void* stream);

@@ -298,6 +298,54 @@ def test_multi_model_scoring_matches_oracle(tmp_path, dev, precision, rtol):
             assert_close(mse[p], want.double().mean() / L.dim, rtol, 0, f"{precision} mse slot {p}")
 
 
+@pytest.mark.parametrize("n_clients,rows", [(12, 2400), (3, 500), (40, 700)])
+def test_fused_f16_scoring_matches_oracle(tmp_path, dev, n_clients, rows):
+    """Second-generation MSE-weight scoring (fp16 head + remainder operands on tcgen05 kind::f16, fused 27x27
+    bottleneck GEMM, in-kernel MSE reduction): per-model MSE against the fp32 oracle in double, for full, small
+    and single-model selections and for unit lengths 1..n (short units exercise the tile hand-over)."""
+    from fedmse_decentralized_b200.data import SyntheticSpec, make_clients, prepare_from_raw
+    spec = SyntheticSpec(n_normal=rows, n_abnormal=40, n_test_normal=20, jitter_rows=10)
+    clients = prepare_from_raw(make_clients(n_clients, spec, seed=11), True, seed=5)
+    cfg = make_cfg(tmp_path, epoch=1, network_size=n_clients, score_precision="fp16x3", write_latents=False,
+                   save_client_models=False)
+    eng = make_engine(cfg, make_shards(clients, dev), "hybrid", "mse_avg", "cuda")
+    be, st, sh = eng.backend, eng.state, eng.sh
+    assert be.fused_f16
+    R = be.dev_rows
+    st.params.mul_(1.0 + 0.05 * torch.randn_like(st.params))        # different models per client
+    host = st.params.cpu()
+    X = sh.dev.cpu()[:R]
+    full = list(range(n_clients))
+    random.Random(3).shuffle(full)
+    worst = 0.0
+    for sel in (full, full[:3], full[:1], full[:2]):
+        ctl = RoundControl(round=0, sel=list(sel), voter_pos=0, jitter=[1.0] * len(sel), vote_client=sel[0],
+                           verify_client=-1)
+        be.begin_round(ctl)
+        for rep in range(2):                                         # twice: the grid barrier words are reused
+            mse = be.merge_scores(st, sh, ctl)
+            torch.cuda.synchronize()
+            for p, c in enumerate(sel):
+                want = float(oracle.row_sse(host[c].double(), X.double(), L).mean() / L.dim)
+                rel = abs(float(mse[p]) - want) / want
+                worst = max(worst, rel)
+                assert rel < 1e-4, f"slot {p} client {c}: {float(mse[p])} vs {want} (rel {rel:.2e})"
+    print(f"fused f16 scoring: worst relative MSE error {worst:.2e}")
+
+
+def test_full_round_with_fused_f16_scoring(tiny_clients, tmp_path, dev):
+    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "hybrid", "mse_avg", score_precision="fp16x3",
+                         num_participants=0.7)
+    for r in range(2):
+        random.seed(60 + r); torch.manual_seed(60 + r)
+        ctl = e_ref.make_control(r)
+        res_ref = e_ref.run_round(r, copy.deepcopy(ctl))
+        res_gpu = e_gpu.run_round(r, copy.deepcopy(ctl))
+        assert res_gpu.aggregator == res_ref.aggregator
+        assert_close(e_gpu.state.params, e_ref.state.params, 3e-3, 3e-5, f"params r{r}")
+        assert_close(torch.tensor(res_gpu.client_metrics), torch.tensor(res_ref.client_metrics), 0, 2e-3, "auc")
+
+
 def test_full_round_with_tensor_core_scoring(tiny_clients, tmp_path, dev):
     e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "autoencoder", "mse_avg", score_precision="tf32x3",
                          num_participants=0.7)
