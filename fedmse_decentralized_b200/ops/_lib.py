@@ -82,6 +82,17 @@ class FmMergeArgs(C.Structure):
                 ("arrive", c_vp), ("expect", C.c_uint32), ("done_ctl", c_vp), ("done_counter", c_vp)]
 
 
+class FmMergeNvlsArgs(C.Structure):
+    _fields_ = [("slab", c_vp), ("world", C.c_int32), ("rank", C.c_int32), ("n_global", C.c_int32),
+                ("sel", c_vp), ("n_sel", C.c_int32), ("mse", c_vp), ("mode", C.c_int32), ("compat", C.c_int32),
+                ("agg_pos", c_vp), ("agg_count", c_vp), ("weights_out", c_vp), ("arrive_mse", c_vp),
+                ("expect_mse", C.c_uint32), ("partial_local", c_vp), ("mc_partial", c_vp), ("mc_theta", c_vp),
+                ("peer_ctl", c_vp), ("arrive_partial", c_vp), ("expect_partial", C.c_uint32), ("grid_counter", c_vp)]
+
+
+ARRIVE_DONE, ARRIVE_GOSSIP, ARRIVE_PARTIAL = 2, 3, 4
+
+
 class FmVerifyArgs(C.Structure):
     _fields_ = [("params", c_vp), ("anchor", c_vp), ("hist", c_vp), ("hist_perf", c_vp), ("hist_valid", c_vp),
                 ("rejected", c_vp), ("n_local", C.c_int32), ("first_client", C.c_int32), ("theta", c_vp),
@@ -170,6 +181,9 @@ def load() -> C.CDLL:
         ("fm_publish", [c_vp, c_vp, C.c_int32, C.c_int32, C.c_int32, c_vp, C.c_int32, C.c_int32, c_vp]),
         ("fm_merge", [C.POINTER(FmMergeArgs), c_vp]),
         ("fm_verify_update", [C.POINTER(FmVerifyArgs), c_vp]),
+        ("fm_merge_nvls", [C.POINTER(FmMergeNvlsArgs), c_vp]),
+        ("fm_flag_wait", [c_vp, C.c_uint32, c_vp]),
+        ("fm_nvls_allreduce_slice", [c_vp, C.c_int32, C.c_int32, C.c_int64, c_vp, C.c_uint32, c_vp, C.c_int32, c_vp, c_vp]),
         ("fm_auc", [C.POINTER(FmAucArgs), c_vp]),
         ("fm_gossip", [C.POINTER(FmGossipArgs), c_vp]),
         ("fm_gossip_publish", [c_vp, c_vp, C.c_int64, c_vp, C.c_int32, c_vp, c_vp]),

@@ -132,6 +132,7 @@ class CudaBackend:
         # multi-GPU: peer-mapped control block (score boards + arrival counters) -> no NCCL on the merge path
         self.exchanges_scores = comm.is_dist
         self.seq = [0, 0, 0]
+        self.nvls = None
         if comm.is_dist:
             from ..parallel.symmetric import SymmetricSlab
             if n_sel_max > _lib.MAX_SEL:
@@ -142,6 +143,14 @@ class CudaBackend:
             self.ctl = self.ctl_slab.tensor.view(-1)
             self.ctl_arrive_ptr = self.ctl_slab.ptr + 4 * 2 * _lib.MAX_SEL
             self.done_counter = torch.zeros(1, dtype=torch.int32, device=dev)
+            # NVLS: [partial | theta] in one symmetric buffer with a multicast view; theta then IS that buffer's
+            # second half, so verification / scoring read the switch-broadcast result in place
+            from ..parallel import nvls
+            self.nvls = nvls.allocate(comm, 2 * self.layout.padded)
+            if self.nvls is not None:
+                self.theta = self.nvls.tensor[self.layout.padded:]
+                self._nvls_counter = torch.zeros(2, dtype=torch.int32, device=dev)
+                self._nvls_seq = 0
 
     def begin_round(self, ctl: RoundControl) -> None:
         """Upload the round's control block: selection (global + local ids) and jitter."""
@@ -331,8 +340,30 @@ class CudaBackend:
             return self._publish(self.mse, n, 1)
         return self.mse[:n]
 
+    def _merge_nvls(self, st, sh, ctl: RoundControl, spec: MergeSpec, mse, agg_pos) -> torch.Tensor:
+        """Merge through the NVSwitch: local weighted partial + multimem.ld_reduce / multimem.st of this rank's slice
+        (``csrc/nvls_kernel.cu``); no selected row crosses NVLink."""
+        n, P, nv = len(ctl.sel), self.layout.padded, self.nvls
+        arrive_mse, expect_mse = self._arrive(1) if mse is not None else (0, 0)
+        self._nvls_seq += 1
+        self.seq[2] += 1
+        a = _lib.FmMergeNvlsArgs(_ptr(st.params), self.comm.world, self.comm.rank, sh.n_global, _ptr(self.ctl_sel), n,
+                                 _ptr(mse), 1 if spec.update_type in ("mse_avg", "fusion_avg") else 0,
+                                 1 if spec.compat_alias else 0, _ptr(agg_pos), _ptr(st.agg_count), _ptr(self.weights),
+                                 arrive_mse, expect_mse, nv.ptr, nv.mc_ptr, nv.mc_ptr + 4 * P, _ptr(self.ctl_slab.table),
+                                 self.ctl_arrive_ptr + 4 * _lib.ARRIVE_PARTIAL, self.comm.world * self._nvls_seq,
+                                 _ptr(self._nvls_counter))
+        _lib.check(self.lib.fm_merge_nvls(C.byref(a), self._stream()), "merge_nvls")
+        # theta is complete once every rank has stored its slice: order the stream (the verification forward reads it)
+        _lib.check(self.lib.fm_flag_wait(self.ctl_arrive_ptr + 4 * _lib.ARRIVE_DONE, self.comm.world * self.seq[2],
+                                         self._stream()), "flag_wait")
+        self.launches += 2
+        return self.theta
+
     def merge(self, st, sh, ctl: RoundControl, spec: MergeSpec, mse, agg_pos, rows=None) -> torch.Tensor:
         n = len(ctl.sel)
+        if self.nvls is not None:
+            return self._merge_nvls(st, sh, ctl, spec, mse, agg_pos)
         a = _lib.FmMergeArgs(_ptr(self.peer_table), self.comm.world, self.comm.rank, sh.n_global,
                              _ptr(self.ctl_sel), n, _ptr(mse),
                              1 if spec.update_type in ("mse_avg", "fusion_avg") else 0,

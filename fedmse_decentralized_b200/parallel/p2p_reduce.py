@@ -2,7 +2,9 @@
 
 ``P2PReducer.allreduce(rows, w)`` returns ``sum over all ranks' rows of w * row`` on every rank without
 NCCL: a local weighted partial, a reduce-scatter by pulling slices of the peers' partials, and an
-all-gather by pulling the reduced slices -- ``2 (N-1)/N * P`` bytes per GPU over NVLink.  ``pull_all``
+all-gather by pulling the reduced slices -- ``2 (N-1)/N * P`` bytes per GPU over NVLink.
+``allreduce_nvls`` does the same through the NVSwitch's multicast reduction (``multimem.ld_reduce`` /
+``multimem.st``, ``csrc/nvls_kernel.cu``) where the fabric exposes it.  ``pull_all``
 is the latency-optimal variant the 27 KB merge uses (every rank reads every row).  Buffers are
 peer-mapped slabs; ordering uses release/acquire arrival counters in a peer-mapped control block.
 """
@@ -60,6 +62,30 @@ class P2PReducer:
         _lib.check(lib.fm_slice_gather(self.reduced.table.data_ptr(), W, self.out.data_ptr(), self.P,
                                        self.arrive_ptr + 4 * 4, W * self.seq[4], s), "slice_gather")
         return self.out
+
+    def enable_nvls(self) -> bool:
+        """Collective.  Allocate the multicast-mapped partial buffer; True when the fabric supports NVLS."""
+        from . import nvls
+        if getattr(self, "nv", None) is None:
+            self.nv = nvls.allocate(self.comm, self.P)
+            self.seq_nv = {5: 0, 6: 0}
+        return self.nv is not None
+
+    def allreduce_nvls(self, w_local: torch.Tensor) -> torch.Tensor:
+        """Same result as ``allreduce`` through the NVSwitch: local weighted partial into the multicast-mapped buffer,
+        then each rank reduces its slice with ``multimem.ld_reduce`` and re-broadcasts it with ``multimem.st`` -- the
+        buffer itself holds the complete sum on every rank afterwards (no gather pass, no second buffer)."""
+        c, lib, W, nv = self.comm, self.lib, self.comm.world, self.nv
+        s = self._stream()
+        ctl_tab = self.ctl.table.data_ptr()
+        self.seq_nv[5] += 1
+        self.seq_nv[6] += 1
+        _lib.check(lib.fm_weighted_rows(self._local_ptrs.data_ptr(), w_local.data_ptr(), self.m, nv.ptr, self.P,
+                                        0, 0, ctl_tab, W, 5, self.grid_counter.data_ptr() + 8, s), "weighted_rows")
+        _lib.check(lib.fm_nvls_allreduce_slice(nv.mc_ptr, W, c.rank, self.P, self.arrive_ptr + 4 * 5, W * self.seq_nv[5],
+                                               ctl_tab, 6, self.grid_counter.data_ptr() + 12, s), "nvls_allreduce_slice")
+        _lib.check(lib.fm_flag_wait(self.arrive_ptr + 4 * 6, W * self.seq_nv[6], s), "flag_wait")
+        return nv.tensor
 
     def pull_all(self, w_all: torch.Tensor) -> torch.Tensor:
         """Every rank reads every row of every rank (rows must be complete: caller synchronises ranks first)."""

@@ -234,6 +234,38 @@ typedef struct FmMergeArgs {
 } FmMergeArgs;
 int fm_merge(const FmMergeArgs* args, void* stream);
 
+/* ---- T2 merge through NVLS (multicast reduce inside the NVSwitch) ------------------------------
+ * Same result as fm_merge on hosts whose fabric exposes multicast: every rank sums w_k * model(sel[k]) over the
+ * selected rows it OWNS into `partial_local` (a symmetric buffer, local reads only), then rank r reduces slice r of
+ * all partials with multimem.ld_reduce through `mc_partial` and writes it to every GPU with multimem.st through
+ * `mc_theta`; theta (the local view of that buffer) is complete once arrive[FM_ARRIVE_DONE] >= world * seq on
+ * this rank (fm_flag_wait orders a stream behind it; fm_verify_update waits for it anyway).
+ * Counters: arrive[FM_ARRIVE_PARTIAL] and arrive[FM_ARRIVE_DONE] of the control block of fm_publish are bumped
+ * once per call on every rank, also when nothing was elected.  grid_counter: two zeroed uint32 of scratch. */
+#define FM_ARRIVE_DONE 2
+#define FM_ARRIVE_PARTIAL 4
+typedef struct FmMergeNvlsArgs {
+    const float* slab;              /* this rank's parameter slab [n_local][P_PAD] */
+    int32_t world; int32_t rank; int32_t n_global;
+    const int32_t* sel; int32_t n_sel;
+    const float* mse; int32_t mode; int32_t compat;
+    const int32_t* agg_pos; int32_t* agg_count;
+    float* weights_out;
+    const uint32_t* arrive_mse; uint32_t expect_mse;          /* NULL for mode 0 */
+    float* partial_local;           /* [P_PAD] local view of the symmetric partial buffer */
+    const float* mc_partial;        /* multicast view of the same buffer */
+    float* mc_theta;                /* multicast view of the symmetric theta buffer */
+    float* const* peer_ctl;         /* [world] control blocks */
+    const uint32_t* arrive_partial; uint32_t expect_partial;  /* this rank's arrive[FM_ARRIVE_PARTIAL] */
+    uint32_t* grid_counter;
+} FmMergeNvlsArgs;
+int fm_merge_nvls(const FmMergeNvlsArgs* args, void* stream);
+int fm_flag_wait(const uint32_t* arrive, uint32_t expect, void* stream);
+/* wide models: in-place all-reduce of a symmetric buffer through its multicast view `mc` (rank r reduces and
+ * re-broadcasts slice r); waits for `arrive` >= expect first, bumps arrive[which] on every rank when done. */
+int fm_nvls_allreduce_slice(float* mc, int32_t world, int32_t rank, int64_t n_floats, const uint32_t* arrive,
+                            uint32_t expect, float* const* peer_ctl, int32_t which, uint32_t* grid_counter, void* stream);
+
 /* ---- T3 verification gate + model update (reference: model_verifier.py:29-99,
  * client_trainer.py:174-206).  One CTA per local client c != aggregator:
  *   perf = 1 / (1 + mean(sse rows of c) / D); first time: accept;

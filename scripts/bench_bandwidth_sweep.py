@@ -65,6 +65,12 @@ def main():
         torch.cuda.synchronize(); comm.barrier()
         got2 = red.pull_all(w_all).clone()
         torch.cuda.synchronize()
+        has_nvls = comm.is_dist and red.enable_nvls()
+        err3 = float("nan")
+        if has_nvls:
+            got3 = red.allreduce_nvls(w_loc).clone()
+            torch.cuda.synchronize(); comm.barrier()
+            err3 = float((got3 - want).abs().max() / want.abs().max())
         err = float((got - want).abs().max() / want.abs().max())
         err2 = float((got2 - want).abs().max() / want.abs().max())
 
@@ -87,6 +93,7 @@ def main():
             return red.pull_all(w_all)
 
         t_p2p = timeit(lambda: red.allreduce(w_loc), a.iters, comm)
+        t_nvls = timeit(lambda: red.allreduce_nvls(w_loc), a.iters, comm) if has_nvls else float("nan")
         t_pull = timeit(pull_all, a.iters, comm)
         t_ag = timeit(nccl_allgather, a.iters, comm)
         t_ar = timeit(nccl_allreduce, a.iters, comm)
@@ -98,6 +105,10 @@ def main():
                               "speedup_vs_nccl_allgather": round(t_ag / t_p2p, 2),
                               "speedup_vs_nccl_allreduce": round(t_ar / t_p2p, 2),
                               "nvlink_roof_ms": round(roof_ms, 4), "frac_of_nvlink_roof": round(roof_ms / t_p2p, 3),
+                              "nvls_ms": round(t_nvls, 4) if has_nvls else None,
+                              "nvls_speedup_vs_nccl_allreduce": round(t_ar / t_nvls, 2) if has_nvls else None,
+                              "nvls_frac_of_nvlink_roof": round(roof_ms / t_nvls, 3) if has_nvls else None,
+                              "max_rel_err_nvls": err3 if has_nvls else None,
                               "max_rel_err": err, "max_rel_err_pull_all": err2}))
         red.close()
         del red

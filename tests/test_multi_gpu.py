@@ -131,3 +131,5 @@ def test_p2p_weighted_allreduce_matches_nccl(tmp_path):
     assert len(lines) == 2
     for l in lines:
         assert l["max_rel_err"] < 1e-5 and l["max_rel_err_pull_all"] < 1e-5 and l["gpus"] == world
+        # NVLS (multimem.ld_reduce / multimem.st) where the fabric exposes multicast; None = fell back
+        assert l["max_rel_err_nvls"] is None or l["max_rel_err_nvls"] < 1e-5
