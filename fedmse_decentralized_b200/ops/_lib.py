@@ -34,6 +34,23 @@ class FmTrainArgs(C.Structure):
                 ("fedprox_mu", C.c_float), ("phase_cycles", c_vp)]
 
 
+class FmTrainGenericArgs(C.Structure):
+    _fields_ = [("params", c_vp), ("adam_m", c_vp), ("adam_v", c_vp), ("adam_t", c_vp), ("anchor", c_vp),
+                ("best", c_vp), ("loss_log", c_vp), ("epochs_run", c_vp), ("trained_rounds", c_vp),
+                ("x_train", c_vp), ("train_off", c_vp), ("x_valid", c_vp), ("valid_off", c_vp),
+                ("sel_local", c_vp), ("n_sel", C.c_int32), ("first_client", C.c_int32),
+                ("epochs", C.c_int32), ("batch", C.c_int32), ("patience", C.c_int32),
+                ("log_stride", C.c_int32), ("lr", C.c_float), ("shrink_lambda", C.c_float),
+                ("fedprox_mu", C.c_float), ("dim", C.c_int32), ("hidden", C.c_int32), ("latent", C.c_int32),
+                ("scratch", c_vp), ("scratch_stride", C.c_int64)]
+
+
+class FmScoreGenericArgs(C.Structure):
+    _fields_ = [("slab", c_vp), ("slot_client", c_vp), ("first_client", C.c_int32), ("n_local", C.c_int32),
+                ("X", c_vp), ("tiles", c_vp), ("n_tiles", C.c_int32), ("out_sse", c_vp), ("out_lat", c_vp),
+                ("lat_pitch", C.c_int32), ("dim", C.c_int32), ("hidden", C.c_int32), ("latent", C.c_int32)]
+
+
 class FmScoreArgs(C.Structure):
     _fields_ = [("slab", c_vp), ("slot_client", c_vp), ("first_client", C.c_int32), ("n_local", C.c_int32),
                 ("X", c_vp), ("tiles", c_vp), ("n_tiles", C.c_int32), ("out_sse", c_vp), ("out_lat", c_vp)]
@@ -167,6 +184,8 @@ def load() -> C.CDLL:
     lib = C.CDLL(LIB_PATH)
     for name, argt in (
         ("fm_train_clients", [C.POINTER(FmTrainArgs), c_vp]),
+        ("fm_train_generic", [C.POINTER(FmTrainGenericArgs), c_vp]),
+        ("fm_score_generic", [C.POINTER(FmScoreGenericArgs), c_vp]),
         ("fm_score_rows", [C.POINTER(FmScoreArgs), c_vp]),
         ("fm_score_rows_tc", [C.POINTER(FmScoreArgs), C.c_int64, C.c_int32, c_vp, c_vp]),
         ("fm_split_residual", [c_vp, c_vp, C.c_int64, c_vp]),
@@ -205,6 +224,8 @@ def load() -> C.CDLL:
         fn.restype = C.c_int
     lib.fm_score_fused_scratch_floats.argtypes = [C.c_int64, C.c_int32]
     lib.fm_score_fused_scratch_floats.restype = C.c_int64
+    lib.fm_train_generic_scratch_floats.argtypes = [C.c_int32] * 4
+    lib.fm_train_generic_scratch_floats.restype = C.c_int64
     lib.fm_auc_scratch_keys.argtypes = [C.c_int32]
     lib.fm_auc_scratch_keys.restype = C.c_int64
     lib.fm_vote_scores_static_error.argtypes = []

@@ -220,6 +220,11 @@ class CudaBackend:
         st.epochs_run.zero_()
         if n == 0:
             return
+        if hp.batch_size > 32:      # thesis setting (batch 64): beyond the shared-memory budget of the persistent kernel
+            from .generic_backend import generic_train
+            generic_train(self.lib, self.layout, st, sh, self.ctl_sel_local, n, hp, self._stream(), self)
+            self.launches += 1
+            return
         a = _lib.FmTrainArgs(
             _ptr(st.params), _ptr(st.adam_m), _ptr(st.adam_v), _ptr(st.adam_t), _ptr(st.anchor), _ptr(st.best),
             _ptr(st.loss_log), _ptr(st.epochs_run), _ptr(st.trained_rounds),

@@ -84,6 +84,10 @@ def make_backend(name: str, layout: ParamLayout, device: torch.device, score_pre
     if name == "oracle":
         return OracleBackend(layout, device)
     if name == "cuda":
+        if (layout.dim, layout.hidden, layout.latent) != (115, 27, 7):
+            # widened / narrowed autoencoders: shape-generic kernels (the specialised ones are laid out for 115-27-7)
+            from ..ops.generic_backend import GenericCudaBackend
+            return GenericCudaBackend(layout, device)
         from ..ops.cuda_backend import CudaBackend
         return CudaBackend(layout, device, score_precision)
     raise ValueError(f"unknown backend {name!r}")

@@ -65,6 +65,37 @@ typedef struct FmTrainArgs {
 } FmTrainArgs;
 int fm_train_clients(const FmTrainArgs* args, void* stream);
 
+/* ---- shape-generic training / scoring (any dim <= FM_XP, hidden, latent; batch <= 4096) ---------
+ * The general path behind the specialised kernels: same math and update order as fm_train_clients /
+ * fm_score_rows (reference: client_trainer.py:360-419; the models' hidden_neus / latent_dim arguments,
+ * Shrink_Autoencoder.py:125-127), parameters laid out as layout.py packs them for (dim, hidden, latent),
+ * rows of [C][P_PAD(dim, hidden, latent)].  One CTA per client; weights, moments and activations stay in global
+ * memory, so nothing limits the width (the scoring kernel keeps 16 rows of activations in shared memory and
+ * serves hidden widths up to ~1,500).  scratch: n_sel * scratch_stride floats with
+ * scratch_stride >= fm_train_generic_scratch_floats(dim, hidden, latent, batch). */
+typedef struct FmTrainGenericArgs {
+    float* params; float* adam_m; float* adam_v; int32_t* adam_t; const float* anchor; float* best;
+    float* loss_log; int32_t* epochs_run; int32_t* trained_rounds;
+    const float* x_train; const int32_t* train_off; const float* x_valid; const int32_t* valid_off;
+    const int32_t* sel_local; int32_t n_sel; int32_t first_client;
+    int32_t epochs; int32_t batch; int32_t patience; int32_t log_stride;
+    float lr; float shrink_lambda; float fedprox_mu;
+    int32_t dim; int32_t hidden; int32_t latent;
+    float* scratch; int64_t scratch_stride;
+} FmTrainGenericArgs;
+int fm_train_generic(const FmTrainGenericArgs* args, void* stream);
+int64_t fm_train_generic_scratch_floats(int32_t dim, int32_t hidden, int32_t latent, int32_t batch);
+
+/* tiles[n_tiles][4] = {slot, row0, nrows (<= 16), out0} as for fm_score_rows; out_sse[out0 + r] and / or
+ * out_lat[(out0 + r) * lat_pitch + i] are written for slots whose client is local. */
+typedef struct FmScoreGenericArgs {
+    const float* slab; const int32_t* slot_client; int32_t first_client; int32_t n_local;
+    const float* X; const int32_t* tiles; int32_t n_tiles;
+    float* out_sse; float* out_lat; int32_t lat_pitch;
+    int32_t dim; int32_t hidden; int32_t latent;
+} FmScoreGenericArgs;
+int fm_score_generic(const FmScoreGenericArgs* args, void* stream);
+
 /* ---- row scoring forward (shared by T2 vote/merge scoring, T3 verification, T4 evaluation) --
  * For every tile {slot, row0, nrows<=64, out0}: run the model of `slot` over rows
  * X[row0 .. row0+nrows) and write per-row sum of squared reconstruction error to
