@@ -285,6 +285,10 @@ def run_ours(args):
                                     f"{args.topology} neighbours (k={args.topology_k}) weighted by MSE on its own validation "
                                     f"rows, verifies, all clients evaluated (BASELINE.json config 4)"),
                        "aggregation": args.aggregation, "topology": args.topology if args.aggregation == "gossip" else None,
+                       "merge_path": ("gossip kernel (one fetch per neighbour row, peer arrival counters)" if args.aggregation == "gossip"
+                                      else "single GPU (local rows)" if comm.world == 1
+                                      else "NVLS multimem.ld_reduce / multimem.st" if getattr(eng.backend, "nvls", None) is not None
+                                      else "P2P pull over NVLink (no multicast on this fabric)"),
                        "clients": n_global, "clients_per_gpu": args.clients_per_gpu,
                        "global_batch": 12, "seq_len": 115, "epochs": args.epochs, "local_patience": 1,
                        "participation": args.participation, "lr": 1e-3, "shrink_lambda": 5,
@@ -398,7 +402,7 @@ def main():
     ap.add_argument("--check", action="store_true",
                     help="no timing: run the scenario on the N ranks and on one GPU and assert equal results")
     ap.add_argument("--check-rounds", type=int, default=3)
-    ap.add_argument("--score-precision", default="tf32x3", choices=["fp32", "tf32", "tf32x3", "fp16x3"],
+    ap.add_argument("--score-precision", default="fp16x3", choices=["fp32", "tf32", "tf32x3", "fp16x3"],
                     help="scoring forwards: exact FFMA kernel, single-pass TF32 or error-compensated 3xTF32 on tcgen05")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)   # timing rule: at least 3 warm-up steps, both arms

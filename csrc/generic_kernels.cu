@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(GNT) score_generic_kernel(const FmScoreGeneric
 }  // namespace fm
 
 extern "C" int64_t fm_train_generic_scratch_floats(int32_t dim, int32_t hidden, int32_t latent, int32_t batch) {
-    return (int64_t)batch * (3 * (int64_t)hidden + 2 * (int64_t)latent + dim + 1) + 32;
+    return (int64_t)batch * (4 * (int64_t)hidden + 2 * (int64_t)latent + dim + 1) + 32;   // h1 h2 dp2 dp1 | z dz | dX | znorm
 }
 
 extern "C" int fm_train_generic(const FmTrainGenericArgs* a, void* stream) {
