@@ -17,11 +17,13 @@
 //  * Biases ride in the GEMMs: the parked tile gets a constant-one column (k = 115), W1 carries b1 in that column
 //    and a pass-through row that makes h1[27] = 1, W32 carries b32 in column 27 and passes the one on, W4 carries
 //    b4 in column 27.  The epilogues between the GEMMs are ReLU + fp16 split only, no tables, no FMAs.
-//  * X (hi/lo) is double buffered in TMEM, so the next tile is parked while the current one is still being read.
+//  * Four pairs are in flight per stage (rings of four D1 / D1b accumulators in TMEM): the MMA -> epilogue -> MMA round
+//    trips are ~2 pair-times long, with two buffers the tensor pipe idled half of the time.  The parked tile is single
+//    buffered in exchange (a unit boundary costs one parking, ~3 % at 62 models per unit).
 //  * No [models x rows] SSE matrix: each epilogue warp writes one partial sum per (model, tile); after a grid-wide
 //    barrier the CTAs reduce them in a fixed order to the per-model MSE (deterministic, replaces chunk_mean).
 //
-// TMEM map (512 columns): X[u&1] hi 128u..+63, lo +64..+127 | D1/h1[b] 256+32b | D1b/h2[b] 320+32b | D2 384..511.
+// TMEM map (512 columns): X hi 0..63, lo 64..127 | D1/h1[r] 128+32r | D1b/h2[r] 256+32r (r = pair mod 4) | D2 384..511.
 // Warp roles: 0-3 epilogues 1a/1b + tile parking, 4-7 epilogue 2 (squared error), 8 MMA issue, 9 weight images,
 // 10 X tiles (TMA).
 //
@@ -40,7 +42,8 @@ using namespace fm::tc;
 constexpr int NT_F = 352;
 constexpr int MMA_WARP = 8, WLOAD_WARP = 9, XLOAD_WARP = 10;
 constexpr int F_TMEM_COLS = 512;
-constexpr int C_X = 0, C_XLO = 64, C_D1 = 256, C_D1B = 320, C_D2 = 384;     // X buffer u at 128 * u
+constexpr int NB = 4;                                     // ring depth of the D1 / D1b accumulators (pairs in flight per stage)
+constexpr int C_X = 0, C_XLO = 64, C_D1 = 128, C_D1B = 256, C_D2 = 384;     // D1[b] = 128 + 32 b, D1b[b] = 256 + 32 b
 // operand image of one model (bytes).  K-major, 128-B swizzle, 64 fp16 per 128-B row (short K is zero padded).
 constexpr int W1_BYTES = 2 * 4096;          // [32 n][128 k]  = two K-blocks of 32 rows x 128 B
 constexpr int W32_BYTES = 4096;             // [32 n][32 k]   (k 32..63 zero)
@@ -55,8 +58,8 @@ struct FSmem {
     alignas(1024) unsigned char w1[2][2 * W1_BYTES];         // hi | lo
     alignas(1024) unsigned char w32[2][2 * W32_BYTES];
     alignas(1024) unsigned char w4[2][2 * W4_BYTES];
-    alignas(8) uint64_t bar_x, bar_xfree, bar_xt[2], bar_w1[2], bar_w32[2], bar_w4[2], bar_d1[2], bar_h1[2], bar_d1b[2],
-        bar_h2[2], bar_d2[2], bar_d2free;
+    alignas(8) uint64_t bar_x, bar_xfree, bar_xt, bar_w1[2], bar_w32[2], bar_w4[2], bar_d1[NB], bar_h1[NB], bar_d1b[NB],
+        bar_h2[NB], bar_d2[2], bar_d2free;
     uint32_t tmem_base;
     double red[12];
 };
@@ -88,14 +91,30 @@ __device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
     return ok != 0;
 }
 // (a, b) -> packed fp16 heads (a in the low half: element k of an A row sits in bits [15:0] of column k / 2 when k is
-// even) and packed fp16 remainders
+// even) and packed fp16 remainders.  The converts saturate at +-65504, so the remainder absorbs what the head cannot hold.
+__device__ __forceinline__ uint32_t pack_f16x2_sat(float lo_half, float hi_half) {
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_half), "f"(lo_half));
+    return r;
+}
+__device__ __forceinline__ uint32_t pack_f16x2_relu_sat(float lo_half, float hi_half) {
+    uint32_t r;
+    asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_half), "f"(lo_half));
+    return r;
+}
 template <bool SWAP>
 __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
-    const __half2 h = SWAP ? __floats2half2_rn(b, a) : __floats2half2_rn(a, b);
-    const float2 f = __half22float2(h);
-    const __half2 l = SWAP ? __floats2half2_rn(b - f.x, a - f.y) : __floats2half2_rn(a - f.x, b - f.y);
-    hi = *reinterpret_cast<const uint32_t*>(&h);
-    lo = *reinterpret_cast<const uint32_t*>(&l);
+    hi = SWAP ? pack_f16x2_sat(b, a) : pack_f16x2_sat(a, b);
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&hi));      // f.x = low half
+    lo = SWAP ? pack_f16x2_sat(b - f.x, a - f.y) : pack_f16x2_sat(a - f.x, b - f.y);
+}
+// the same for relu(a), relu(b): one convert does ReLU + saturation + packing
+template <bool SWAP>
+__device__ __forceinline__ void split2_relu(float a, float b, uint32_t& hi, uint32_t& lo) {
+    hi = SWAP ? pack_f16x2_relu_sat(b, a) : pack_f16x2_relu_sat(a, b);
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+    const float ra = fmaxf(a, 0.f), rb = fmaxf(b, 0.f);
+    lo = SWAP ? pack_f16x2_sat(rb - f.x, ra - f.y) : pack_f16x2_sat(ra - f.x, rb - f.y);
 }
 __device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
     unsigned long long ra, rb, rd;
@@ -188,11 +207,12 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
     auto next_pair = [&](PairCursor& c) { if (++c.m >= c.m1) next_unit(c); };
 
     if (tid == 0) {
-        mbar_init(&S.bar_x, 1); mbar_init(&S.bar_xfree, 256); mbar_init(&S.bar_d2free, 128);
+        mbar_init(&S.bar_x, 1); mbar_init(&S.bar_xfree, 256); mbar_init(&S.bar_d2free, 128); mbar_init(&S.bar_xt, 128);
         for (int b = 0; b < 2; ++b) {
-            mbar_init(&S.bar_xt[b], 128); mbar_init(&S.bar_w1[b], 1); mbar_init(&S.bar_w32[b], 1); mbar_init(&S.bar_w4[b], 1);
-            mbar_init(&S.bar_d1[b], 1); mbar_init(&S.bar_d1b[b], 1); mbar_init(&S.bar_d2[b], 1);
-            mbar_init(&S.bar_h1[b], 128); mbar_init(&S.bar_h2[b], 128);
+            mbar_init(&S.bar_w1[b], 1); mbar_init(&S.bar_w32[b], 1); mbar_init(&S.bar_w4[b], 1); mbar_init(&S.bar_d2[b], 1);
+        }
+        for (int b = 0; b < NB; ++b) {
+            mbar_init(&S.bar_d1[b], 1); mbar_init(&S.bar_d1b[b], 1); mbar_init(&S.bar_h1[b], 128); mbar_init(&S.bar_h2[b], 128);
         }
         fence_mbar_init();
     }
@@ -218,9 +238,11 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             // issued as soon as its inputs are there (non-blocking barrier tests), so the steady-state order
             // ... MMA1(g+2) MMA1b(g+1) MMA2(g) ... emerges by itself and a unit boundary (MMA1 of the next unit waits
             // for its tile) never blocks the MMAs that the tile's arrival depends on -- units of any length are safe.
-            // Buffer reuse is covered by issue order (the tensor pipe executes in order): MMA1(q) overwrites D1[q&1]
-            // only after MMA1b(q-2), its last reader, was issued (q1 <= q1b + 1); MMA1b(q) overwrites D1b[q&1] only
-            // after MMA2(q-2) was issued (q1b <= q2 + 1); MMA2 waits for epilogue 2 to have copied D2 out.
+            // Buffer reuse is covered by issue order (the tensor pipe executes in order): MMA1(q) overwrites D1[q % NB]
+            // only after MMA1b(q - NB), its last reader, was issued (q1 <= q1b + NB - 1); MMA1b(q) overwrites
+            // D1b[q % NB] only after MMA2(q - NB) was issued (q1b <= q2 + NB - 1); MMA2 waits for epilogue 2 to have
+            // copied D2 out.  NB = 4 pairs in flight per stage cover the MMA -> epilogue -> MMA round trips (with two
+            // the tensor pipe idled half of the time: ncu of the first version).
             // Parity safety: every barrier tested here completes its next phase only after work that this thread
             // issues after having seen the current one.
             PairCursor c1 = first_pair();
@@ -228,16 +250,16 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             int n_pairs = 0;
             { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; next_pair(t); } }
             auto ready1 = [&]() -> bool {
-                if (q1 >= n_pairs || q1 > q1b + 1) return false;
+                if (q1 >= n_pairs || q1 > q1b + (NB - 1)) return false;
                 if (!mbar_test(&S.bar_w1[q1 & 1], (uint32_t)((q1 >> 1) & 1))) return false;
-                if (c1.ord != unit1 && !mbar_test(&S.bar_xt[c1.ord & 1], (uint32_t)((c1.ord >> 1) & 1))) return false;
+                if (c1.ord != unit1 && !mbar_test(&S.bar_xt, (uint32_t)(c1.ord & 1))) return false;
                 return true;
             };
-            auto issue1 = [&]() {                       // MMA1(q1): D1[b] = X[u] . W1^T  (3 x 8 k-steps)
-                const int b = q1 & 1, ub = c1.ord & 1;
+            auto issue1 = [&]() {                       // MMA1(q1): D1[r] = X . W1^T  (3 x 8 k-steps)
+                const int b = q1 & 1, rb = q1 & (NB - 1);
                 unit1 = c1.ord;
                 tc_fence_after();
-                const uint32_t d1 = tmem + C_D1 + 32 * b, xh = tmem + 128 * ub + C_X, xl = tmem + 128 * ub + C_XLO;
+                const uint32_t d1 = tmem + C_D1 + 32 * rb, xh = tmem + C_X, xl = tmem + C_XLO;
 #pragma unroll
                 for (int kk = 0; kk < 8; ++kk) {
                     const uint64_t bh = dw1[b] + (uint64_t)(((kk >> 2) * 4096 + (kk & 3) * 32) >> 4);
@@ -246,19 +268,19 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     mma_ts_f16(d1, xh + kk * 8, bl, IDESC_N32, 1u);
                     mma_ts_f16(d1, xl + kk * 8, bh, IDESC_N32, 1u);
                 }
-                tc_commit(&S.bar_d1[b]);
+                tc_commit(&S.bar_d1[rb]);
                 next_pair(c1);
                 ++q1;
             };
             auto ready1b = [&]() -> bool {
-                if (q1b >= q1 || q1b > q2 + 1) return false;
-                const uint32_t ph = (uint32_t)((q1b >> 1) & 1);
-                return mbar_test(&S.bar_h1[q1b & 1], ph) && mbar_test(&S.bar_w32[q1b & 1], ph);
+                if (q1b >= q1 || q1b > q2 + (NB - 1)) return false;
+                return mbar_test(&S.bar_h1[q1b & (NB - 1)], (uint32_t)((q1b / NB) & 1)) &&
+                       mbar_test(&S.bar_w32[q1b & 1], (uint32_t)((q1b >> 1) & 1));
             };
-            auto issue1b = [&]() {                      // MMA1b(q1b): D1b[b] = h1[b] . W32^T  (3 x 2 k-steps)
-                const int b = q1b & 1;
+            auto issue1b = [&]() {                      // MMA1b(q1b): D1b[r] = h1[r] . W32^T  (3 x 2 k-steps)
+                const int b = q1b & 1, rb = q1b & (NB - 1);
                 tc_fence_after();
-                const uint32_t d = tmem + C_D1B + 32 * b, ah = tmem + C_D1 + 32 * b, al = ah + 16;
+                const uint32_t d = tmem + C_D1B + 32 * rb, ah = tmem + C_D1 + 32 * rb, al = ah + 16;
 #pragma unroll
                 for (int ks = 0; ks < 2; ++ks) {
                     const uint64_t bh = dw32[b] + (uint64_t)((ks * 32) >> 4), bl = bh + (uint64_t)(W32_BYTES >> 4);
@@ -266,19 +288,19 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     mma_ts_f16(d, ah + ks * 8, bl, IDESC_N32, 1u);
                     mma_ts_f16(d, al + ks * 8, bh, IDESC_N32, 1u);
                 }
-                tc_commit(&S.bar_d1b[b]);
+                tc_commit(&S.bar_d1b[rb]);
                 ++q1b;
             };
             auto ready2 = [&]() -> bool {
                 if (q2 >= q1b) return false;
-                const uint32_t ph = (uint32_t)((q2 >> 1) & 1);
-                if (!mbar_test(&S.bar_h2[q2 & 1], ph) || !mbar_test(&S.bar_w4[q2 & 1], ph)) return false;
+                if (!mbar_test(&S.bar_h2[q2 & (NB - 1)], (uint32_t)((q2 / NB) & 1)) ||
+                    !mbar_test(&S.bar_w4[q2 & 1], (uint32_t)((q2 >> 1) & 1))) return false;
                 return q2 == 0 || mbar_test(&S.bar_d2free, (uint32_t)((q2 - 1) & 1));   // epilogue 2 (q2 - 1) holds D2 in registers
             };
-            auto issue2 = [&]() {                       // MMA2(q2): D2 = h2[b] . W4^T  (3 x 2 k-steps)
-                const int b = q2 & 1;
+            auto issue2 = [&]() {                       // MMA2(q2): D2 = h2[r] . W4^T  (3 x 2 k-steps)
+                const int b = q2 & 1, rb = q2 & (NB - 1);
                 tc_fence_after();
-                const uint32_t d = tmem + C_D2, ah = tmem + C_D1B + 32 * b, al = ah + 16;
+                const uint32_t d = tmem + C_D2, ah = tmem + C_D1B + 32 * rb, al = ah + 16;
 #pragma unroll
                 for (int ks = 0; ks < 2; ++ks) {
                     const uint64_t bh = dw4[b] + (uint64_t)((ks * 32) >> 4), bl = bh + (uint64_t)(W4_BYTES >> 4);
@@ -297,10 +319,10 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         }
         __syncwarp();
     } else if (warp == WLOAD_WARP) {
-        // Weight images, in the order the tensor pipe frees their buffers: after MMA1(q) retires w1(q+2) is requested,
-        // after MMA1b(q) w32(q+2), after MMA2(q) w4(q+2).  Every wait below is on an MMA that the issuing thread can
-        // reach with images requested earlier in this sequence, and the next completion of each parity barrier needs
-        // the image requested right after the wait (no phase can be missed).
+        // Weight images: after MMA1(q) retires w1(q+2) is requested, after MMA1b(q) w32(q+2), after MMA2(q) w4(q+2).
+        // Two buffers per kind suffice whatever the accumulator ring depth: the MMAs of one kind execute one after
+        // the other, so a buffer is busy only from its load to the retirement of its MMA.  The next completion of
+        // every barrier tested here needs the image requested right after the test succeeded (no phase is missed).
         if (elect_one()) {
             int n_pairs = 0;
             { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; next_pair(t); } }
@@ -327,17 +349,12 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                 bulk_load(S.w4[b], img + IMG_W4, 2 * W4_BYTES, &S.bar_w4[b]);
                 next_pair(cw4); ++l4;
             };
-            for (int q = 0; q < 2 && q < n_pairs; ++q) { load_w1(); load_w32(); load_w4(); }
-            auto after1 = [&](int q) { if (q + 2 < n_pairs) { mbar_wait(&S.bar_d1[q & 1], (uint32_t)((q >> 1) & 1)); load_w1(); } };
-            auto after1b = [&](int q) { if (q + 2 < n_pairs) { mbar_wait(&S.bar_d1b[q & 1], (uint32_t)((q >> 1) & 1)); load_w32(); } };
-            auto after2 = [&](int q) { if (q + 2 < n_pairs) { mbar_wait(&S.bar_d2[q & 1], (uint32_t)((q >> 1) & 1)); load_w4(); } };
-            after1(0);
-            if (n_pairs > 1) after1(1);
-            after1b(0);
-            for (int g = 0; g < n_pairs; ++g) {
-                if (g + 2 < n_pairs) after1(g + 2);
-                if (g + 1 < n_pairs) after1b(g + 1);
-                after2(g);
+            // image l of a kind goes into buffer l & 1 once the MMA that read image l - 2 has retired; the three kinds
+            // advance independently (non-blocking tests), so a slow stage never holds back the loads of another
+            while (l1 < n_pairs || l32 < n_pairs || l4 < n_pairs) {
+                if (l1 < n_pairs && (l1 < 2 || mbar_test(&S.bar_d1[(l1 - 2) & (NB - 1)], (uint32_t)(((l1 - 2) / NB) & 1)))) load_w1();
+                if (l32 < n_pairs && (l32 < 2 || mbar_test(&S.bar_d1b[(l32 - 2) & (NB - 1)], (uint32_t)(((l32 - 2) / NB) & 1)))) load_w32();
+                if (l4 < n_pairs && (l4 < 2 || mbar_test(&S.bar_d2[(l4 - 2) & 1], (uint32_t)(((l4 - 2) >> 1) & 1)))) load_w4();
             }
         }
         __syncwarp();
@@ -366,15 +383,13 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         uint32_t v[32], hi[16], lo[16];
         auto park_x = [&](int ut) {                   // fp32 tile -> fp16 head + remainder, one row per thread, k = 115 := 1
             mbar_wait(&S.bar_x, (uint32_t)(ut & 1));
-            const uint32_t xb_t = lane_base + 128 * (ut & 1);
+            const uint32_t xb_t = lane_base;
 #pragma unroll
             for (int cb = 0; cb < 4; ++cb) {
                 const unsigned char* xb = S.x + cb * XBLK + r * 128;
 #pragma unroll
                 for (int q4 = 0; q4 < 8; ++q4) {
                     float4 xv = *reinterpret_cast<const float4*>(xb + ((q4 ^ (r & 7)) << 4));
-                    xv.x = fminf(fmaxf(xv.x, -F16_MAX), F16_MAX); xv.y = fminf(fmaxf(xv.y, -F16_MAX), F16_MAX);
-                    xv.z = fminf(fmaxf(xv.z, -F16_MAX), F16_MAX); xv.w = fminf(fmaxf(xv.w, -F16_MAX), F16_MAX);
                     if (cb == 3 && q4 == 4) xv.w = 1.f;                    // k = 96 + 16 + 3 = 115: the bias column
                     split2<SWAP>(xv.x, xv.y, hi[q4 * 2], lo[q4 * 2]);
                     split2<SWAP>(xv.z, xv.w, hi[q4 * 2 + 1], lo[q4 * 2 + 1]);
@@ -384,7 +399,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             }
             tmem_st_wait();
             tc_fence_before();
-            mbar_arrive(&S.bar_xt[ut & 1]);
+            mbar_arrive(&S.bar_xt);
             mbar_arrive(&S.bar_xfree);
         };
         auto relu_split = [&](uint32_t col, uint64_t* bar_in, uint64_t* bar_out, uint32_t ph) {
@@ -392,26 +407,22 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             tc_fence_after();
             tmem_ld32(lane_base + col, v);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const float a = fminf(fmaxf(__uint_as_float(v[2 * j]), 0.f), F16_MAX);
-                const float b = fminf(fmaxf(__uint_as_float(v[2 * j + 1]), 0.f), F16_MAX);
-                split2<SWAP>(a, b, hi[j], lo[j]);
-            }
+            for (int j = 0; j < 16; ++j) split2_relu<SWAP>(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]), hi[j], lo[j]);
             tmem_st16(lane_base + col, hi);            // in place: the fp16 operand replaces the fp32 accumulator it came from
             tmem_st16(lane_base + col + 16, lo);
             tmem_st_wait();
             tc_fence_before();
             mbar_arrive(bar_out);
         };
-        auto e1 = [&](int q) { relu_split(C_D1 + 32 * (q & 1), &S.bar_d1[q & 1], &S.bar_h1[q & 1], (uint32_t)((q >> 1) & 1)); };
-        auto e1b = [&](int q) { relu_split(C_D1B + 32 * (q & 1), &S.bar_d1b[q & 1], &S.bar_h2[q & 1], (uint32_t)((q >> 1) & 1)); };
+        auto e1 = [&](int q) { const int rb = q & (NB - 1); relu_split(C_D1 + 32 * rb, &S.bar_d1[rb], &S.bar_h1[rb], (uint32_t)((q / NB) & 1)); };
+        auto e1b = [&](int q) { const int rb = q & (NB - 1); relu_split(C_D1B + 32 * rb, &S.bar_d1b[rb], &S.bar_h2[rb], (uint32_t)((q / NB) & 1)); };
         int n_pairs = 0, n_units_ne = 0;
         { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; n_units_ne = t.ord + 1; next_pair(t); } }
         // Three kinds of work, each taken in order as soon as its input is there (warp-uniform non-blocking tests):
         //   e1(qe1)    when MMA1(qe1) has retired,   e1b(qe1b)  when MMA1b(qe1b) has retired,
-        //   park(unit) when the unit's fp32 tile has landed in the staging buffer AND its TMEM buffer (unit & 1) is free:
-        //              its last reader was MMA1 of the last pair of unit - 2, whose retirement this warp has seen once
-        //              the next e1 pair belongs to unit - 1 or later.
+        //   park(unit) when the unit's fp32 tile has landed in the staging buffer AND the X columns of TMEM are free:
+        //              their last reader was MMA1 of the last pair of unit - 1, whose retirement this warp has seen once
+        //              the next e1 pair belongs to this unit (or there is none left).
         // A fixed order would deadlock on units shorter than three pairs (the next tile only lands after the
         // squared-error warps entered the current unit, which needs e1b of its first pair).
         PairCursor ce1 = first_pair();                // pair e1 handles next
@@ -419,19 +430,19 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         auto uniform = [&](bool ok) -> bool { return __all_sync(0xffffffffu, ok) != 0; };
         while (qe1b < n_pairs) {
             bool did = false;
-            if (parked < n_units_ne && (qe1 >= n_pairs || ce1.ord >= parked - 1) &&
+            if (parked < n_units_ne && (qe1 >= n_pairs || ce1.ord >= parked) &&
                 uniform(mbar_test(&S.bar_x, (uint32_t)(parked & 1)))) {
                 park_x(parked);
                 ++parked;
                 did = true;
             }
-            if (qe1 < n_pairs && uniform(mbar_test(&S.bar_d1[qe1 & 1], (uint32_t)((qe1 >> 1) & 1)))) {
+            if (qe1 < n_pairs && uniform(mbar_test(&S.bar_d1[qe1 & (NB - 1)], (uint32_t)((qe1 / NB) & 1)))) {
                 e1(qe1);
                 next_pair(ce1);
                 ++qe1;
                 did = true;
             }
-            if (qe1b < qe1 && uniform(mbar_test(&S.bar_d1b[qe1b & 1], (uint32_t)((qe1b >> 1) & 1)))) {
+            if (qe1b < qe1 && uniform(mbar_test(&S.bar_d1b[qe1b & (NB - 1)], (uint32_t)((qe1b / NB) & 1)))) {
                 e1b(qe1b);
                 ++qe1b;
                 did = true;
@@ -463,14 +474,14 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             }
             mbar_wait(&S.bar_d2[g & 1], (uint32_t)((g >> 1) & 1));
             tc_fence_after();
-            float2 acc = make_float2(0.f, 0.f);
-            auto acc_block = [&](const uint32_t (&v)[32], int cb) {
+            float2 acc[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+            auto acc_block = [&](const uint32_t (&v)[32], int cb) {       // four independent chains: the FMAs pipeline
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
                     const int d2 = cb * 16 + j;       // float2 index
                     if (d2 < 58) {
                         const float2 e = fadd2(make_float2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])), nx[d2]);
-                        acc = ffma2(e, e, acc);
+                        acc[j & 3] = ffma2(e, e, acc[j & 3]);
                     }
                 }
             };
@@ -481,7 +492,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             mbar_arrive(&S.bar_d2free);               // D2 is in registers: MMA2 of the next pair may overwrite it
             acc_block(v0, 2); acc_block(v1, 3);
             const int row = c.tile * TROWS + r;
-            float sse = row < x_rows ? acc.x + acc.y : 0.f;
+            float sse = row < x_rows ? ((acc[0].x + acc[0].y) + (acc[1].x + acc[1].y)) + ((acc[2].x + acc[2].y) + (acc[3].x + acc[3].y)) : 0.f;
             sse = warp_sum(sse);
             if (lane == 0) partial[((size_t)c.m * n_tiles + c.tile) * 4 + wq] = sse;
             PairCursor cn = c;
