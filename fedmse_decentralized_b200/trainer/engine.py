@@ -149,7 +149,11 @@ class FederationEngine:
     def prefetch_control(self, round_idx: int) -> None:
         """Do the host work of the NEXT round's control block while the GPU is busy with this one: the
         client selection and the uniform draws the common case needs (first voter succeeds).  Values go
-        through a FIFO, so the RNG streams are consumed in exactly the reference's order either way."""
+        through a FIFO, so the draws reach the scores in the same order whether or not they were drawn ahead.
+        (Parity with a same-seed run of the reference holds for the FIRST vote only: between rounds the reference
+        also draws from the global torch generator whenever a DataLoader iterator is created and when
+        ModelVerifier builds a fresh model, which this engine does not replay.  The jitter is a +-1e-4 tie-break,
+        so only elections between near-equal scores can differ.)"""
         if self._prefetched is not None:
             return
         n_sel = max(1, int(self.cfg.num_participants * self.N))
