@@ -17,15 +17,16 @@
 //  * Biases ride in the GEMMs: the parked tile gets a constant-one column (k = 115), W1 carries b1 in that column
 //    and a pass-through row that makes h1[27] = 1, W32 carries b32 in column 27 and passes the one on, W4 carries
 //    b4 in column 27.  The epilogues between the GEMMs are ReLU + fp16 split only, no tables, no FMAs.
-//  * Four pairs are in flight per stage (rings of four D1 / D1b accumulators in TMEM): the MMA -> epilogue -> MMA round
-//    trips are ~2 pair-times long, with two buffers the tensor pipe idled half of the time.  The parked tile is single
-//    buffered in exchange (a unit boundary costs one parking, ~3 % at 62 models per unit).
+//  * D2 (the reconstruction, 128 columns) is double buffered in TMEM and read by EIGHT epilogue warps: with one buffer
+//    the loop MMA2 -> squared error -> release -> next MMA2 set the pace of the kernel (ncu of the first two versions:
+//    1.7 k cycles per pair, tensor pipe 55 % active).  D1 / D1b are double buffered, the parked tile is single buffered
+//    in exchange (a unit boundary costs one parking, ~3 % at 62 models per unit).
 //  * No [models x rows] SSE matrix: each epilogue warp writes one partial sum per (model, tile); after a grid-wide
 //    barrier the CTAs reduce them in a fixed order to the per-model MSE (deterministic, replaces chunk_mean).
 //
-// TMEM map (512 columns): X hi 0..63, lo 64..127 | D1/h1[r] 128+32r | D1b/h2[r] 256+32r (r = pair mod 4) | D2 384..511.
-// Warp roles: 0-3 epilogues 1a/1b + tile parking, 4-7 epilogue 2 (squared error), 8 MMA issue, 9 weight images,
-// 10 X tiles (TMA).
+// TMEM map (512 columns): X hi 0..63, lo 64..127 | D1/h1[r] 128+32r | D1b/h2[r] 192+32r (r = pair mod 2) | D2[b] 256+128b.
+// Warp roles: 0-3 epilogues 1a/1b + tile parking, 4-11 epilogue 2 (squared error; two warps per TMEM lane quarter, half
+// of the output columns each), 12 MMA issue, 13 weight images, 14 X tiles (TMA).
 //
 // Tensor-pipe issue order in steady state:  ... MMA1(g+2)  MMA1b(g+1)  MMA2(g)  MMA1(g+3) ...
 // TMA multicast is not used; the operand images and the dev matrix live in this GPU's memory.
@@ -39,11 +40,11 @@ namespace tcf {
 
 using namespace fm::tc;
 
-constexpr int NT_F = 352;
-constexpr int MMA_WARP = 8, WLOAD_WARP = 9, XLOAD_WARP = 10;
+constexpr int NT_F = 480;                                 // 15 warps, at most 4 per SM sub-partition: 128 registers per thread
+constexpr int MMA_WARP = 12, WLOAD_WARP = 13, XLOAD_WARP = 14;
 constexpr int F_TMEM_COLS = 512;
-constexpr int NB = 4;                                     // ring depth of the D1 / D1b accumulators (pairs in flight per stage)
-constexpr int C_X = 0, C_XLO = 64, C_D1 = 128, C_D1B = 256, C_D2 = 384;     // D1[b] = 128 + 32 b, D1b[b] = 256 + 32 b
+constexpr int NB = 2;                                     // ring depth of the D1 / D1b accumulators (pairs in flight per stage)
+constexpr int C_X = 0, C_XLO = 64, C_D1 = 128, C_D1B = C_D1 + 32 * NB, C_D2 = 256;   // D1[r] = 128 + 32 r, D1b[r] = 192 + 32 r, D2[b] = 256 + 128 b
 // operand image of one model (bytes).  K-major, 128-B swizzle, 64 fp16 per 128-B row (short K is zero padded).
 constexpr int W1_BYTES = 2 * 4096;          // [32 n][128 k]  = two K-blocks of 32 rows x 128 B
 constexpr int W32_BYTES = 4096;             // [32 n][32 k]   (k 32..63 zero)
@@ -59,9 +60,9 @@ struct FSmem {
     alignas(1024) unsigned char w32[2][2 * W32_BYTES];
     alignas(1024) unsigned char w4[2][2 * W4_BYTES];
     alignas(8) uint64_t bar_x, bar_xfree, bar_xt, bar_w1[2], bar_w32[2], bar_w4[2], bar_d1[NB], bar_h1[NB], bar_d1b[NB],
-        bar_h2[NB], bar_d2[2], bar_d2free;
+        bar_h2[NB], bar_d2[2], bar_d2free[2];
     uint32_t tmem_base;
-    double red[12];
+    double red[16];
 };
 
 // byte offset of fp16 element (row, k) inside a [rows x 64 fp16] K-block with the 128-B swizzle
@@ -207,9 +208,10 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
     auto next_pair = [&](PairCursor& c) { if (++c.m >= c.m1) next_unit(c); };
 
     if (tid == 0) {
-        mbar_init(&S.bar_x, 1); mbar_init(&S.bar_xfree, 256); mbar_init(&S.bar_d2free, 128); mbar_init(&S.bar_xt, 128);
+        mbar_init(&S.bar_x, 1); mbar_init(&S.bar_xfree, 384); mbar_init(&S.bar_xt, 128);
         for (int b = 0; b < 2; ++b) {
             mbar_init(&S.bar_w1[b], 1); mbar_init(&S.bar_w32[b], 1); mbar_init(&S.bar_w4[b], 1); mbar_init(&S.bar_d2[b], 1);
+            mbar_init(&S.bar_d2free[b], 256);
         }
         for (int b = 0; b < NB; ++b) {
             mbar_init(&S.bar_d1[b], 1); mbar_init(&S.bar_d1b[b], 1); mbar_init(&S.bar_h1[b], 128); mbar_init(&S.bar_h2[b], 128);
@@ -240,9 +242,10 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             // for its tile) never blocks the MMAs that the tile's arrival depends on -- units of any length are safe.
             // Buffer reuse is covered by issue order (the tensor pipe executes in order): MMA1(q) overwrites D1[q % NB]
             // only after MMA1b(q - NB), its last reader, was issued (q1 <= q1b + NB - 1); MMA1b(q) overwrites
-            // D1b[q % NB] only after MMA2(q - NB) was issued (q1b <= q2 + NB - 1); MMA2 waits for epilogue 2 to have
-            // copied D2 out.  NB = 4 pairs in flight per stage cover the MMA -> epilogue -> MMA round trips (with two
-            // the tensor pipe idled half of the time: ncu of the first version).
+            // D1b[q % NB] only after MMA2(q - NB) was issued (q1b <= q2 + NB - 1); MMA2(q) writes D2[q & 1] once epilogue 2
+            // of pair q - 2 has read it.  D2 is the buffer that needs the slack: with a single D2 the loop MMA2 ->
+            // squared error -> release -> next MMA2 was the cycle of the whole kernel (1.7 k cycles per pair, tensor pipe
+            // 55 % active in ncu, whether two or four D1 / D1b buffers were in flight).
             // Parity safety: every barrier tested here completes its next phase only after work that this thread
             // issues after having seen the current one.
             PairCursor c1 = first_pair();
@@ -295,12 +298,12 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                 if (q2 >= q1b) return false;
                 if (!mbar_test(&S.bar_h2[q2 & (NB - 1)], (uint32_t)((q2 / NB) & 1)) ||
                     !mbar_test(&S.bar_w4[q2 & 1], (uint32_t)((q2 >> 1) & 1))) return false;
-                return q2 == 0 || mbar_test(&S.bar_d2free, (uint32_t)((q2 - 1) & 1));   // epilogue 2 (q2 - 1) holds D2 in registers
+                return q2 < 2 || mbar_test(&S.bar_d2free[q2 & 1], (uint32_t)(((q2 - 2) >> 1) & 1));   // epilogue 2 (q2 - 2) has read D2[q2 & 1]
             };
             auto issue2 = [&]() {                       // MMA2(q2): D2 = h2[r] . W4^T  (3 x 2 k-steps)
                 const int b = q2 & 1, rb = q2 & (NB - 1);
                 tc_fence_after();
-                const uint32_t d = tmem + C_D2, ah = tmem + C_D1B + 32 * rb, al = ah + 16;
+                const uint32_t d = tmem + C_D2 + 128 * b, ah = tmem + C_D1B + 32 * rb, al = ah + 16;
 #pragma unroll
                 for (int ks = 0; ks < 2; ++ks) {
                     const uint64_t bh = dw4[b] + (uint64_t)((ks * 32) >> 4), bl = bh + (uint64_t)(W4_BYTES >> 4);
@@ -377,7 +380,6 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         __syncwarp();
     } else if (warp < 4) {
         // ---- group A: parks tiles in TMEM, epilogues 1a (h1) and 1b (h2) of every pair ----
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 128;" ::);
         const int r = warp * 32 + lane;
         const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
         uint32_t v[32], hi[16], lo[16];
@@ -450,13 +452,14 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             if (!did) __nanosleep(20);
         }
     } else {
-        // ---- group B: epilogue 2 (squared error against the row kept in registers), partial sums ----
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 208;" ::);
-        const int wq = warp & 3;
+        // ---- group B: epilogue 2 (squared error against the row kept in registers), partial sums.  Eight warps: warps
+        //      4-7 take output columns 0..63 of their lane quarter, warps 8-11 columns 64..127, so a pair costs each
+        //      thread two 32-column loads and 32 packed subtract / multiply-adds ----
+        const int wq = warp & 3, half = (warp - 4) >> 2;
         const int r = wq * 32 + lane;
         const uint32_t lane_base = tmem + ((uint32_t)(wq * 32) << 16);
-        uint32_t v0[32], v1[32];
-        float2 nx[58];                              // -x of this thread's row (116 floats), for the whole unit
+        uint32_t v[32];
+        float2 nx[32];                              // -x of this thread's half row (64 floats), for the whole unit
         PairCursor c = first_pair();
         int g = 0, ut = 0;
         bool fresh = true;
@@ -464,37 +467,38 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             if (fresh) {
                 mbar_wait(&S.bar_x, (uint32_t)(ut & 1));
 #pragma unroll
-                for (int q = 0; q < 29; ++q) {
-                    const float4 xv = *reinterpret_cast<const float4*>(S.x + (q >> 3) * XBLK + r * 128 + (((q & 7) ^ (r & 7)) << 4));
-                    nx[q * 2] = make_float2(-xv.x, -xv.y);
-                    nx[q * 2 + 1] = make_float2(-xv.z, q == 28 ? 0.f : -xv.w);        // element 115 is padding (D2[115] == 0)
+                for (int q = 0; q < 16; ++q) {
+                    const int qq = half * 16 + q;     // float4 index inside the 128-float row
+                    const float4 xv = *reinterpret_cast<const float4*>(S.x + (qq >> 3) * XBLK + r * 128 + (((qq & 7) ^ (r & 7)) << 4));
+                    // columns 115..127 of D2 are exact zeros (no such rows in W4): their x is padding
+                    nx[q * 2] = make_float2(qq * 4 < D ? -xv.x : 0.f, qq * 4 + 1 < D ? -xv.y : 0.f);
+                    nx[q * 2 + 1] = make_float2(qq * 4 + 2 < D ? -xv.z : 0.f, qq * 4 + 3 < D ? -xv.w : 0.f);
                 }
                 mbar_arrive(&S.bar_xfree);
                 fresh = false;
             }
-            mbar_wait(&S.bar_d2[g & 1], (uint32_t)((g >> 1) & 1));
+            const int b = g & 1;
+            mbar_wait(&S.bar_d2[b], (uint32_t)((g >> 1) & 1));
             tc_fence_after();
             float2 acc[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
-            auto acc_block = [&](const uint32_t (&v)[32], int cb) {       // four independent chains: the FMAs pipeline
+            auto acc_block = [&](int cb) {            // four independent chains: the FMAs pipeline
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
-                    const int d2 = cb * 16 + j;       // float2 index
-                    if (d2 < 58) {
-                        const float2 e = fadd2(make_float2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])), nx[d2]);
-                        acc[j & 3] = ffma2(e, e, acc[j & 3]);
-                    }
+                    const float2 e = fadd2(make_float2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])), nx[cb * 16 + j]);
+                    acc[j & 3] = ffma2(e, e, acc[j & 3]);
                 }
             };
-            tmem_ld64(lane_base + C_D2, v0, v1);
-            acc_block(v0, 0); acc_block(v1, 1);
-            tmem_ld64(lane_base + C_D2 + 64, v0, v1);
+            const uint32_t d2 = lane_base + C_D2 + 128 * b + 64 * half;
+            tmem_ld32(d2, v);
+            acc_block(0);
+            tmem_ld32(d2 + 32, v);
             tc_fence_before();
-            mbar_arrive(&S.bar_d2free);               // D2 is in registers: MMA2 of the next pair may overwrite it
-            acc_block(v0, 2); acc_block(v1, 3);
+            mbar_arrive(&S.bar_d2free[b]);            // this thread's share of D2[b] is in registers
+            acc_block(1);
             const int row = c.tile * TROWS + r;
             float sse = row < x_rows ? ((acc[0].x + acc[0].y) + (acc[1].x + acc[1].y)) + ((acc[2].x + acc[2].y) + (acc[3].x + acc[3].y)) : 0.f;
             sse = warp_sum(sse);
-            if (lane == 0) partial[((size_t)c.m * n_tiles + c.tile) * 4 + wq] = sse;
+            if (lane == 0) partial[((size_t)c.m * n_tiles + c.tile) * 8 + half * 4 + wq] = sse;
             PairCursor cn = c;
             next_pair(cn);
             if (!cn.ok || cn.i != c.i) { ++ut; fresh = true; }
@@ -523,9 +527,9 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
     }
     __syncthreads();
     for (int m = blockIdx.x; m < n_models; m += gridDim.x) {
-        const float* pm = partial + (size_t)m * n_tiles * 4;
+        const float* pm = partial + (size_t)m * n_tiles * 8;
         double s = 0.0;
-        for (int i = tid; i < n_tiles * 4; i += NT_F) s += (double)__ldcg(pm + i);
+        for (int i = tid; i < n_tiles * 8; i += NT_F) s += (double)__ldcg(pm + i);
         s = warp_sum(s);
         if (lane == 0) S.red[warp] = s;
         __syncthreads();
@@ -568,7 +572,7 @@ int encode_x_map_f(CUtensorMap* map, const float* base, int64_t rows) {
 
 extern "C" int64_t fm_score_fused_scratch_floats(int64_t x_rows, int32_t n_models) {
     const int64_t n_tiles = (x_rows + fm::tc::TROWS - 1) / fm::tc::TROWS;
-    return n_tiles * 4 * (int64_t)(n_models > 0 ? n_models : 1);
+    return n_tiles * 8 * (int64_t)(n_models > 0 ? n_models : 1);
 }
 
 extern "C" int fm_score_fused_f16(const FmFusedScoreArgs* a, void* stream) {
