@@ -45,21 +45,25 @@ constexpr int MMA_WARP = 12, WLOAD_WARP = 13, XLOAD_WARP = 14;
 constexpr int F_TMEM_COLS = 512;
 constexpr int NB = 2;                                     // ring depth of the D1 / D1b accumulators (pairs in flight per stage)
 constexpr int C_X = 0, C_XLO = 64, C_D1 = 128, C_D1B = C_D1 + 32 * NB, C_D2 = 256;   // D1[r] = 128 + 32 r, D1b[r] = 192 + 32 r, D2[b] = 256 + 128 b
-// operand image of one model (bytes).  K-major, 128-B swizzle, 64 fp16 per 128-B row (short K is zero padded).
+// operand image of one model (bytes), K-major.  W1 (K = 128): 128-B swizzle, two K-blocks of 64 fp16 per row.
+// W32 and W4 (K = 32): 64-B swizzle, one 64-byte row per output feature -- no padding travels.  The images are what
+// every SM pulls from L2 for every (tile, model) pair, and at ~42 B / clk / SM of L2 bandwidth the 56 KB of the first
+// layout (128-B rows everywhere, K padded to 64) cost 1.35 k cycles per pair, more than the 0.93 k of tensor work.
+constexpr int NW = 3;                       // shared-memory stages per image kind
 constexpr int W1_BYTES = 2 * 4096;          // [32 n][128 k]  = two K-blocks of 32 rows x 128 B
-constexpr int W32_BYTES = 4096;             // [32 n][32 k]   (k 32..63 zero)
-constexpr int W4_BYTES = 128 * 128;         // [128 n][32 k]  (k 32..63 zero)
+constexpr int W32_BYTES = 32 * 64;          // [32 n][32 k]
+constexpr int W4_BYTES = 128 * 64;          // [128 n][32 k]
 constexpr int IMG_W1 = 0, IMG_W1LO = IMG_W1 + W1_BYTES, IMG_W32 = IMG_W1LO + W1_BYTES, IMG_W32LO = IMG_W32 + W32_BYTES,
-              IMG_W4 = IMG_W32LO + W32_BYTES, IMG_W4LO = IMG_W4 + W4_BYTES, IMG_F_BYTES = IMG_W4LO + W4_BYTES;   // 57,344
+              IMG_W4 = IMG_W32LO + W32_BYTES, IMG_W4LO = IMG_W4 + W4_BYTES, IMG_F_BYTES = IMG_W4LO + W4_BYTES;   // 36,864
 static_assert(IMG_F_BYTES <= FM_TC_IMAGE_BYTES, "the f16 image must fit the image slot of the header");
 constexpr float F16_MAX = 65504.f;
 
 struct FSmem {
     alignas(1024) unsigned char x[4 * XBLK];                 // fp32 staging of one 128-row tile (TMA, 128-B swizzle)
-    alignas(1024) unsigned char w1[2][2 * W1_BYTES];         // hi | lo
-    alignas(1024) unsigned char w32[2][2 * W32_BYTES];
-    alignas(1024) unsigned char w4[2][2 * W4_BYTES];
-    alignas(8) uint64_t bar_x, bar_xfree, bar_xt, bar_w1[2], bar_w32[2], bar_w4[2], bar_d1[NB], bar_h1[NB], bar_d1b[NB],
+    alignas(1024) unsigned char w1[NW][2 * W1_BYTES];        // hi | lo
+    alignas(1024) unsigned char w32[NW][2 * W32_BYTES];
+    alignas(1024) unsigned char w4[NW][2 * W4_BYTES];
+    alignas(8) uint64_t bar_x, bar_xfree, bar_xt, bar_w1[NW], bar_w32[NW], bar_w4[NW], bar_w1free[NW], bar_w32free[NW], bar_w4free[NW], bar_d1[NB], bar_h1[NB], bar_d1b[NB],
         bar_h2[NB], bar_d2[2], bar_d2free[2];
     uint32_t tmem_base;
     double red[16];
@@ -68,6 +72,21 @@ struct FSmem {
 // byte offset of fp16 element (row, k) inside a [rows x 64 fp16] K-block with the 128-B swizzle
 __host__ __device__ __forceinline__ int sw128h(int row, int k) {
     return row * 128 + ((((k >> 3) ^ (row & 7)) << 4) | ((k & 7) << 1));
+}
+// the same for a [rows x 32 fp16] operand with the 64-B swizzle: 16-byte chunk c of row r sits at chunk c ^ ((r >> 1) & 3)
+__host__ __device__ __forceinline__ int sw64h(int row, int k) {
+    return row * 64 + ((((k >> 3) ^ ((row >> 1) & 3)) << 4) | ((k & 7) << 1));
+}
+// K-major, 64-byte swizzle shared-memory matrix descriptor: 8-row atoms of 512 B (SBO), layout type SWIZZLE_64B = 4
+__device__ __forceinline__ uint64_t smem_desc_sw64(const void* p) {
+    const uint32_t a = smem_u32(p);
+    uint64_t d = 0;
+    d |= (uint64_t)((a & 0x3FFFFu) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(512 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)4 << 61;
+    return d;
 }
 __host__ __device__ constexpr uint32_t idesc_f16(int M, int N) {       // D = F32, A = B = F16, both K-major, dense
     return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
@@ -161,12 +180,12 @@ __global__ void __launch_bounds__(256) prep_images_f16_kernel(const float* __res
         const float v = row[p];
         if (p < OFF_B1) { const int n = p / D, k = p - n * D; put(IMG_W1, IMG_W1LO, (k >> 6) * 4096 + sw128h(n, k & 63), v); }
         else if (p < OFF_W2) put(IMG_W1, IMG_W1LO, 4096 + sw128h(p - OFF_B1, 115 & 63), v);     // b1 rides in column 115 (x[115] == 1)
-        else if (p >= OFF_W4 && p < OFF_B4) { const int q = p - OFF_W4, d = q / H, j = q - d * H; put(IMG_W4, IMG_W4LO, sw128h(d, j), v); }
-        else if (p >= OFF_B4) put(IMG_W4, IMG_W4LO, sw128h(p - OFF_B4, 27), v);                 // b4 rides in column 27 (h2[27] == 1)
+        else if (p >= OFF_W4 && p < OFF_B4) { const int q = p - OFF_W4, d = q / H, j = q - d * H; put(IMG_W4, IMG_W4LO, sw64h(d, j), v); }
+        else if (p >= OFF_B4) put(IMG_W4, IMG_W4LO, sw64h(p - OFF_B4, 27), v);                 // b4 rides in column 27 (h2[27] == 1)
     }
     if (tid == 0) {
         put(IMG_W1, IMG_W1LO, 4096 + sw128h(27, 115 & 63), 1.f);      // h1[27] = relu(1 * x[115]) = 1
-        put(IMG_W32, IMG_W32LO, sw128h(27, 27), 1.f);                 // h2[27] = relu(1 * h1[27]) = 1
+        put(IMG_W32, IMG_W32LO, sw64h(27, 27), 1.f);                  // h2[27] = relu(1 * h1[27]) = 1
     }
     // W32 = W3 W2 (27 x 27), b32 = W3 b2 + b3 in column 27
     for (int e = tid; e < H * (H + 1); e += 256) {
@@ -174,7 +193,7 @@ __global__ void __launch_bounds__(256) prep_images_f16_kernel(const float* __res
         float acc = k < H ? 0.f : b3s[n];
 #pragma unroll
         for (int i = 0; i < Z; ++i) acc = fmaf(w3s[n * Z + i], k < H ? w2s[i * H + k] : b2s[i], acc);
-        put(IMG_W32, IMG_W32LO, sw128h(n, k), acc);
+        put(IMG_W32, IMG_W32LO, sw64h(n, k), acc);
     }
 }
 
@@ -209,10 +228,11 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
 
     if (tid == 0) {
         mbar_init(&S.bar_x, 1); mbar_init(&S.bar_xfree, 384); mbar_init(&S.bar_xt, 128);
-        for (int b = 0; b < 2; ++b) {
-            mbar_init(&S.bar_w1[b], 1); mbar_init(&S.bar_w32[b], 1); mbar_init(&S.bar_w4[b], 1); mbar_init(&S.bar_d2[b], 1);
-            mbar_init(&S.bar_d2free[b], 256);
+        for (int b = 0; b < NW; ++b) {
+            mbar_init(&S.bar_w1[b], 1); mbar_init(&S.bar_w32[b], 1); mbar_init(&S.bar_w4[b], 1);
+            mbar_init(&S.bar_w1free[b], 1); mbar_init(&S.bar_w32free[b], 1); mbar_init(&S.bar_w4free[b], 1);
         }
+        for (int b = 0; b < 2; ++b) { mbar_init(&S.bar_d2[b], 1); mbar_init(&S.bar_d2free[b], 256); }
         for (int b = 0; b < NB; ++b) {
             mbar_init(&S.bar_d1[b], 1); mbar_init(&S.bar_d1b[b], 1); mbar_init(&S.bar_h1[b], 128); mbar_init(&S.bar_h2[b], 128);
         }
@@ -233,9 +253,9 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
     if (!has_work) {
     } else if (warp == MMA_WARP) {
         if (elect_one()) {
-            const uint64_t dw1[2] = {smem_desc_sw128(S.w1[0]), smem_desc_sw128(S.w1[1])};
-            const uint64_t dw32[2] = {smem_desc_sw128(S.w32[0]), smem_desc_sw128(S.w32[1])};
-            const uint64_t dw4[2] = {smem_desc_sw128(S.w4[0]), smem_desc_sw128(S.w4[1])};
+            uint64_t dw1[NW], dw32[NW], dw4[NW];
+#pragma unroll
+            for (int i = 0; i < NW; ++i) { dw1[i] = smem_desc_sw128(S.w1[i]); dw32[i] = smem_desc_sw64(S.w32[i]); dw4[i] = smem_desc_sw64(S.w4[i]); }
             // Three issue stages walk the pairs in order: q1 / q1b / q2 = next pair of MMA1 / MMA1b / MMA2.  A stage is
             // issued as soon as its inputs are there (non-blocking barrier tests), so the steady-state order
             // ... MMA1(g+2) MMA1b(g+1) MMA2(g) ... emerges by itself and a unit boundary (MMA1 of the next unit waits
@@ -254,12 +274,12 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; next_pair(t); } }
             auto ready1 = [&]() -> bool {
                 if (q1 >= n_pairs || q1 > q1b + (NB - 1)) return false;
-                if (!mbar_test(&S.bar_w1[q1 & 1], (uint32_t)((q1 >> 1) & 1))) return false;
+                if (!mbar_test(&S.bar_w1[q1 % NW], (uint32_t)((q1 / NW) & 1))) return false;
                 if (c1.ord != unit1 && !mbar_test(&S.bar_xt, (uint32_t)(c1.ord & 1))) return false;
                 return true;
             };
             auto issue1 = [&]() {                       // MMA1(q1): D1[r] = X . W1^T  (3 x 8 k-steps)
-                const int b = q1 & 1, rb = q1 & (NB - 1);
+                const int b = q1 % NW, rb = q1 & (NB - 1);
                 unit1 = c1.ord;
                 tc_fence_after();
                 const uint32_t d1 = tmem + C_D1 + 32 * rb, xh = tmem + C_X, xl = tmem + C_XLO;
@@ -272,16 +292,17 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     mma_ts_f16(d1, xl + kk * 8, bh, IDESC_N32, 1u);
                 }
                 tc_commit(&S.bar_d1[rb]);
+                tc_commit(&S.bar_w1free[b]);              // the image stage may be refilled once these MMAs have retired
                 next_pair(c1);
                 ++q1;
             };
             auto ready1b = [&]() -> bool {
                 if (q1b >= q1 || q1b > q2 + (NB - 1)) return false;
                 return mbar_test(&S.bar_h1[q1b & (NB - 1)], (uint32_t)((q1b / NB) & 1)) &&
-                       mbar_test(&S.bar_w32[q1b & 1], (uint32_t)((q1b >> 1) & 1));
+                       mbar_test(&S.bar_w32[q1b % NW], (uint32_t)((q1b / NW) & 1));
             };
             auto issue1b = [&]() {                      // MMA1b(q1b): D1b[r] = h1[r] . W32^T  (3 x 2 k-steps)
-                const int b = q1b & 1, rb = q1b & (NB - 1);
+                const int b = q1b % NW, rb = q1b & (NB - 1);
                 tc_fence_after();
                 const uint32_t d = tmem + C_D1B + 32 * rb, ah = tmem + C_D1 + 32 * rb, al = ah + 16;
 #pragma unroll
@@ -292,18 +313,19 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     mma_ts_f16(d, al + ks * 8, bh, IDESC_N32, 1u);
                 }
                 tc_commit(&S.bar_d1b[rb]);
+                tc_commit(&S.bar_w32free[b]);
                 ++q1b;
             };
             auto ready2 = [&]() -> bool {
                 if (q2 >= q1b) return false;
                 if (!mbar_test(&S.bar_h2[q2 & (NB - 1)], (uint32_t)((q2 / NB) & 1)) ||
-                    !mbar_test(&S.bar_w4[q2 & 1], (uint32_t)((q2 >> 1) & 1))) return false;
+                    !mbar_test(&S.bar_w4[q2 % NW], (uint32_t)((q2 / NW) & 1))) return false;
                 return q2 < 2 || mbar_test(&S.bar_d2free[q2 & 1], (uint32_t)(((q2 - 2) >> 1) & 1));   // epilogue 2 (q2 - 2) has read D2[q2 & 1]
             };
             auto issue2 = [&]() {                       // MMA2(q2): D2 = h2[r] . W4^T  (3 x 2 k-steps)
-                const int b = q2 & 1, rb = q2 & (NB - 1);
+                const int b = q2 % NW, rb = q2 & (NB - 1);
                 tc_fence_after();
-                const uint32_t d = tmem + C_D2 + 128 * b, ah = tmem + C_D1B + 32 * rb, al = ah + 16;
+                const uint32_t d = tmem + C_D2 + 128 * (q2 & 1), ah = tmem + C_D1B + 32 * rb, al = ah + 16;
 #pragma unroll
                 for (int ks = 0; ks < 2; ++ks) {
                     const uint64_t bh = dw4[b] + (uint64_t)((ks * 32) >> 4), bl = bh + (uint64_t)(W4_BYTES >> 4);
@@ -311,7 +333,8 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     mma_ts_f16(d, ah + ks * 8, bl, IDESC_N128, 1u);
                     mma_ts_f16(d, al + ks * 8, bh, IDESC_N128, 1u);
                 }
-                tc_commit(&S.bar_d2[b]);
+                tc_commit(&S.bar_d2[q2 & 1]);
+                tc_commit(&S.bar_w4free[b]);
                 ++q2;
             };
             while (q2 < n_pairs) {
@@ -323,9 +346,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         __syncwarp();
     } else if (warp == WLOAD_WARP) {
         // Weight images: after MMA1(q) retires w1(q+2) is requested, after MMA1b(q) w32(q+2), after MMA2(q) w4(q+2).
-        // Two buffers per kind suffice whatever the accumulator ring depth: the MMAs of one kind execute one after
-        // the other, so a buffer is busy only from its load to the retirement of its MMA.  The next completion of
-        // every barrier tested here needs the image requested right after the test succeeded (no phase is missed).
+        // (NW stages per kind: an image is requested NW pairs ahead of its MMA.)
         if (elect_one()) {
             int n_pairs = 0;
             { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; next_pair(t); } }
@@ -333,31 +354,32 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             int l1 = 0, l32 = 0, l4 = 0;
             auto load_w1 = [&]() {
                 const unsigned char* img = images + (size_t)cw1.m * FM_TC_IMAGE_BYTES;
-                const int b = l1 & 1;
+                const int b = l1 % NW;
                 mbar_expect_tx(&S.bar_w1[b], 2 * W1_BYTES);
                 bulk_load(S.w1[b], img + IMG_W1, 2 * W1_BYTES, &S.bar_w1[b]);
                 next_pair(cw1); ++l1;
             };
             auto load_w32 = [&]() {
                 const unsigned char* img = images + (size_t)cw32.m * FM_TC_IMAGE_BYTES;
-                const int b = l32 & 1;
+                const int b = l32 % NW;
                 mbar_expect_tx(&S.bar_w32[b], 2 * W32_BYTES);
                 bulk_load(S.w32[b], img + IMG_W32, 2 * W32_BYTES, &S.bar_w32[b]);
                 next_pair(cw32); ++l32;
             };
             auto load_w4 = [&]() {
                 const unsigned char* img = images + (size_t)cw4.m * FM_TC_IMAGE_BYTES;
-                const int b = l4 & 1;
+                const int b = l4 % NW;
                 mbar_expect_tx(&S.bar_w4[b], 2 * W4_BYTES);
                 bulk_load(S.w4[b], img + IMG_W4, 2 * W4_BYTES, &S.bar_w4[b]);
                 next_pair(cw4); ++l4;
             };
-            // image l of a kind goes into buffer l & 1 once the MMA that read image l - 2 has retired; the three kinds
-            // advance independently (non-blocking tests), so a slow stage never holds back the loads of another
+            // image l of a kind goes into stage l % NW once the MMAs that read image l - NW have retired (the issuing
+            // thread commits a "stage free" barrier behind them; its next completion needs the image requested right
+            // after the test succeeded, so no phase can be missed); the three kinds advance independently
             while (l1 < n_pairs || l32 < n_pairs || l4 < n_pairs) {
-                if (l1 < n_pairs && (l1 < 2 || mbar_test(&S.bar_d1[(l1 - 2) & (NB - 1)], (uint32_t)(((l1 - 2) / NB) & 1)))) load_w1();
-                if (l32 < n_pairs && (l32 < 2 || mbar_test(&S.bar_d1b[(l32 - 2) & (NB - 1)], (uint32_t)(((l32 - 2) / NB) & 1)))) load_w32();
-                if (l4 < n_pairs && (l4 < 2 || mbar_test(&S.bar_d2[(l4 - 2) & 1], (uint32_t)(((l4 - 2) >> 1) & 1)))) load_w4();
+                if (l1 < n_pairs && (l1 < NW || mbar_test(&S.bar_w1free[l1 % NW], (uint32_t)((l1 / NW - 1) & 1)))) load_w1();
+                if (l32 < n_pairs && (l32 < NW || mbar_test(&S.bar_w32free[l32 % NW], (uint32_t)((l32 / NW - 1) & 1)))) load_w32();
+                if (l4 < n_pairs && (l4 < NW || mbar_test(&S.bar_w4free[l4 % NW], (uint32_t)((l4 / NW - 1) & 1)))) load_w4();
             }
         }
         __syncwarp();

@@ -12,7 +12,24 @@ rep = sys.argv[1]
 nreg = int(sys.argv[sys.argv.index("--regions") + 1]) if "--regions" in sys.argv else 0
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
-hdr, unit, val = rows[0], rows[1], rows[2]
+hdr, unit = rows[0], rows[1]
+all_vals = rows[2:]
+val = all_vals[0]
+if "--all" in sys.argv:      # one block per captured kernel launch
+    keep = ["Kernel Name", "gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
+            "launch__shared_mem_per_block_dynamic", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+            "smsp__issue_active.avg.pct_of_peak_sustained_active", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+            "sm__warps_active.avg.pct_of_peak_sustained_active", "dram__bytes_read.sum", "dram__bytes_write.sum",
+            "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+            "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum"]
+    for v in all_vals:
+        if len(v) != len(hdr):
+            continue
+        for i, h in enumerate(hdr):
+            if h in keep:
+                print(f"{h:75s} {v[i][:90]:>30s} {unit[i]}")
+        print()
+    sys.exit(0)
 want = ["Kernel Name", "gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
         "launch__shared_mem_per_block_dynamic", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
         "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum",

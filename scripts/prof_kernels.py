@@ -25,6 +25,8 @@ ap.add_argument("--epochs", type=int, default=5)
 ap.add_argument("--patience", type=int, default=1)
 ap.add_argument("--score-precision", default="fp32")
 ap.add_argument("--phase-cycles", action="store_true")
+ap.add_argument("--aggregation", default="elected", choices=["elected", "gossip"])
+ap.add_argument("--participation", type=float, default=0.5)
 ap.add_argument("--dev-rows-mult", type=int, default=1,
                 help="repeat the pooled dev matrix: 8 reproduces on one GPU the per-GPU scoring work of an 8-GPU run")
 a = ap.parse_args()
@@ -35,7 +37,8 @@ if a.dev_rows_mult > 1:
     devset = np.tile(devset, (a.dev_rows_mult, 1))
 sh = ShardStore.build(clients, devset).to(dev)
 cfg = ExperimentConfig(epoch=a.epochs, network_size=a.clients, backend="cuda", write_latents=False,
-                       save_client_models=False, local_patience=a.patience, score_precision=a.score_precision)
+                       save_client_models=False, local_patience=a.patience, score_precision=a.score_precision,
+                       aggregation=a.aggregation, topology="random-k", topology_k=4, num_participants=a.participation)
 eng = FederationEngine(cfg, sh, "hybrid", "mse_avg")
 be, st = eng.backend, eng.state
 if a.phase_cycles:
