@@ -85,16 +85,25 @@ def prepare_from_scenario(scenario: Dict, network_size: int, new_device: bool = 
 
 def prepare_from_raw(raw: Sequence[ClientRaw], new_device: bool = True, seed: Optional[int] = None
                      ) -> Tuple[List[PreparedClient], np.ndarray]:
-    """In-memory variant used for synthetic scenarios (no CSV round trip)."""
-    rng = np.random.default_rng(seed) if seed is not None else None
+    """In-memory variant used for synthetic scenarios (no CSV round trip).
 
-    def perm(n):
-        return rng.permutation(n) if rng is not None else np.random.permutation(n)
+    With a ``seed`` every client shuffles with its own generator keyed by ``(seed, index)`` and the dev pool with
+    ``(seed, "dev")``: a multi-GPU rank that only holds the abnormal rows of the clients it owns (``make_clients(...,
+    full=owned)``) then still builds the same validation shards and dev matrix as every other rank."""
+    if seed is None:
+        perm_of = lambda i: np.random.permutation            # noqa: E731 - the reference's global-generator behaviour
+        perm_dev = np.random.permutation
+    else:
+        gens = {}
 
+        def perm_of(i):
+            return gens.setdefault(i, np.random.default_rng([seed, 1, i])).permutation
+        perm_dev = np.random.default_rng([seed, 2]).permutation
     clients = []
-    for cl in raw:
+    for i, cl in enumerate(raw):
+        perm = perm_of(i)
         normal = cl.normal[perm(len(cl.normal))]
         abnormal = cl.abnormal[perm(len(cl.abnormal))]
         clients.append(prepare_client(cl.name, normal, abnormal, cl.test_normal, new_device))
-    dev = pool_dev_set(clients, sampler=lambda a, n: a[perm(len(a))[:n]])
+    dev = pool_dev_set(clients, sampler=lambda a, n: a[perm_dev(len(a))[:n]])
     return clients, dev
