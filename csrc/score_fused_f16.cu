@@ -26,7 +26,7 @@
 //
 // TMEM map (512 columns): X hi 0..63, lo 64..127 | D1/h1[r] 128+32r | D1b/h2[r] 192+32r (r = pair mod 2) | D2[b] 256+128b.
 // Warp roles: 0-3 epilogues 1a/1b + tile parking, 4-11 epilogue 2 (squared error; two warps per TMEM lane quarter, half
-// of the output columns each), 12 MMA issue, 13 weight images, 14 X tiles (TMA).
+// of the output columns each), 12 / 13 / 14 MMA issue (one thread per GEMM stage), 15 weight images + X tiles (TMA).
 //
 // Tensor-pipe issue order in steady state:  ... MMA1(g+2)  MMA1b(g+1)  MMA2(g)  MMA1(g+3) ...
 // TMA multicast is not used; the operand images and the dev matrix live in this GPU's memory.
@@ -40,8 +40,8 @@ namespace tcf {
 
 using namespace fm::tc;
 
-constexpr int NT_F = 480;                                 // 15 warps, at most 4 per SM sub-partition: 128 registers per thread
-constexpr int MMA_WARP = 12, WLOAD_WARP = 13, XLOAD_WARP = 14;
+constexpr int NT_F = 512;                                 // 16 warps, 4 per SM sub-partition: 128 registers per thread
+constexpr int MMA1_WARP = 12, MMA1B_WARP = 13, MMA2_WARP = 14, LOAD_WARP = 15;
 constexpr int F_TMEM_COLS = 512;
 constexpr int NB = 2;                                     // ring depth of the D1 / D1b accumulators (pairs in flight per stage)
 constexpr int C_X = 0, C_XLO = 64, C_D1 = 128, C_D1B = C_D1 + 32 * NB, C_D2 = 256;   // D1[r] = 128 + 32 r, D1b[r] = 192 + 32 r, D2[b] = 256 + 128 b
@@ -63,7 +63,7 @@ struct FSmem {
     alignas(1024) unsigned char w1[NW][2 * W1_BYTES];        // hi | lo
     alignas(1024) unsigned char w32[NW][2 * W32_BYTES];
     alignas(1024) unsigned char w4[NW][2 * W4_BYTES];
-    alignas(8) uint64_t bar_x, bar_xfree, bar_xt, bar_w1[NW], bar_w32[NW], bar_w4[NW], bar_w1free[NW], bar_w32free[NW], bar_w4free[NW], bar_d1[NB], bar_h1[NB], bar_d1b[NB],
+    alignas(8) uint64_t bar_x, bar_xfree, bar_xt, bar_w1[NW], bar_w32[NW], bar_w4[NW], bar_w1free[NW], bar_w32free[NW], bar_w4free[NW], bar_d1[NB], bar_h1[NB], bar_d1b[NB], bar_d1free[NB], bar_d1bfree[NB],
         bar_h2[NB], bar_d2[2], bar_d2free[2];
     uint32_t tmem_base;
     double red[16];
@@ -235,10 +235,11 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         for (int b = 0; b < 2; ++b) { mbar_init(&S.bar_d2[b], 1); mbar_init(&S.bar_d2free[b], 256); }
         for (int b = 0; b < NB; ++b) {
             mbar_init(&S.bar_d1[b], 1); mbar_init(&S.bar_d1b[b], 1); mbar_init(&S.bar_h1[b], 128); mbar_init(&S.bar_h2[b], 128);
+            mbar_init(&S.bar_d1free[b], 1); mbar_init(&S.bar_d1bfree[b], 1);
         }
         fence_mbar_init();
     }
-    if (warp == MMA_WARP) {
+    if (warp == MMA1_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)), "r"(F_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
@@ -251,152 +252,125 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
     // total pairs of this CTA and, per role, a walk over them in the same order
     const bool has_work = first_pair().ok;
     if (!has_work) {
-    } else if (warp == MMA_WARP) {
-        if (elect_one()) {
-            uint64_t dw1[NW], dw32[NW], dw4[NW];
-#pragma unroll
-            for (int i = 0; i < NW; ++i) { dw1[i] = smem_desc_sw128(S.w1[i]); dw32[i] = smem_desc_sw64(S.w32[i]); dw4[i] = smem_desc_sw64(S.w4[i]); }
-            // Three issue stages walk the pairs in order: q1 / q1b / q2 = next pair of MMA1 / MMA1b / MMA2.  A stage is
-            // issued as soon as its inputs are there (non-blocking barrier tests), so the steady-state order
-            // ... MMA1(g+2) MMA1b(g+1) MMA2(g) ... emerges by itself and a unit boundary (MMA1 of the next unit waits
-            // for its tile) never blocks the MMAs that the tile's arrival depends on -- units of any length are safe.
-            // Buffer reuse is covered by issue order (the tensor pipe executes in order): MMA1(q) overwrites D1[q % NB]
-            // only after MMA1b(q - NB), its last reader, was issued (q1 <= q1b + NB - 1); MMA1b(q) overwrites
-            // D1b[q % NB] only after MMA2(q - NB) was issued (q1b <= q2 + NB - 1); MMA2(q) writes D2[q & 1] once epilogue 2
-            // of pair q - 2 has read it.  D2 is the buffer that needs the slack: with a single D2 the loop MMA2 ->
-            // squared error -> release -> next MMA2 was the cycle of the whole kernel (1.7 k cycles per pair, tensor pipe
-            // 55 % active in ncu, whether two or four D1 / D1b buffers were in flight).
-            // Parity safety: every barrier tested here completes its next phase only after work that this thread
-            // issues after having seen the current one.
-            PairCursor c1 = first_pair();
-            int q1 = 0, q1b = 0, q2 = 0, unit1 = -1;
-            int n_pairs = 0;
-            { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; next_pair(t); } }
-            auto ready1 = [&]() -> bool {
-                if (q1 >= n_pairs || q1 > q1b + (NB - 1)) return false;
-                if (!mbar_test(&S.bar_w1[q1 % NW], (uint32_t)((q1 / NW) & 1))) return false;
-                if (c1.ord != unit1 && !mbar_test(&S.bar_xt, (uint32_t)(c1.ord & 1))) return false;
-                return true;
-            };
-            auto issue1 = [&]() {                       // MMA1(q1): D1[r] = X . W1^T  (3 x 8 k-steps)
-                const int b = q1 % NW, rb = q1 & (NB - 1);
-                unit1 = c1.ord;
-                tc_fence_after();
-                const uint32_t d1 = tmem + C_D1 + 32 * rb, xh = tmem + C_X, xl = tmem + C_XLO;
-#pragma unroll
-                for (int kk = 0; kk < 8; ++kk) {
-                    const uint64_t bh = dw1[b] + (uint64_t)(((kk >> 2) * 4096 + (kk & 3) * 32) >> 4);
-                    const uint64_t bl = bh + (uint64_t)(W1_BYTES >> 4);
-                    mma_ts_f16(d1, xh + kk * 8, bh, IDESC_N32, kk ? 1u : 0u);
-                    mma_ts_f16(d1, xh + kk * 8, bl, IDESC_N32, 1u);
-                    mma_ts_f16(d1, xl + kk * 8, bh, IDESC_N32, 1u);
-                }
-                tc_commit(&S.bar_d1[rb]);
-                tc_commit(&S.bar_w1free[b]);              // the image stage may be refilled once these MMAs have retired
-                next_pair(c1);
-                ++q1;
-            };
-            auto ready1b = [&]() -> bool {
-                if (q1b >= q1 || q1b > q2 + (NB - 1)) return false;
-                return mbar_test(&S.bar_h1[q1b & (NB - 1)], (uint32_t)((q1b / NB) & 1)) &&
-                       mbar_test(&S.bar_w32[q1b % NW], (uint32_t)((q1b / NW) & 1));
-            };
-            auto issue1b = [&]() {                      // MMA1b(q1b): D1b[r] = h1[r] . W32^T  (3 x 2 k-steps)
-                const int b = q1b % NW, rb = q1b & (NB - 1);
-                tc_fence_after();
-                const uint32_t d = tmem + C_D1B + 32 * rb, ah = tmem + C_D1 + 32 * rb, al = ah + 16;
-#pragma unroll
-                for (int ks = 0; ks < 2; ++ks) {
-                    const uint64_t bh = dw32[b] + (uint64_t)((ks * 32) >> 4), bl = bh + (uint64_t)(W32_BYTES >> 4);
-                    mma_ts_f16(d, ah + ks * 8, bh, IDESC_N32, ks ? 1u : 0u);
-                    mma_ts_f16(d, ah + ks * 8, bl, IDESC_N32, 1u);
-                    mma_ts_f16(d, al + ks * 8, bh, IDESC_N32, 1u);
-                }
-                tc_commit(&S.bar_d1b[rb]);
-                tc_commit(&S.bar_w32free[b]);
-                ++q1b;
-            };
-            auto ready2 = [&]() -> bool {
-                if (q2 >= q1b) return false;
-                if (!mbar_test(&S.bar_h2[q2 & (NB - 1)], (uint32_t)((q2 / NB) & 1)) ||
-                    !mbar_test(&S.bar_w4[q2 % NW], (uint32_t)((q2 / NW) & 1))) return false;
-                return q2 < 2 || mbar_test(&S.bar_d2free[q2 & 1], (uint32_t)(((q2 - 2) >> 1) & 1));   // epilogue 2 (q2 - 2) has read D2[q2 & 1]
-            };
-            auto issue2 = [&]() {                       // MMA2(q2): D2 = h2[r] . W4^T  (3 x 2 k-steps)
-                const int b = q2 % NW, rb = q2 & (NB - 1);
-                tc_fence_after();
-                const uint32_t d = tmem + C_D2 + 128 * (q2 & 1), ah = tmem + C_D1B + 32 * rb, al = ah + 16;
-#pragma unroll
-                for (int ks = 0; ks < 2; ++ks) {
-                    const uint64_t bh = dw4[b] + (uint64_t)((ks * 32) >> 4), bl = bh + (uint64_t)(W4_BYTES >> 4);
-                    mma_ts_f16(d, ah + ks * 8, bh, IDESC_N128, ks ? 1u : 0u);
-                    mma_ts_f16(d, ah + ks * 8, bl, IDESC_N128, 1u);
-                    mma_ts_f16(d, al + ks * 8, bh, IDESC_N128, 1u);
-                }
-                tc_commit(&S.bar_d2[q2 & 1]);
-                tc_commit(&S.bar_w4free[b]);
-                ++q2;
-            };
-            while (q2 < n_pairs) {
-                if (ready2()) issue2();                 // oldest work first: it frees the most downstream buffers
-                if (ready1b()) issue1b();
-                if (ready1()) issue1();
-            }
-        }
-        __syncwarp();
-    } else if (warp == WLOAD_WARP) {
-        // Weight images: after MMA1(q) retires w1(q+2) is requested, after MMA1b(q) w32(q+2), after MMA2(q) w4(q+2).
-        // (NW stages per kind: an image is requested NW pairs ahead of its MMA.)
+    } else if (warp == MMA1_WARP || warp == MMA1B_WARP || warp == MMA2_WARP) {
+        // Three issuing threads, one per GEMM stage.  ncu of the single-issuer versions showed the tensor pipe active
+        // for exactly its ~0.93 k cycles of math per pair and idle for the ~0.8-1.0 k cycles the issuing thread spent
+        // on everything else (waits, phase arithmetic, descriptor selection): the MMA queue drains while its only
+        // producer does bookkeeping, so period = math + issue overhead, whatever the buffering.  With one issuer per
+        // stage the bookkeeping of one overlaps the MMAs of the others.  Each thread walks the pairs in order with
+        // blocking waits; every cross-thread hazard is covered by a commit barrier ("these MMAs have RETIRED"):
+        //   MMA1(q)  overwrites D1[q&1]   -> waits bar_d1free  (MMA1b(q-2) retired, committed by the MMA1b thread)
+        //   MMA1b(q) overwrites D1b[q&1]  -> waits bar_d1bfree (MMA2(q-2) retired, committed by the MMA2 thread)
+        //   MMA2(q)  overwrites D2[q&1]   -> waits bar_d2free  (epilogue 2 of pair q-2 has read it)
+        // No thread ever waits for something that needs its own later work, so units of any length are safe.
         if (elect_one()) {
             int n_pairs = 0;
             { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; next_pair(t); } }
-            PairCursor cw1 = first_pair(), cw32 = cw1, cw4 = cw1;       // model of the NEXT image to request, per kind
-            int l1 = 0, l32 = 0, l4 = 0;
-            auto load_w1 = [&]() {
-                const unsigned char* img = images + (size_t)cw1.m * FM_TC_IMAGE_BYTES;
-                const int b = l1 % NW;
-                mbar_expect_tx(&S.bar_w1[b], 2 * W1_BYTES);
-                bulk_load(S.w1[b], img + IMG_W1, 2 * W1_BYTES, &S.bar_w1[b]);
-                next_pair(cw1); ++l1;
-            };
-            auto load_w32 = [&]() {
-                const unsigned char* img = images + (size_t)cw32.m * FM_TC_IMAGE_BYTES;
-                const int b = l32 % NW;
-                mbar_expect_tx(&S.bar_w32[b], 2 * W32_BYTES);
-                bulk_load(S.w32[b], img + IMG_W32, 2 * W32_BYTES, &S.bar_w32[b]);
-                next_pair(cw32); ++l32;
-            };
-            auto load_w4 = [&]() {
-                const unsigned char* img = images + (size_t)cw4.m * FM_TC_IMAGE_BYTES;
-                const int b = l4 % NW;
-                mbar_expect_tx(&S.bar_w4[b], 2 * W4_BYTES);
-                bulk_load(S.w4[b], img + IMG_W4, 2 * W4_BYTES, &S.bar_w4[b]);
-                next_pair(cw4); ++l4;
-            };
-            // image l of a kind goes into stage l % NW once the MMAs that read image l - NW have retired (the issuing
-            // thread commits a "stage free" barrier behind them; its next completion needs the image requested right
-            // after the test succeeded, so no phase can be missed); the three kinds advance independently
-            while (l1 < n_pairs || l32 < n_pairs || l4 < n_pairs) {
-                if (l1 < n_pairs && (l1 < NW || mbar_test(&S.bar_w1free[l1 % NW], (uint32_t)((l1 / NW - 1) & 1)))) load_w1();
-                if (l32 < n_pairs && (l32 < NW || mbar_test(&S.bar_w32free[l32 % NW], (uint32_t)((l32 / NW - 1) & 1)))) load_w32();
-                if (l4 < n_pairs && (l4 < NW || mbar_test(&S.bar_w4free[l4 % NW], (uint32_t)((l4 / NW - 1) & 1)))) load_w4();
+            int s = 0;                 // image stage q % NW and its phase (q / NW) & 1, kept incrementally
+            uint32_t sph = 0;
+            if (warp == MMA1_WARP) {
+                const uint64_t dw1 = smem_desc_sw128(S.w1[0]);
+                PairCursor c1 = first_pair();
+                int unit1 = -1;
+                for (int q = 0; q < n_pairs; ++q) {
+                    const int r = q & 1;
+                    if (c1.ord != unit1) { mbar_wait(&S.bar_xt, (uint32_t)(c1.ord & 1)); unit1 = c1.ord; }   // tile parked
+                    mbar_wait(&S.bar_w1[s], sph);
+                    if (q >= NB) mbar_wait(&S.bar_d1free[r], (uint32_t)(((q - NB) >> 1) & 1));
+                    tc_fence_after();
+                    const uint32_t d1 = tmem + C_D1 + 32 * r, xh = tmem + C_X, xl = tmem + C_XLO;
+                    const uint64_t bw = dw1 + (uint64_t)((s * 2 * W1_BYTES) >> 4);
+#pragma unroll
+                    for (int kk = 0; kk < 8; ++kk) {
+                        const uint64_t bh = bw + (uint64_t)(((kk >> 2) * 4096 + (kk & 3) * 32) >> 4);
+                        const uint64_t bl = bh + (uint64_t)(W1_BYTES >> 4);
+                        mma_ts_f16(d1, xh + kk * 8, bh, IDESC_N32, kk ? 1u : 0u);
+                        mma_ts_f16(d1, xh + kk * 8, bl, IDESC_N32, 1u);
+                        mma_ts_f16(d1, xl + kk * 8, bh, IDESC_N32, 1u);
+                    }
+                    tc_commit(&S.bar_d1[r]);
+                    tc_commit(&S.bar_w1free[s]);
+                    next_pair(c1);
+                    if (++s == NW) { s = 0; sph ^= 1u; }
+                }
+            } else if (warp == MMA1B_WARP) {
+                const uint64_t dw32 = smem_desc_sw64(S.w32[0]);
+                for (int q = 0; q < n_pairs; ++q) {
+                    const int r = q & 1;
+                    mbar_wait(&S.bar_h1[r], (uint32_t)((q >> 1) & 1));
+                    mbar_wait(&S.bar_w32[s], sph);
+                    if (q >= NB) mbar_wait(&S.bar_d1bfree[r], (uint32_t)(((q - NB) >> 1) & 1));
+                    tc_fence_after();
+                    const uint32_t d = tmem + C_D1B + 32 * r, ah = tmem + C_D1 + 32 * r, al = ah + 16;
+                    const uint64_t bw = dw32 + (uint64_t)((s * 2 * W32_BYTES) >> 4);
+#pragma unroll
+                    for (int ks = 0; ks < 2; ++ks) {
+                        const uint64_t bh = bw + (uint64_t)((ks * 32) >> 4), bl = bh + (uint64_t)(W32_BYTES >> 4);
+                        mma_ts_f16(d, ah + ks * 8, bh, IDESC_N32, ks ? 1u : 0u);
+                        mma_ts_f16(d, ah + ks * 8, bl, IDESC_N32, 1u);
+                        mma_ts_f16(d, al + ks * 8, bh, IDESC_N32, 1u);
+                    }
+                    tc_commit(&S.bar_d1b[r]);
+                    tc_commit(&S.bar_w32free[s]);
+                    tc_commit(&S.bar_d1free[r]);
+                    if (++s == NW) { s = 0; sph ^= 1u; }
+                }
+            } else {
+                const uint64_t dw4 = smem_desc_sw64(S.w4[0]);
+                for (int q = 0; q < n_pairs; ++q) {
+                    const int r = q & 1;
+                    mbar_wait(&S.bar_h2[r], (uint32_t)((q >> 1) & 1));
+                    mbar_wait(&S.bar_w4[s], sph);
+                    if (q >= 2) mbar_wait(&S.bar_d2free[r], (uint32_t)(((q - 2) >> 1) & 1));
+                    tc_fence_after();
+                    const uint32_t d = tmem + C_D2 + 128 * r, ah = tmem + C_D1B + 32 * r, al = ah + 16;
+                    const uint64_t bw = dw4 + (uint64_t)((s * 2 * W4_BYTES) >> 4);
+#pragma unroll
+                    for (int ks = 0; ks < 2; ++ks) {
+                        const uint64_t bh = bw + (uint64_t)((ks * 32) >> 4), bl = bh + (uint64_t)(W4_BYTES >> 4);
+                        mma_ts_f16(d, ah + ks * 8, bh, IDESC_N128, ks ? 1u : 0u);
+                        mma_ts_f16(d, ah + ks * 8, bl, IDESC_N128, 1u);
+                        mma_ts_f16(d, al + ks * 8, bh, IDESC_N128, 1u);
+                    }
+                    tc_commit(&S.bar_d2[r]);
+                    tc_commit(&S.bar_w4free[s]);
+                    tc_commit(&S.bar_d1bfree[r]);
+                    if (++s == NW) { s = 0; sph ^= 1u; }
+                }
             }
         }
         __syncwarp();
-    } else if (warp == XLOAD_WARP) {
-        // fp32 tiles of the units, one ahead: the staging buffer is refilled once the parking warps and the
-        // squared-error warps both have their copy of the current tile (bar_xfree)
+    } else if (warp == LOAD_WARP) {
+        // One thread feeds the shared memory: weight images NW pairs ahead (image l of a kind goes into stage l % NW
+        // once the MMAs that read image l - NW have retired -- the issuing thread commits a "stage free" barrier behind
+        // them, and its next completion needs the image requested right after the test succeeded, so no phase can be
+        // missed) and the fp32 tile of the next unit (once the parking warps and the squared-error warps both have
+        // their copy of the current one).  Everything is polled, so no kind of load can hold back another.
         if (elect_one()) {
-            PairCursor cx = first_pair();
-            int ut = 0;
-            for (;;) {
-                mbar_expect_tx(&S.bar_x, 4u * XBLK);
+            int n_pairs = 0, n_units_ne = 0;
+            { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; n_units_ne = t.ord + 1; next_pair(t); } }
+            PairCursor cw1 = first_pair(), cw32 = cw1, cw4 = cw1, cx = cw1;
+            int l1 = 0, l32 = 0, l4 = 0, lx = 0;
+            auto load_img = [&](unsigned char* dst, int m, int off, uint32_t bytes, uint64_t* bar) {
+                mbar_expect_tx(bar, bytes);
+                bulk_load(dst, images + (size_t)m * FM_TC_IMAGE_BYTES + off, bytes, bar);
+            };
+            while (l1 < n_pairs || l32 < n_pairs || l4 < n_pairs || lx < n_units_ne) {
+                if (lx < n_units_ne && (lx == 0 || mbar_test(&S.bar_xfree, (uint32_t)((lx - 1) & 1)))) {
+                    mbar_expect_tx(&S.bar_x, 4u * XBLK);
 #pragma unroll
-                for (int kb = 0; kb < 4; ++kb) tma_load_2d(S.x + kb * XBLK, &xmap, kb * 32, cx.tile * TROWS, &S.bar_x);
-                next_unit(cx);
-                if (!cx.ok) break;
-                mbar_wait(&S.bar_xfree, (uint32_t)(ut & 1));
-                ++ut;
+                    for (int kb = 0; kb < 4; ++kb) tma_load_2d(S.x + kb * XBLK, &xmap, kb * 32, cx.tile * TROWS, &S.bar_x);
+                    next_unit(cx); ++lx;
+                }
+                if (l1 < n_pairs && (l1 < NW || mbar_test(&S.bar_w1free[l1 % NW], (uint32_t)((l1 / NW - 1) & 1)))) {
+                    load_img(S.w1[l1 % NW], cw1.m, IMG_W1, 2 * W1_BYTES, &S.bar_w1[l1 % NW]); next_pair(cw1); ++l1;
+                }
+                if (l32 < n_pairs && (l32 < NW || mbar_test(&S.bar_w32free[l32 % NW], (uint32_t)((l32 / NW - 1) & 1)))) {
+                    load_img(S.w32[l32 % NW], cw32.m, IMG_W32, 2 * W32_BYTES, &S.bar_w32[l32 % NW]); next_pair(cw32); ++l32;
+                }
+                if (l4 < n_pairs && (l4 < NW || mbar_test(&S.bar_w4free[l4 % NW], (uint32_t)((l4 / NW - 1) & 1)))) {
+                    load_img(S.w4[l4 % NW], cw4.m, IMG_W4, 2 * W4_BYTES, &S.bar_w4[l4 % NW]); next_pair(cw4); ++l4;
+                }
             }
         }
         __syncwarp();
@@ -530,7 +504,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == MMA_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(F_TMEM_COLS));
+    if (warp == MMA1_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(F_TMEM_COLS));
 
     // ---- grid-wide barrier (the grid never exceeds the SM count and a CTA fills an SM: all CTAs are resident), then
     //      the per-model MSE from the partial sums in a fixed order ----
