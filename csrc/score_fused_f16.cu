@@ -57,6 +57,11 @@ constexpr int IMG_W1 = 0, IMG_W1LO = IMG_W1 + W1_BYTES, IMG_W32 = IMG_W1LO + W1_
               IMG_W4 = IMG_W32LO + W32_BYTES, IMG_W4LO = IMG_W4 + W4_BYTES, IMG_F_BYTES = IMG_W4LO + W4_BYTES;   // 36,864
 static_assert(IMG_F_BYTES <= FM_TC_IMAGE_BYTES, "the f16 image must fit the image slot of the header");
 constexpr float F16_MAX = 65504.f;
+// debug cycle slots (CTA 0): issuing threads 1 / 1b / 2: waits (tile or epilogue, image, free buffer) and issue;
+// parking+epilogue warp 0: park, e1, e1b, idle polling; squared-error warp 4: wait D2, until D2 released, rest, unit entry
+enum { TK_1_XT = 0, TK_1_W, TK_1_FREE, TK_1_ISSUE, TK_1B_H, TK_1B_W, TK_1B_FREE, TK_1B_ISSUE, TK_2_H, TK_2_W, TK_2_FREE, TK_2_ISSUE,
+       TK_A_PARK, TK_A_E1, TK_A_E1B, TK_A_IDLE, TK_B_WAIT, TK_B_HOLD, TK_B_REST, TK_B_ENTRY, TK_TOTAL, TK_N };
+#define FT(slot) do { if (TIMING && tk_on) { const long long now_ = clock64(); tk[slot] += now_ - tk_t; tk_t = now_; } } while (0)
 
 struct FSmem {
     alignas(1024) unsigned char x[4 * XBLK];                 // fp32 staging of one 128-row tile (TMA, 128-B swizzle)
@@ -111,7 +116,7 @@ __device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
     return ok != 0;
 }
 // (a, b) -> packed fp16 heads (a in the low half: element k of an A row sits in bits [15:0] of column k / 2 when k is
-// even) and packed fp16 remainders.  The converts saturate at +-65504, so the remainder absorbs what the head cannot hold.
+// even -- verified on the device: the other order is off by 1e-3) and packed fp16 remainders.  The converts saturate at +-65504, so the remainder absorbs what the head cannot hold.
 __device__ __forceinline__ uint32_t pack_f16x2_sat(float lo_half, float hi_half) {
     uint32_t r;
     asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_half), "f"(lo_half));
@@ -122,19 +127,17 @@ __device__ __forceinline__ uint32_t pack_f16x2_relu_sat(float lo_half, float hi_
     asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_half), "f"(lo_half));
     return r;
 }
-template <bool SWAP>
 __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
-    hi = SWAP ? pack_f16x2_sat(b, a) : pack_f16x2_sat(a, b);
+    hi = pack_f16x2_sat(a, b);
     const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&hi));      // f.x = low half
-    lo = SWAP ? pack_f16x2_sat(b - f.x, a - f.y) : pack_f16x2_sat(a - f.x, b - f.y);
+    lo = pack_f16x2_sat(a - f.x, b - f.y);
 }
 // the same for relu(a), relu(b): one convert does ReLU + saturation + packing
-template <bool SWAP>
 __device__ __forceinline__ void split2_relu(float a, float b, uint32_t& hi, uint32_t& lo) {
-    hi = SWAP ? pack_f16x2_relu_sat(b, a) : pack_f16x2_relu_sat(a, b);
+    hi = pack_f16x2_relu_sat(a, b);
     const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&hi));
     const float ra = fmaxf(a, 0.f), rb = fmaxf(b, 0.f);
-    lo = SWAP ? pack_f16x2_sat(rb - f.x, ra - f.y) : pack_f16x2_sat(ra - f.x, rb - f.y);
+    lo = pack_f16x2_sat(ra - f.x, rb - f.y);
 }
 __device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
     unsigned long long ra, rb, rd;
@@ -197,7 +200,8 @@ __global__ void __launch_bounds__(256) prep_images_f16_kernel(const float* __res
     }
 }
 
-template <bool SWAP>
+// TIMING: CTA 0 accumulates SM cycles per wait / work item into dbg[0..23] (see the TK_* slots), for tuning only
+template <bool TIMING>
 __global__ void __launch_bounds__(NT_F, 1)
 score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned char* __restrict__ images,
                        const int* __restrict__ owned_slots, const int* __restrict__ n_owned_ptr, int x_rows, int n_chunks,
@@ -268,6 +272,10 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; next_pair(t); } }
             int s = 0;                 // image stage q % NW and its phase (q / NW) & 1, kept incrementally
             uint32_t sph = 0;
+            const bool tk_on = TIMING && blockIdx.x == 0;
+            long long tk[TK_N] = {};
+            long long tk_t = TIMING ? clock64() : 0;
+            const long long tk_0 = tk_t;
             if (warp == MMA1_WARP) {
                 const uint64_t dw1 = smem_desc_sw128(S.w1[0]);
                 PairCursor c1 = first_pair();
@@ -275,8 +283,11 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                 for (int q = 0; q < n_pairs; ++q) {
                     const int r = q & 1;
                     if (c1.ord != unit1) { mbar_wait(&S.bar_xt, (uint32_t)(c1.ord & 1)); unit1 = c1.ord; }   // tile parked
+                    FT(TK_1_XT);
                     mbar_wait(&S.bar_w1[s], sph);
+                    FT(TK_1_W);
                     if (q >= NB) mbar_wait(&S.bar_d1free[r], (uint32_t)(((q - NB) >> 1) & 1));
+                    FT(TK_1_FREE);
                     tc_fence_after();
                     const uint32_t d1 = tmem + C_D1 + 32 * r, xh = tmem + C_X, xl = tmem + C_XLO;
                     const uint64_t bw = dw1 + (uint64_t)((s * 2 * W1_BYTES) >> 4);
@@ -292,14 +303,19 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     tc_commit(&S.bar_w1free[s]);
                     next_pair(c1);
                     if (++s == NW) { s = 0; sph ^= 1u; }
+                    FT(TK_1_ISSUE);
                 }
+                if (tk_on) tk[TK_TOTAL] = clock64() - tk_0;
             } else if (warp == MMA1B_WARP) {
                 const uint64_t dw32 = smem_desc_sw64(S.w32[0]);
                 for (int q = 0; q < n_pairs; ++q) {
                     const int r = q & 1;
                     mbar_wait(&S.bar_h1[r], (uint32_t)((q >> 1) & 1));
+                    FT(TK_1B_H);
                     mbar_wait(&S.bar_w32[s], sph);
+                    FT(TK_1B_W);
                     if (q >= NB) mbar_wait(&S.bar_d1bfree[r], (uint32_t)(((q - NB) >> 1) & 1));
+                    FT(TK_1B_FREE);
                     tc_fence_after();
                     const uint32_t d = tmem + C_D1B + 32 * r, ah = tmem + C_D1 + 32 * r, al = ah + 16;
                     const uint64_t bw = dw32 + (uint64_t)((s * 2 * W32_BYTES) >> 4);
@@ -314,14 +330,18 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     tc_commit(&S.bar_w32free[s]);
                     tc_commit(&S.bar_d1free[r]);
                     if (++s == NW) { s = 0; sph ^= 1u; }
+                    FT(TK_1B_ISSUE);
                 }
             } else {
                 const uint64_t dw4 = smem_desc_sw64(S.w4[0]);
                 for (int q = 0; q < n_pairs; ++q) {
                     const int r = q & 1;
                     mbar_wait(&S.bar_h2[r], (uint32_t)((q >> 1) & 1));
+                    FT(TK_2_H);
                     mbar_wait(&S.bar_w4[s], sph);
+                    FT(TK_2_W);
                     if (q >= 2) mbar_wait(&S.bar_d2free[r], (uint32_t)(((q - 2) >> 1) & 1));
+                    FT(TK_2_FREE);
                     tc_fence_after();
                     const uint32_t d = tmem + C_D2 + 128 * r, ah = tmem + C_D1B + 32 * r, al = ah + 16;
                     const uint64_t bw = dw4 + (uint64_t)((s * 2 * W4_BYTES) >> 4);
@@ -336,8 +356,10 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     tc_commit(&S.bar_w4free[s]);
                     tc_commit(&S.bar_d1bfree[r]);
                     if (++s == NW) { s = 0; sph ^= 1u; }
+                    FT(TK_2_ISSUE);
                 }
             }
+            if (tk_on) for (int i = 0; i < TK_N; ++i) if (tk[i]) dbg[i] = (unsigned long long)tk[i];
         }
         __syncwarp();
     } else if (warp == LOAD_WARP) {
@@ -389,8 +411,8 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                 for (int q4 = 0; q4 < 8; ++q4) {
                     float4 xv = *reinterpret_cast<const float4*>(xb + ((q4 ^ (r & 7)) << 4));
                     if (cb == 3 && q4 == 4) xv.w = 1.f;                    // k = 96 + 16 + 3 = 115: the bias column
-                    split2<SWAP>(xv.x, xv.y, hi[q4 * 2], lo[q4 * 2]);
-                    split2<SWAP>(xv.z, xv.w, hi[q4 * 2 + 1], lo[q4 * 2 + 1]);
+                    split2(xv.x, xv.y, hi[q4 * 2], lo[q4 * 2]);
+                    split2(xv.z, xv.w, hi[q4 * 2 + 1], lo[q4 * 2 + 1]);
                 }
                 tmem_st16(xb_t + C_X + cb * 16, hi);
                 tmem_st16(xb_t + C_XLO + cb * 16, lo);
@@ -405,7 +427,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             tc_fence_after();
             tmem_ld32(lane_base + col, v);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) split2_relu<SWAP>(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]), hi[j], lo[j]);
+            for (int j = 0; j < 16; ++j) split2_relu(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]), hi[j], lo[j]);
             tmem_st16(lane_base + col, hi);            // in place: the fp16 operand replaces the fp32 accumulator it came from
             tmem_st16(lane_base + col + 16, lo);
             tmem_st_wait();
@@ -426,27 +448,35 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         PairCursor ce1 = first_pair();                // pair e1 handles next
         int qe1 = 0, qe1b = 0, parked = 0;
         auto uniform = [&](bool ok) -> bool { return __all_sync(0xffffffffu, ok) != 0; };
+        const bool tk_on = TIMING && blockIdx.x == 0 && tid == 0;
+        long long tk[TK_N] = {};
+        long long tk_t = TIMING ? clock64() : 0;
         while (qe1b < n_pairs) {
             bool did = false;
+            FT(TK_A_IDLE);
             if (parked < n_units_ne && (qe1 >= n_pairs || ce1.ord >= parked) &&
                 uniform(mbar_test(&S.bar_x, (uint32_t)(parked & 1)))) {
                 park_x(parked);
                 ++parked;
                 did = true;
+                FT(TK_A_PARK);
             }
             if (qe1 < n_pairs && uniform(mbar_test(&S.bar_d1[qe1 & (NB - 1)], (uint32_t)((qe1 / NB) & 1)))) {
                 e1(qe1);
                 next_pair(ce1);
                 ++qe1;
                 did = true;
+                FT(TK_A_E1);
             }
             if (qe1b < qe1 && uniform(mbar_test(&S.bar_d1b[qe1b & (NB - 1)], (uint32_t)((qe1b / NB) & 1)))) {
                 e1b(qe1b);
                 ++qe1b;
                 did = true;
+                FT(TK_A_E1B);
             }
             if (!did) __nanosleep(20);
         }
+        if (tk_on) for (int i = TK_A_PARK; i <= TK_A_IDLE; ++i) dbg[i] = (unsigned long long)tk[i];
     } else {
         // ---- group B: epilogue 2 (squared error against the row kept in registers), partial sums.  Eight warps: warps
         //      4-7 take output columns 0..63 of their lane quarter, warps 8-11 columns 64..127, so a pair costs each
@@ -459,7 +489,11 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         PairCursor c = first_pair();
         int g = 0, ut = 0;
         bool fresh = true;
+        const bool tk_on = TIMING && blockIdx.x == 0 && tid == 128;
+        long long tk[TK_N] = {};
+        long long tk_t = TIMING ? clock64() : 0;
         while (c.ok) {
+            FT(TK_B_REST);
             if (fresh) {
                 mbar_wait(&S.bar_x, (uint32_t)(ut & 1));
 #pragma unroll
@@ -472,10 +506,12 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                 }
                 mbar_arrive(&S.bar_xfree);
                 fresh = false;
+                FT(TK_B_ENTRY);
             }
             const int b = g & 1;
             mbar_wait(&S.bar_d2[b], (uint32_t)((g >> 1) & 1));
             tc_fence_after();
+            FT(TK_B_WAIT);
             float2 acc[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
             auto acc_block = [&](int cb) {            // four independent chains: the FMAs pipeline
 #pragma unroll
@@ -490,6 +526,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             tmem_ld32(d2 + 32, v);
             tc_fence_before();
             mbar_arrive(&S.bar_d2free[b]);            // this thread's share of D2[b] is in registers
+            FT(TK_B_HOLD);
             acc_block(1);
             const int row = c.tile * TROWS + r;
             float sse = row < x_rows ? ((acc[0].x + acc[0].y) + (acc[1].x + acc[1].y)) + ((acc[2].x + acc[2].y) + (acc[3].x + acc[3].y)) : 0.f;
@@ -501,6 +538,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             c = cn;
             ++g;
         }
+        if (tk_on) for (int i = TK_B_WAIT; i <= TK_B_ENTRY; ++i) dbg[i] = (unsigned long long)tk[i];
     }
     tc_fence_before();
     __syncthreads();
@@ -587,9 +625,7 @@ extern "C" int fm_score_fused_f16(const FmFusedScoreArgs* a, void* stream) {
     static int sms = 0;
     if (!sms) { int dev; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
     const size_t smem = sizeof(FSmem);
-    static int swap_halves = -1;
-    if (swap_halves < 0) { const char* e = getenv("FM_F16_SWAP"); swap_halves = (e && e[0] == '1') ? 1 : 0; }
-    auto kern = swap_halves ? score_fused_f16_kernel<true> : score_fused_f16_kernel<false>;
+    auto kern = a->dbg_cycles ? score_fused_f16_kernel<true> : score_fused_f16_kernel<false>;
     err = cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return (int)err;
     // chunks of models per tile: balance the units over the SMs (same cost model as score_multi_tc.cu)
