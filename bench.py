@@ -127,11 +127,12 @@ def build_engine(args, comm, n_global, first, cnt):
     sh_host.valid = Segmented.from_list([c.valid for c in prepared])
     sh = sh_host.to(comm.device)
     # pinned host copies of what an IoT gateway would deliver fresh every round (local training data)
-    pin_train = sh_host.train.x.pin_memory()
+    pin = (lambda t: t.pin_memory()) if comm.device.type == "cuda" else (lambda t: t)
+    pin_train = pin(sh_host.train.x)
     v0, v1 = sh_host.valid.off_host[first], sh_host.valid.off_host[first + cnt]
-    pin_valid = sh_host.valid.x[v0:v1].pin_memory()
+    pin_valid = pin(sh_host.valid.x[v0:v1])
     cfg = ExperimentConfig(num_participants=args.participation, epoch=args.epochs, lr_rate=1e-3, shrink_lambda=5,
-                           network_size=n_global, batch_size=12, backend="cuda", write_latents=False,
+                           network_size=n_global, batch_size=12, backend=getattr(args, "backend", "cuda"), write_latents=False,
                            save_client_models=False, reference_compat=True,
                            score_precision=args.score_precision, aggregation=args.aggregation,
                            topology=args.topology, topology_k=args.topology_k, topology_seed=args.seed)
@@ -163,22 +164,29 @@ def run_check(args, comm, n_global, first, cnt):
     from fedmse_decentralized_b200.parallel import Comm
     R = args.check_rounds
     eng, sh, pt, pv = build_engine(args, comm, n_global, first, cnt)
+    seed_all(args.seed + 17)     # the round loop's host RNG (selection, tie-break jitter) starts from the same state in both arms
     multi = bench_loop(eng, pt, pv, R)
-    torch.cuda.synchronize(comm.device)
+    if comm.device.type == "cuda":
+        torch.cuda.synchronize(comm.device)
     eng.close()
     comm.barrier()
     verdict = None
     if comm.rank == 0:
         solo = Comm(rank=0, world=1, device=comm.device)
         eng1, sh1, pt1, pv1 = build_engine(args, solo, n_global, 0, n_global)
+        seed_all(args.seed + 17)
         single = bench_loop(eng1, pt1, pv1, R)
-        torch.cuda.synchronize(comm.device)
+        if comm.device.type == "cuda":
+            torch.cuda.synchronize(comm.device)
         bad = []
         worst = 0.0
         for r, (a, b) in enumerate(zip(multi, single)):
-            if a.selected != b.selected: bad.append(f"round {r}: selection differs")
+            if a.selected != b.selected: bad.append(f"round {r}: selection differs ({a.selected[:4]} vs {b.selected[:4]})")
             if a.aggregator != b.aggregator: bad.append(f"round {r}: aggregator {a.aggregator} vs {b.aggregator}")
-            if a.epochs_run != b.epochs_run: bad.append(f"round {r}: epochs run differ")
+            if a.epochs_run != b.epochs_run:
+                df = [(g, a.epochs_run.get(g), b.epochs_run.get(g)) for g in sorted(set(a.epochs_run) | set(b.epochs_run))
+                      if a.epochs_run.get(g) != b.epochs_run.get(g)]
+                bad.append(f"round {r}: epochs run differ for {len(df)} clients, e.g. {df[:3]}")
             if [v["is_verified"] for v in a.verification] != [v["is_verified"] for v in b.verification]:
                 bad.append(f"round {r}: verification verdicts differ")
             d = max(abs(x - y) for x, y in zip(a.client_metrics, b.client_metrics))
@@ -402,6 +410,7 @@ def main():
     ap.add_argument("--check", action="store_true",
                     help="no timing: run the scenario on the N ranks and on one GPU and assert equal results")
     ap.add_argument("--check-rounds", type=int, default=3)
+    ap.add_argument("--backend", default="cuda", choices=["cuda", "oracle"], help="oracle: CPU plumbing check of --check only")
     ap.add_argument("--score-precision", default="fp16x3", choices=["fp32", "tf32", "tf32x3", "fp16x3"],
                     help="scoring forwards: exact FFMA kernel, single-pass TF32 or error-compensated 3xTF32 on tcgen05")
     args = ap.parse_args()

@@ -79,10 +79,14 @@ def _world():
     return 2 if n < 4 else (4 if n < 8 else 8)
 
 
-def _same(one, many, n_clients):
+def _same(one, many, n_clients, auc_tol=1e-6):
+    """Discrete outcomes (aggregator ids, verdicts, epochs run) must be identical; AUCs within ``auc_tol``.  The merged
+    model is summed in a different order on N GPUs (per-rank partials added inside the NVSwitch) than on one (selection
+    order), i.e. it differs in the last bits, and over many rounds that flips the rank of a few near-tied test scores:
+    one swapped pair moves a client's AUC by 1 / (n+ n-) ~ 2e-5 here."""
     assert one["agg"] == many["agg"] and one["ver"] == many["ver"] and one["epochs"] == many["epochs"]
     for a, b in zip(one["metrics"], many["metrics"]):
-        assert len(a) == n_clients and max(abs(x - y) for x, y in zip(a, b)) < 1e-6
+        assert len(a) == n_clients and max(abs(x - y) for x, y in zip(a, b)) < auc_tol
 
 
 @pytest.mark.parametrize("agg,upd", [("elected", "mse_avg"), ("elected", "avg"), ("gossip", "mse_avg")])
@@ -104,7 +108,7 @@ def test_n_gpus_match_one_gpu_quota_exhaustion(tmp_path):
     world = _world()
     kw = dict(FM_CLIENTS=10, FM_ROUNDS=16, FM_PART=0.5, FM_PIPE=1)
     one, many = _run(1, tmp_path, "elected", **kw), _run(world, tmp_path, "elected", **kw)
-    _same(one, many, 10)
+    _same(one, many, 10, auc_tol=3e-4)
     assert -1 in one["agg"] or len(set(one["agg"])) >= 6
 
 
@@ -113,7 +117,7 @@ def test_n_gpus_match_one_gpu_pipelined_staged_64_clients(tmp_path, agg):
     """The bench's loop (pipelined rounds + staged uploads, tcgen05 scoring) on 64 clients x 6 rounds."""
     world = _world()
     kw = dict(FM_CLIENTS=64, FM_ROUNDS=6, FM_PART=0.5, FM_PIPE=1, FM_PREC="tf32x3", FM_TOPO="random-k")
-    _same(_run(1, tmp_path, agg, **kw), _run(world, tmp_path, agg, **kw), 64)
+    _same(_run(1, tmp_path, agg, **kw), _run(world, tmp_path, agg, **kw), 64, auc_tol=3e-4)
 
 
 def test_p2p_weighted_allreduce_matches_nccl(tmp_path):
