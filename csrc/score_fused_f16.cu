@@ -21,8 +21,9 @@
 //    the loop MMA2 -> squared error -> release -> next MMA2 set the pace of the kernel (ncu of the first two versions:
 //    1.7 k cycles per pair, tensor pipe 55 % active).  D1 / D1b are double buffered, the parked tile is single buffered
 //    in exchange (a unit boundary costs one parking, ~3 % at 62 models per unit).
-//  * No [models x rows] SSE matrix: each epilogue warp writes one partial sum per (model, tile); after a grid-wide
-//    barrier the CTAs reduce them in a fixed order to the per-model MSE (deterministic, replaces chunk_mean).
+//  * No [models x rows] SSE matrix: every squared-error thread adds its row's error to its own running sum per model
+//    (a fire-and-forget RED to a slot nobody else writes); after a grid-wide barrier the CTAs add those sums in a fixed
+//    order to the per-model MSE (deterministic, replaces chunk_mean).
 //
 // TMEM map (512 columns): X hi 0..63, lo 64..127 | D1/h1[r] 128+32r | D1b/h2[r] 192+32r (r = pair mod 2) | D2[b] 256+128b.
 // Warp roles: 0-3 tile parking + epilogue 1a, 4-7 epilogue 1b, 8-15 epilogue 2 (squared error; two warps per TMEM lane
@@ -50,7 +51,8 @@ constexpr int C_X = 0, C_XLO = 64, C_D1 = 128, C_D1B = C_D1 + 32 * NB, C_D2 = 25
 // W32 and W4 (K = 32): 64-B swizzle, one 64-byte row per output feature -- no padding travels.  The images are what
 // every SM pulls from L2 for every (tile, model) pair, and at ~42 B / clk / SM of L2 bandwidth the 56 KB of the first
 // layout (128-B rows everywhere, K padded to 64) cost 1.35 k cycles per pair, more than the 0.93 k of tensor work.
-constexpr int NW = 2;                       // shared-memory stages per image kind
+constexpr int NW = 3;                       // barrier slots per image kind (>= stages of every kind)
+constexpr int NW1 = 3, NW32 = 3, NW4 = 2;   // shared-memory stages: what fits next to the two 64 KB fp32 tiles
 constexpr int W1_BYTES = 2 * 4096;          // [32 n][128 k]  = two K-blocks of 32 rows x 128 B
 constexpr int W32_BYTES = 32 * 64;          // [32 n][32 k]
 constexpr int W4_BYTES = 128 * 64;          // [128 n][32 k]
@@ -61,14 +63,14 @@ constexpr float F16_MAX = 65504.f;
 // debug cycle slots (CTA 0): issuing threads 1 / 1b / 2: waits (tile or epilogue, image, free buffer) and issue;
 // parking+epilogue warp 0: park, e1, e1b, idle polling; squared-error warp 4: wait D2, until D2 released, rest, unit entry
 enum { TK_1_XT = 0, TK_1_W, TK_1_FREE, TK_1_ISSUE, TK_1B_H, TK_1B_W, TK_1B_FREE, TK_1B_ISSUE, TK_2_H, TK_2_W, TK_2_FREE, TK_2_ISSUE,
-       TK_A_PARK, TK_A_E1, TK_A_E1B, TK_A_IDLE, TK_B_WAIT, TK_B_HOLD, TK_B_REST, TK_B_ENTRY, TK_TOTAL, TK_N };
+       TK_A_PARK, TK_A_E1, TK_A_E1B, TK_A_IDLE, TK_B_WAIT, TK_B_HOLD, TK_B_REST, TK_B_ENTRY, TK_TOTAL, TK_A_E1WAIT, TK_A_E1BWAIT, TK_N };
 #define FT(slot) do { if (TIMING && tk_on) { const long long now_ = clock64(); tk[slot] += now_ - tk_t; tk_t = now_; } } while (0)
 
 struct FSmem {
     alignas(1024) unsigned char x[2][4 * XBLK];              // fp32 tiles of the current and the next unit (TMA, 128-B swizzle)
-    alignas(1024) unsigned char w1[NW][2 * W1_BYTES];        // hi | lo
-    alignas(1024) unsigned char w32[NW][2 * W32_BYTES];
-    alignas(1024) unsigned char w4[NW][2 * W4_BYTES];
+    alignas(1024) unsigned char w1[NW1][2 * W1_BYTES];       // hi | lo
+    alignas(1024) unsigned char w32[NW32][2 * W32_BYTES];
+    alignas(1024) unsigned char w4[NW4][2 * W4_BYTES];
     alignas(8) uint64_t bar_x[2], bar_xfree[2], bar_xt, bar_w1[NW], bar_w32[NW], bar_w4[NW], bar_w1free[NW], bar_w32free[NW], bar_w4free[NW], bar_d1[NB], bar_h1[NB], bar_d1b[NB], bar_d1free[NB], bar_d1bfree[NB],
         bar_h2[NB], bar_d2[2], bar_d2free[2];
     uint32_t tmem_base;
@@ -249,6 +251,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)), "r"(F_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
+    for (int i = tid; i < n_models * 256; i += NT_F) partial[(size_t)blockIdx.x * n_models * 256 + i] = 0.f;
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -304,7 +307,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     tc_commit(&S.bar_d1[r]);
                     tc_commit(&S.bar_w1free[s]);
                     next_pair(c1);
-                    if (++s == NW) { s = 0; sph ^= 1u; }
+                    if (++s == NW1) { s = 0; sph ^= 1u; }
                     FT(TK_1_ISSUE);
                 }
                 if (tk_on) tk[TK_TOTAL] = clock64() - tk_0;
@@ -331,7 +334,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     tc_commit(&S.bar_d1b[r]);
                     tc_commit(&S.bar_w32free[s]);
                     tc_commit(&S.bar_d1free[r]);
-                    if (++s == NW) { s = 0; sph ^= 1u; }
+                    if (++s == NW32) { s = 0; sph ^= 1u; }
                     FT(TK_1B_ISSUE);
                 }
             } else {
@@ -357,7 +360,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     tc_commit(&S.bar_d2[r]);
                     tc_commit(&S.bar_w4free[s]);
                     tc_commit(&S.bar_d1bfree[r]);
-                    if (++s == NW) { s = 0; sph ^= 1u; }
+                    if (++s == NW4) { s = 0; sph ^= 1u; }
                     FT(TK_2_ISSUE);
                 }
             }
@@ -387,14 +390,14 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     for (int kb = 0; kb < 4; ++kb) tma_load_2d(S.x[lx & 1] + kb * XBLK, &xmap, kb * 32, cx.tile * TROWS, &S.bar_x[lx & 1]);
                     next_unit(cx); ++lx;
                 }
-                if (l1 < n_pairs && (l1 < NW || mbar_test(&S.bar_w1free[l1 % NW], (uint32_t)((l1 / NW - 1) & 1)))) {
-                    load_img(S.w1[l1 % NW], cw1.m, IMG_W1, 2 * W1_BYTES, &S.bar_w1[l1 % NW]); next_pair(cw1); ++l1;
+                if (l1 < n_pairs && (l1 < NW1 || mbar_test(&S.bar_w1free[l1 % NW1], (uint32_t)((l1 / NW1 - 1) & 1)))) {
+                    load_img(S.w1[l1 % NW1], cw1.m, IMG_W1, 2 * W1_BYTES, &S.bar_w1[l1 % NW1]); next_pair(cw1); ++l1;
                 }
-                if (l32 < n_pairs && (l32 < NW || mbar_test(&S.bar_w32free[l32 % NW], (uint32_t)((l32 / NW - 1) & 1)))) {
-                    load_img(S.w32[l32 % NW], cw32.m, IMG_W32, 2 * W32_BYTES, &S.bar_w32[l32 % NW]); next_pair(cw32); ++l32;
+                if (l32 < n_pairs && (l32 < NW32 || mbar_test(&S.bar_w32free[l32 % NW32], (uint32_t)((l32 / NW32 - 1) & 1)))) {
+                    load_img(S.w32[l32 % NW32], cw32.m, IMG_W32, 2 * W32_BYTES, &S.bar_w32[l32 % NW32]); next_pair(cw32); ++l32;
                 }
-                if (l4 < n_pairs && (l4 < NW || mbar_test(&S.bar_w4free[l4 % NW], (uint32_t)((l4 / NW - 1) & 1)))) {
-                    load_img(S.w4[l4 % NW], cw4.m, IMG_W4, 2 * W4_BYTES, &S.bar_w4[l4 % NW]); next_pair(cw4); ++l4;
+                if (l4 < n_pairs && (l4 < NW4 || mbar_test(&S.bar_w4free[l4 % NW4], (uint32_t)((l4 / NW4 - 1) & 1)))) {
+                    load_img(S.w4[l4 % NW4], cw4.m, IMG_W4, 2 * W4_BYTES, &S.bar_w4[l4 % NW4]); next_pair(cw4); ++l4;
                 }
             }
         }
@@ -428,8 +431,12 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             mbar_arrive(&S.bar_xt);
             mbar_arrive(&S.bar_xfree[ut & 1]);
         };
-        auto relu_split = [&](uint32_t col, uint64_t* bar_in, uint64_t* bar_out, uint32_t ph) {
+        const bool tk_on = TIMING && blockIdx.x == 0 && lane == 0 && wq == 0;
+        long long tk[TK_N] = {};
+        long long tk_t = TIMING ? clock64() : 0;
+        auto relu_split = [&](uint32_t col, uint64_t* bar_in, uint64_t* bar_out, uint32_t ph, int wait_slot) {
             mbar_wait(bar_in, ph);
+            FT(wait_slot);
             tc_fence_after();
             tmem_ld32(lane_base + col, v);
 #pragma unroll
@@ -442,9 +449,6 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         };
         int n_pairs = 0;
         { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; next_pair(t); } }
-        const bool tk_on = TIMING && blockIdx.x == 0 && lane == 0 && wq == 0;
-        long long tk[TK_N] = {};
-        long long tk_t = TIMING ? clock64() : 0;
         if (warp < E1B_WARP0) {
             // the X columns of TMEM are single buffered: the next unit's tile is parked right after epilogue 1a of this
             // unit's last pair (whose MMA1, the last reader, has retired by then)
@@ -453,21 +457,21 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             FT(TK_A_PARK);
             for (int q = 0; q < n_pairs; ++q) {
                 const int rb = q & (NB - 1);
-                relu_split(C_D1 + 32 * rb, &S.bar_d1[rb], &S.bar_h1[rb], (uint32_t)((q / NB) & 1));
+                relu_split(C_D1 + 32 * rb, &S.bar_d1[rb], &S.bar_h1[rb], (uint32_t)((q / NB) & 1), TK_A_E1WAIT);
                 FT(TK_A_E1);
                 PairCursor cn = c;
                 next_pair(cn);
                 if (cn.ok && cn.ord != c.ord) { park_x(cn.ord); FT(TK_A_PARK); }
                 c = cn;
             }
-            if (tk_on) { dbg[TK_A_PARK] = (unsigned long long)tk[TK_A_PARK]; dbg[TK_A_E1] = (unsigned long long)tk[TK_A_E1]; }
+            if (tk_on) { dbg[TK_A_PARK] = (unsigned long long)tk[TK_A_PARK]; dbg[TK_A_E1] = (unsigned long long)tk[TK_A_E1]; dbg[TK_A_E1WAIT] = (unsigned long long)tk[TK_A_E1WAIT]; }
         } else {
             for (int q = 0; q < n_pairs; ++q) {
                 const int rb = q & (NB - 1);
-                relu_split(C_D1B + 32 * rb, &S.bar_d1b[rb], &S.bar_h2[rb], (uint32_t)((q / NB) & 1));
+                relu_split(C_D1B + 32 * rb, &S.bar_d1b[rb], &S.bar_h2[rb], (uint32_t)((q / NB) & 1), TK_A_E1BWAIT);
                 FT(TK_A_E1B);
             }
-            if (tk_on) dbg[TK_A_E1B] = (unsigned long long)tk[TK_A_E1B];
+            if (tk_on) { dbg[TK_A_E1B] = (unsigned long long)tk[TK_A_E1B]; dbg[TK_A_E1BWAIT] = (unsigned long long)tk[TK_A_E1BWAIT]; }
         }
     } else {
         // ---- group B: epilogue 2 (squared error), partial sums.  Eight warps: warps 8-11 take output columns 0..63 of
@@ -476,10 +480,13 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         const int wq = warp & 3, half = (warp - B_WARP0) >> 2;
         const int r = wq * 32 + lane;
         const uint32_t lane_base = tmem + ((uint32_t)(wq * 32) << 16);
-        uint32_t v[32];
+        uint32_t v0[32], v1[32];
         PairCursor c = first_pair();
         int g = 0;
         bool fresh = true;
+        // per-thread running sums: lanes[cta][model][256] -- every slot has exactly one writer, in program order, so the
+        // fire-and-forget reductions below are deterministic and cost no shuffle, no wait and no address arithmetic
+        float* my_lane = partial + ((size_t)blockIdx.x * n_models) * 256 + (warp - B_WARP0) * 32 + lane;
         const bool tk_on = TIMING && blockIdx.x == 0 && tid == B_WARP0 * 32;
         long long tk[TK_N] = {};
         long long tk_t = TIMING ? clock64() : 0;
@@ -493,7 +500,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             tc_fence_after();
             FT(TK_B_WAIT);
             float2 acc[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
-            auto acc_block = [&](int cb) {            // 32 columns: four independent chains, x from shared memory
+            auto acc_block = [&](const uint32_t (&v)[32], int cb) {     // 32 columns: four independent chains, x from shared memory
 #pragma unroll
                 for (int j4 = 0; j4 < 8; ++j4) {
                     const int qq = half * 16 + cb * 8 + j4;          // float4 index inside the 128-float row (pad columns are 0)
@@ -504,18 +511,15 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     acc[(2 * j4 + 1) & 3] = ffma2(e1, e1, acc[(2 * j4 + 1) & 3]);
                 }
             };
-            const uint32_t d2 = lane_base + C_D2 + 128 * b + 64 * half;
-            tmem_ld32(d2, v);
-            acc_block(0);
-            tmem_ld32(d2 + 32, v);
+            tmem_ld64(lane_base + C_D2 + 128 * b + 64 * half, v0, v1);      // both halves of this thread's share, one wait
             tc_fence_before();
-            mbar_arrive(&S.bar_d2free[b]);            // this thread's share of D2[b] is in registers
+            mbar_arrive(&S.bar_d2free[b]);            // D2[b] is in registers: MMA2 of pair g + 2 may overwrite it
             FT(TK_B_HOLD);
-            acc_block(1);
+            acc_block(v0, 0);
+            acc_block(v1, 1);
             const int row = c.tile * TROWS + r;
-            float sse = row < x_rows ? ((acc[0].x + acc[0].y) + (acc[1].x + acc[1].y)) + ((acc[2].x + acc[2].y) + (acc[3].x + acc[3].y)) : 0.f;
-            sse = warp_sum(sse);
-            if (lane == 0) partial[((size_t)c.m * n_tiles + c.tile) * 8 + half * 4 + wq] = sse;
+            const float sse = row < x_rows ? ((acc[0].x + acc[0].y) + (acc[1].x + acc[1].y)) + ((acc[2].x + acc[2].y) + (acc[3].x + acc[3].y)) : 0.f;
+            atomicAdd(my_lane + (size_t)c.m * 256, sse);              // result unused: a RED, nobody else writes this slot
             PairCursor cn = c;
             next_pair(cn);
             if (!cn.ok || cn.ord != c.ord) { mbar_arrive(&S.bar_xfree[ub]); fresh = true; }   // done with this unit's tile
@@ -524,6 +528,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         }
         if (tk_on) for (int i = TK_B_WAIT; i <= TK_B_ENTRY; ++i) dbg[i] = (unsigned long long)tk[i];
     }
+    __threadfence();                         // this thread's running sums are visible device-wide before the grid barrier
     tc_fence_before();
     __syncthreads();
     if (warp == MMA1_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(F_TMEM_COLS));
@@ -545,9 +550,9 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
     }
     __syncthreads();
     for (int m = blockIdx.x; m < n_models; m += gridDim.x) {
-        const float* pm = partial + (size_t)m * n_tiles * 8;
         double s = 0.0;
-        for (int i = tid; i < n_tiles * 8; i += NT_F) s += (double)__ldcg(pm + i);
+        for (int i = tid; i < (int)gridDim.x * 256; i += NT_F)       // fixed order: thread-strided, then warps in order
+            s += (double)__ldcg(partial + ((size_t)(i >> 8) * n_models + m) * 256 + (i & 255));
         s = warp_sum(s);
         if (lane == 0) S.red[warp] = s;
         __syncthreads();
@@ -590,7 +595,8 @@ int encode_x_map_f(CUtensorMap* map, const float* base, int64_t rows) {
 
 extern "C" int64_t fm_score_fused_scratch_floats(int64_t x_rows, int32_t n_models) {
     const int64_t n_tiles = (x_rows + fm::tc::TROWS - 1) / fm::tc::TROWS;
-    return n_tiles * 8 * (int64_t)(n_models > 0 ? n_models : 1);
+    (void)n_tiles;                                   // per-thread running sums: [CTAs <= 160][models][256]
+    return 160 * 256 * (int64_t)(n_models > 0 ? n_models : 1);
 }
 
 extern "C" int fm_score_fused_f16(const FmFusedScoreArgs* a, void* stream) {
