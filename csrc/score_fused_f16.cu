@@ -21,14 +21,12 @@
 //    the loop MMA2 -> squared error -> release -> next MMA2 set the pace of the kernel (ncu of the first two versions:
 //    1.7 k cycles per pair, tensor pipe 55 % active).  D1 / D1b are double buffered, the parked tile is single buffered
 //    in exchange (a unit boundary costs one parking, ~3 % at 62 models per unit).
-//  * No [models x rows] SSE matrix: every squared-error thread adds its row's error to its own running sum per model
-//    (a fire-and-forget RED to a slot nobody else writes); after a grid-wide barrier the CTAs add those sums in a fixed
-//    order to the per-model MSE (deterministic, replaces chunk_mean).
+//  * No [models x rows] SSE matrix: each epilogue warp writes one partial sum per (model, tile); after a grid-wide
+//    barrier the CTAs reduce them in a fixed order to the per-model MSE (deterministic, replaces chunk_mean).
 //
 // TMEM map (512 columns): X hi 0..63, lo 64..127 | D1/h1[r] 128+32r | D1b/h2[r] 192+32r (r = pair mod 2) | D2[b] 256+128b.
-// Warp roles: 0-3 tile parking + epilogue 1a, 4-7 epilogue 1b, 8-15 epilogue 2 (squared error; two warps per TMEM lane
-// quarter, half of the output columns each), 16 / 17 / 18 MMA issue (one thread per GEMM stage), 19 weight images + X
-// tiles (TMA).  Shared memory: two fp32 tiles (current / next unit, 128 KB) + two stages of each operand image (72 KB).
+// Warp roles: 0-3 epilogues 1a/1b + tile parking, 4-11 epilogue 2 (squared error; two warps per TMEM lane quarter, half
+// of the output columns each), 12 / 13 / 14 MMA issue (one thread per GEMM stage), 15 weight images + X tiles (TMA).
 //
 // Tensor-pipe issue order in steady state:  ... MMA1(g+2)  MMA1b(g+1)  MMA2(g)  MMA1(g+3) ...
 // TMA multicast is not used; the operand images and the dev matrix live in this GPU's memory.
@@ -42,8 +40,8 @@ namespace tcf {
 
 using namespace fm::tc;
 
-constexpr int NT_F = 640;                                 // 20 warps, 5 per SM sub-partition: 96 registers per thread
-constexpr int E1B_WARP0 = 4, B_WARP0 = 8, MMA1_WARP = 16, MMA1B_WARP = 17, MMA2_WARP = 18, LOAD_WARP = 19;
+constexpr int NT_F = 512;                                 // 16 warps, 4 per SM sub-partition: 128 registers per thread
+constexpr int MMA1_WARP = 12, MMA1B_WARP = 13, MMA2_WARP = 14, LOAD_WARP = 15;
 constexpr int F_TMEM_COLS = 512;
 constexpr int NB = 2;                                     // ring depth of the D1 / D1b accumulators (pairs in flight per stage)
 constexpr int C_X = 0, C_XLO = 64, C_D1 = 128, C_D1B = C_D1 + 32 * NB, C_D2 = 256;   // D1[r] = 128 + 32 r, D1b[r] = 192 + 32 r, D2[b] = 256 + 128 b
@@ -51,8 +49,7 @@ constexpr int C_X = 0, C_XLO = 64, C_D1 = 128, C_D1B = C_D1 + 32 * NB, C_D2 = 25
 // W32 and W4 (K = 32): 64-B swizzle, one 64-byte row per output feature -- no padding travels.  The images are what
 // every SM pulls from L2 for every (tile, model) pair, and at ~42 B / clk / SM of L2 bandwidth the 56 KB of the first
 // layout (128-B rows everywhere, K padded to 64) cost 1.35 k cycles per pair, more than the 0.93 k of tensor work.
-constexpr int NW = 3;                       // barrier slots per image kind (>= stages of every kind)
-constexpr int NW1 = 3, NW32 = 3, NW4 = 2;   // shared-memory stages: what fits next to the two 64 KB fp32 tiles
+constexpr int NW = 3;                       // shared-memory stages per image kind
 constexpr int W1_BYTES = 2 * 4096;          // [32 n][128 k]  = two K-blocks of 32 rows x 128 B
 constexpr int W32_BYTES = 32 * 64;          // [32 n][32 k]
 constexpr int W4_BYTES = 128 * 64;          // [128 n][32 k]
@@ -63,18 +60,18 @@ constexpr float F16_MAX = 65504.f;
 // debug cycle slots (CTA 0): issuing threads 1 / 1b / 2: waits (tile or epilogue, image, free buffer) and issue;
 // parking+epilogue warp 0: park, e1, e1b, idle polling; squared-error warp 4: wait D2, until D2 released, rest, unit entry
 enum { TK_1_XT = 0, TK_1_W, TK_1_FREE, TK_1_ISSUE, TK_1B_H, TK_1B_W, TK_1B_FREE, TK_1B_ISSUE, TK_2_H, TK_2_W, TK_2_FREE, TK_2_ISSUE,
-       TK_A_PARK, TK_A_E1, TK_A_E1B, TK_A_IDLE, TK_B_WAIT, TK_B_HOLD, TK_B_REST, TK_B_ENTRY, TK_TOTAL, TK_A_E1WAIT, TK_A_E1BWAIT, TK_N };
+       TK_A_PARK, TK_A_E1, TK_A_E1B, TK_A_IDLE, TK_B_WAIT, TK_B_HOLD, TK_B_REST, TK_B_ENTRY, TK_TOTAL, TK_N };
 #define FT(slot) do { if (TIMING && tk_on) { const long long now_ = clock64(); tk[slot] += now_ - tk_t; tk_t = now_; } } while (0)
 
 struct FSmem {
-    alignas(1024) unsigned char x[2][4 * XBLK];              // fp32 tiles of the current and the next unit (TMA, 128-B swizzle)
-    alignas(1024) unsigned char w1[NW1][2 * W1_BYTES];       // hi | lo
-    alignas(1024) unsigned char w32[NW32][2 * W32_BYTES];
-    alignas(1024) unsigned char w4[NW4][2 * W4_BYTES];
-    alignas(8) uint64_t bar_x[2], bar_xfree[2], bar_xt, bar_w1[NW], bar_w32[NW], bar_w4[NW], bar_w1free[NW], bar_w32free[NW], bar_w4free[NW], bar_d1[NB], bar_h1[NB], bar_d1b[NB], bar_d1free[NB], bar_d1bfree[NB],
+    alignas(1024) unsigned char x[4 * XBLK];                 // fp32 staging of one 128-row tile (TMA, 128-B swizzle)
+    alignas(1024) unsigned char w1[NW][2 * W1_BYTES];        // hi | lo
+    alignas(1024) unsigned char w32[NW][2 * W32_BYTES];
+    alignas(1024) unsigned char w4[NW][2 * W4_BYTES];
+    alignas(8) uint64_t bar_x, bar_xfree, bar_xt, bar_w1[NW], bar_w32[NW], bar_w4[NW], bar_w1free[NW], bar_w32free[NW], bar_w4free[NW], bar_d1[NB], bar_h1[NB], bar_d1b[NB], bar_d1free[NB], bar_d1bfree[NB],
         bar_h2[NB], bar_d2[2], bar_d2free[2];
     uint32_t tmem_base;
-    double red[20];
+    double red[16];
 };
 
 // byte offset of fp16 element (row, k) inside a [rows x 64 fp16] K-block with the 128-B swizzle
@@ -234,8 +231,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
     auto next_pair = [&](PairCursor& c) { if (++c.m >= c.m1) next_unit(c); };
 
     if (tid == 0) {
-        mbar_init(&S.bar_x[0], 1); mbar_init(&S.bar_x[1], 1); mbar_init(&S.bar_xfree[0], 384); mbar_init(&S.bar_xfree[1], 384);
-        mbar_init(&S.bar_xt, 128);
+        mbar_init(&S.bar_x, 1); mbar_init(&S.bar_xfree, 384); mbar_init(&S.bar_xt, 128);
         for (int b = 0; b < NW; ++b) {
             mbar_init(&S.bar_w1[b], 1); mbar_init(&S.bar_w32[b], 1); mbar_init(&S.bar_w4[b], 1);
             mbar_init(&S.bar_w1free[b], 1); mbar_init(&S.bar_w32free[b], 1); mbar_init(&S.bar_w4free[b], 1);
@@ -251,7 +247,6 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)), "r"(F_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
-    for (int i = tid; i < n_models * 256; i += NT_F) partial[(size_t)blockIdx.x * n_models * 256 + i] = 0.f;
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -307,7 +302,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     tc_commit(&S.bar_d1[r]);
                     tc_commit(&S.bar_w1free[s]);
                     next_pair(c1);
-                    if (++s == NW1) { s = 0; sph ^= 1u; }
+                    if (++s == NW) { s = 0; sph ^= 1u; }
                     FT(TK_1_ISSUE);
                 }
                 if (tk_on) tk[TK_TOTAL] = clock64() - tk_0;
@@ -334,7 +329,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     tc_commit(&S.bar_d1b[r]);
                     tc_commit(&S.bar_w32free[s]);
                     tc_commit(&S.bar_d1free[r]);
-                    if (++s == NW32) { s = 0; sph ^= 1u; }
+                    if (++s == NW) { s = 0; sph ^= 1u; }
                     FT(TK_1B_ISSUE);
                 }
             } else {
@@ -360,7 +355,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     tc_commit(&S.bar_d2[r]);
                     tc_commit(&S.bar_w4free[s]);
                     tc_commit(&S.bar_d1bfree[r]);
-                    if (++s == NW4) { s = 0; sph ^= 1u; }
+                    if (++s == NW) { s = 0; sph ^= 1u; }
                     FT(TK_2_ISSUE);
                 }
             }
@@ -383,39 +378,35 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                 bulk_load(dst, images + (size_t)m * FM_TC_IMAGE_BYTES + off, bytes, bar);
             };
             while (l1 < n_pairs || l32 < n_pairs || l4 < n_pairs || lx < n_units_ne) {
-                // tile of unit lx into buffer lx & 1, free once unit lx - 2 is parked in TMEM and its squared errors are done
-                if (lx < n_units_ne && (lx < 2 || mbar_test(&S.bar_xfree[lx & 1], (uint32_t)(((lx - 2) >> 1) & 1)))) {
-                    mbar_expect_tx(&S.bar_x[lx & 1], 4u * XBLK);
+                if (lx < n_units_ne && (lx == 0 || mbar_test(&S.bar_xfree, (uint32_t)((lx - 1) & 1)))) {
+                    mbar_expect_tx(&S.bar_x, 4u * XBLK);
 #pragma unroll
-                    for (int kb = 0; kb < 4; ++kb) tma_load_2d(S.x[lx & 1] + kb * XBLK, &xmap, kb * 32, cx.tile * TROWS, &S.bar_x[lx & 1]);
+                    for (int kb = 0; kb < 4; ++kb) tma_load_2d(S.x + kb * XBLK, &xmap, kb * 32, cx.tile * TROWS, &S.bar_x);
                     next_unit(cx); ++lx;
                 }
-                if (l1 < n_pairs && (l1 < NW1 || mbar_test(&S.bar_w1free[l1 % NW1], (uint32_t)((l1 / NW1 - 1) & 1)))) {
-                    load_img(S.w1[l1 % NW1], cw1.m, IMG_W1, 2 * W1_BYTES, &S.bar_w1[l1 % NW1]); next_pair(cw1); ++l1;
+                if (l1 < n_pairs && (l1 < NW || mbar_test(&S.bar_w1free[l1 % NW], (uint32_t)((l1 / NW - 1) & 1)))) {
+                    load_img(S.w1[l1 % NW], cw1.m, IMG_W1, 2 * W1_BYTES, &S.bar_w1[l1 % NW]); next_pair(cw1); ++l1;
                 }
-                if (l32 < n_pairs && (l32 < NW32 || mbar_test(&S.bar_w32free[l32 % NW32], (uint32_t)((l32 / NW32 - 1) & 1)))) {
-                    load_img(S.w32[l32 % NW32], cw32.m, IMG_W32, 2 * W32_BYTES, &S.bar_w32[l32 % NW32]); next_pair(cw32); ++l32;
+                if (l32 < n_pairs && (l32 < NW || mbar_test(&S.bar_w32free[l32 % NW], (uint32_t)((l32 / NW - 1) & 1)))) {
+                    load_img(S.w32[l32 % NW], cw32.m, IMG_W32, 2 * W32_BYTES, &S.bar_w32[l32 % NW]); next_pair(cw32); ++l32;
                 }
-                if (l4 < n_pairs && (l4 < NW4 || mbar_test(&S.bar_w4free[l4 % NW4], (uint32_t)((l4 / NW4 - 1) & 1)))) {
-                    load_img(S.w4[l4 % NW4], cw4.m, IMG_W4, 2 * W4_BYTES, &S.bar_w4[l4 % NW4]); next_pair(cw4); ++l4;
+                if (l4 < n_pairs && (l4 < NW || mbar_test(&S.bar_w4free[l4 % NW], (uint32_t)((l4 / NW - 1) & 1)))) {
+                    load_img(S.w4[l4 % NW], cw4.m, IMG_W4, 2 * W4_BYTES, &S.bar_w4[l4 % NW]); next_pair(cw4); ++l4;
                 }
             }
         }
         __syncwarp();
-    } else if (warp < B_WARP0) {
-        // ---- epilogue warps between the GEMMs.  Warps 0-3: tile parking + epilogue 1a (h1 of every pair); warps 4-7:
-        //      epilogue 1b (h2).  Each is a straight line of blocking waits.  (One group doing both was the pace-maker of
-        //      the kernel: ~650 cycles per ReLU + split hop on a lone warp per sub-partition, 1.3 k per pair.) ----
-        const int wq = warp & 3;
-        const int r = wq * 32 + lane;
-        const uint32_t lane_base = tmem + ((uint32_t)(wq * 32) << 16);
+    } else if (warp < 4) {
+        // ---- group A: parks tiles in TMEM, epilogues 1a (h1) and 1b (h2) of every pair ----
+        const int r = warp * 32 + lane;
+        const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
         uint32_t v[32], hi[16], lo[16];
         auto park_x = [&](int ut) {                   // fp32 tile -> fp16 head + remainder, one row per thread, k = 115 := 1
-            mbar_wait(&S.bar_x[ut & 1], (uint32_t)((ut >> 1) & 1));
-            const unsigned char* xs = S.x[ut & 1];
+            mbar_wait(&S.bar_x, (uint32_t)(ut & 1));
+            const uint32_t xb_t = lane_base;
 #pragma unroll
             for (int cb = 0; cb < 4; ++cb) {
-                const unsigned char* xb = xs + cb * XBLK + r * 128;
+                const unsigned char* xb = S.x + cb * XBLK + r * 128;
 #pragma unroll
                 for (int q4 = 0; q4 < 8; ++q4) {
                     float4 xv = *reinterpret_cast<const float4*>(xb + ((q4 ^ (r & 7)) << 4));
@@ -423,20 +414,16 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     split2(xv.x, xv.y, hi[q4 * 2], lo[q4 * 2]);
                     split2(xv.z, xv.w, hi[q4 * 2 + 1], lo[q4 * 2 + 1]);
                 }
-                tmem_st16(lane_base + C_X + cb * 16, hi);
-                tmem_st16(lane_base + C_XLO + cb * 16, lo);
+                tmem_st16(xb_t + C_X + cb * 16, hi);
+                tmem_st16(xb_t + C_XLO + cb * 16, lo);
             }
             tmem_st_wait();
             tc_fence_before();
             mbar_arrive(&S.bar_xt);
-            mbar_arrive(&S.bar_xfree[ut & 1]);
+            mbar_arrive(&S.bar_xfree);
         };
-        const bool tk_on = TIMING && blockIdx.x == 0 && lane == 0 && wq == 0;
-        long long tk[TK_N] = {};
-        long long tk_t = TIMING ? clock64() : 0;
-        auto relu_split = [&](uint32_t col, uint64_t* bar_in, uint64_t* bar_out, uint32_t ph, int wait_slot) {
+        auto relu_split = [&](uint32_t col, uint64_t* bar_in, uint64_t* bar_out, uint32_t ph) {
             mbar_wait(bar_in, ph);
-            FT(wait_slot);
             tc_fence_after();
             tmem_ld32(lane_base + col, v);
 #pragma unroll
@@ -447,88 +434,112 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             tc_fence_before();
             mbar_arrive(bar_out);
         };
-        int n_pairs = 0;
-        { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; next_pair(t); } }
-        if (warp < E1B_WARP0) {
-            // the X columns of TMEM are single buffered: the next unit's tile is parked right after epilogue 1a of this
-            // unit's last pair (whose MMA1, the last reader, has retired by then)
-            PairCursor c = first_pair();
-            park_x(0);
-            FT(TK_A_PARK);
-            for (int q = 0; q < n_pairs; ++q) {
-                const int rb = q & (NB - 1);
-                relu_split(C_D1 + 32 * rb, &S.bar_d1[rb], &S.bar_h1[rb], (uint32_t)((q / NB) & 1), TK_A_E1WAIT);
-                FT(TK_A_E1);
-                PairCursor cn = c;
-                next_pair(cn);
-                if (cn.ok && cn.ord != c.ord) { park_x(cn.ord); FT(TK_A_PARK); }
-                c = cn;
+        auto e1 = [&](int q) { const int rb = q & (NB - 1); relu_split(C_D1 + 32 * rb, &S.bar_d1[rb], &S.bar_h1[rb], (uint32_t)((q / NB) & 1)); };
+        auto e1b = [&](int q) { const int rb = q & (NB - 1); relu_split(C_D1B + 32 * rb, &S.bar_d1b[rb], &S.bar_h2[rb], (uint32_t)((q / NB) & 1)); };
+        int n_pairs = 0, n_units_ne = 0;
+        { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; n_units_ne = t.ord + 1; next_pair(t); } }
+        // Three kinds of work, each taken in order as soon as its input is there (warp-uniform non-blocking tests):
+        //   e1(qe1)    when MMA1(qe1) has retired,   e1b(qe1b)  when MMA1b(qe1b) has retired,
+        //   park(unit) when the unit's fp32 tile has landed in the staging buffer AND the X columns of TMEM are free:
+        //              their last reader was MMA1 of the last pair of unit - 1, whose retirement this warp has seen once
+        //              the next e1 pair belongs to this unit (or there is none left).
+        // A fixed order would deadlock on units shorter than three pairs (the next tile only lands after the
+        // squared-error warps entered the current unit, which needs e1b of its first pair).
+        PairCursor ce1 = first_pair();                // pair e1 handles next
+        int qe1 = 0, qe1b = 0, parked = 0;
+        auto uniform = [&](bool ok) -> bool { return __all_sync(0xffffffffu, ok) != 0; };
+        const bool tk_on = TIMING && blockIdx.x == 0 && tid == 0;
+        long long tk[TK_N] = {};
+        long long tk_t = TIMING ? clock64() : 0;
+        while (qe1b < n_pairs) {
+            bool did = false;
+            FT(TK_A_IDLE);
+            if (parked < n_units_ne && (qe1 >= n_pairs || ce1.ord >= parked) &&
+                uniform(mbar_test(&S.bar_x, (uint32_t)(parked & 1)))) {
+                park_x(parked);
+                ++parked;
+                did = true;
+                FT(TK_A_PARK);
             }
-            if (tk_on) { dbg[TK_A_PARK] = (unsigned long long)tk[TK_A_PARK]; dbg[TK_A_E1] = (unsigned long long)tk[TK_A_E1]; dbg[TK_A_E1WAIT] = (unsigned long long)tk[TK_A_E1WAIT]; }
-        } else {
-            for (int q = 0; q < n_pairs; ++q) {
-                const int rb = q & (NB - 1);
-                relu_split(C_D1B + 32 * rb, &S.bar_d1b[rb], &S.bar_h2[rb], (uint32_t)((q / NB) & 1), TK_A_E1BWAIT);
+            if (qe1 < n_pairs && uniform(mbar_test(&S.bar_d1[qe1 & (NB - 1)], (uint32_t)((qe1 / NB) & 1)))) {
+                e1(qe1);
+                next_pair(ce1);
+                ++qe1;
+                did = true;
+                FT(TK_A_E1);
+            }
+            if (qe1b < qe1 && uniform(mbar_test(&S.bar_d1b[qe1b & (NB - 1)], (uint32_t)((qe1b / NB) & 1)))) {
+                e1b(qe1b);
+                ++qe1b;
+                did = true;
                 FT(TK_A_E1B);
             }
-            if (tk_on) { dbg[TK_A_E1B] = (unsigned long long)tk[TK_A_E1B]; dbg[TK_A_E1BWAIT] = (unsigned long long)tk[TK_A_E1BWAIT]; }
+            if (!did) __nanosleep(20);
         }
+        if (tk_on) for (int i = TK_A_PARK; i <= TK_A_IDLE; ++i) dbg[i] = (unsigned long long)tk[i];
     } else {
-        // ---- group B: epilogue 2 (squared error), partial sums.  Eight warps: warps 8-11 take output columns 0..63 of
-        //      their lane quarter, warps 12-15 columns 64..127.  The row of x comes from the unit's fp32 tile in shared
-        //      memory (swizzle-aware LDS.128, conflict free), which stays in place for the whole unit ----
-        const int wq = warp & 3, half = (warp - B_WARP0) >> 2;
+        // ---- group B: epilogue 2 (squared error against the row kept in registers), partial sums.  Eight warps: warps
+        //      4-7 take output columns 0..63 of their lane quarter, warps 8-11 columns 64..127, so a pair costs each
+        //      thread two 32-column loads and 32 packed subtract / multiply-adds ----
+        const int wq = warp & 3, half = (warp - 4) >> 2;
         const int r = wq * 32 + lane;
         const uint32_t lane_base = tmem + ((uint32_t)(wq * 32) << 16);
-        uint32_t v0[32], v1[32];
+        uint32_t v[32];
+        float2 nx[32];                              // -x of this thread's half row (64 floats), for the whole unit
         PairCursor c = first_pair();
-        int g = 0;
+        int g = 0, ut = 0;
         bool fresh = true;
-        // per-thread running sums: lanes[cta][model][256] -- every slot has exactly one writer, in program order, so the
-        // fire-and-forget reductions below are deterministic and cost no shuffle, no wait and no address arithmetic
-        float* my_lane = partial + ((size_t)blockIdx.x * n_models) * 256 + (warp - B_WARP0) * 32 + lane;
-        const bool tk_on = TIMING && blockIdx.x == 0 && tid == B_WARP0 * 32;
+        const bool tk_on = TIMING && blockIdx.x == 0 && tid == 128;
         long long tk[TK_N] = {};
         long long tk_t = TIMING ? clock64() : 0;
         while (c.ok) {
             FT(TK_B_REST);
-            const int ub = c.ord & 1;
-            if (fresh) { mbar_wait(&S.bar_x[ub], (uint32_t)((c.ord >> 1) & 1)); fresh = false; FT(TK_B_ENTRY); }
-            const unsigned char* xrow = S.x[ub] + r * 128;
+            if (fresh) {
+                mbar_wait(&S.bar_x, (uint32_t)(ut & 1));
+#pragma unroll
+                for (int q = 0; q < 16; ++q) {
+                    const int qq = half * 16 + q;     // float4 index inside the 128-float row
+                    const float4 xv = *reinterpret_cast<const float4*>(S.x + (qq >> 3) * XBLK + r * 128 + (((qq & 7) ^ (r & 7)) << 4));
+                    // columns 115..127 of D2 are exact zeros (no such rows in W4): their x is padding
+                    nx[q * 2] = make_float2(qq * 4 < D ? -xv.x : 0.f, qq * 4 + 1 < D ? -xv.y : 0.f);
+                    nx[q * 2 + 1] = make_float2(qq * 4 + 2 < D ? -xv.z : 0.f, qq * 4 + 3 < D ? -xv.w : 0.f);
+                }
+                mbar_arrive(&S.bar_xfree);
+                fresh = false;
+                FT(TK_B_ENTRY);
+            }
             const int b = g & 1;
             mbar_wait(&S.bar_d2[b], (uint32_t)((g >> 1) & 1));
             tc_fence_after();
             FT(TK_B_WAIT);
             float2 acc[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
-            auto acc_block = [&](const uint32_t (&v)[32], int cb) {     // 32 columns: four independent chains, x from shared memory
+            auto acc_block = [&](int cb) {            // four independent chains: the FMAs pipeline
 #pragma unroll
-                for (int j4 = 0; j4 < 8; ++j4) {
-                    const int qq = half * 16 + cb * 8 + j4;          // float4 index inside the 128-float row (pad columns are 0)
-                    const float4 xv = *reinterpret_cast<const float4*>(xrow + (qq >> 3) * XBLK + (((qq & 7) ^ (r & 7)) << 4));
-                    const float2 e0 = fadd2(make_float2(__uint_as_float(v[4 * j4]), __uint_as_float(v[4 * j4 + 1])), make_float2(-xv.x, -xv.y));
-                    const float2 e1 = fadd2(make_float2(__uint_as_float(v[4 * j4 + 2]), __uint_as_float(v[4 * j4 + 3])), make_float2(-xv.z, -xv.w));
-                    acc[(2 * j4) & 3] = ffma2(e0, e0, acc[(2 * j4) & 3]);
-                    acc[(2 * j4 + 1) & 3] = ffma2(e1, e1, acc[(2 * j4 + 1) & 3]);
+                for (int j = 0; j < 16; ++j) {
+                    const float2 e = fadd2(make_float2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])), nx[cb * 16 + j]);
+                    acc[j & 3] = ffma2(e, e, acc[j & 3]);
                 }
             };
-            tmem_ld64(lane_base + C_D2 + 128 * b + 64 * half, v0, v1);      // both halves of this thread's share, one wait
+            const uint32_t d2 = lane_base + C_D2 + 128 * b + 64 * half;
+            tmem_ld32(d2, v);
+            acc_block(0);
+            tmem_ld32(d2 + 32, v);
             tc_fence_before();
-            mbar_arrive(&S.bar_d2free[b]);            // D2[b] is in registers: MMA2 of pair g + 2 may overwrite it
+            mbar_arrive(&S.bar_d2free[b]);            // this thread's share of D2[b] is in registers
             FT(TK_B_HOLD);
-            acc_block(v0, 0);
-            acc_block(v1, 1);
+            acc_block(1);
             const int row = c.tile * TROWS + r;
-            const float sse = row < x_rows ? ((acc[0].x + acc[0].y) + (acc[1].x + acc[1].y)) + ((acc[2].x + acc[2].y) + (acc[3].x + acc[3].y)) : 0.f;
-            atomicAdd(my_lane + (size_t)c.m * 256, sse);              // result unused: a RED, nobody else writes this slot
+            float sse = row < x_rows ? ((acc[0].x + acc[0].y) + (acc[1].x + acc[1].y)) + ((acc[2].x + acc[2].y) + (acc[3].x + acc[3].y)) : 0.f;
+            sse = warp_sum(sse);
+            if (lane == 0) partial[((size_t)c.m * n_tiles + c.tile) * 8 + half * 4 + wq] = sse;
             PairCursor cn = c;
             next_pair(cn);
-            if (!cn.ok || cn.ord != c.ord) { mbar_arrive(&S.bar_xfree[ub]); fresh = true; }   // done with this unit's tile
+            if (!cn.ok || cn.i != c.i) { ++ut; fresh = true; }
             c = cn;
             ++g;
         }
         if (tk_on) for (int i = TK_B_WAIT; i <= TK_B_ENTRY; ++i) dbg[i] = (unsigned long long)tk[i];
     }
-    __threadfence();                         // this thread's running sums are visible device-wide before the grid barrier
     tc_fence_before();
     __syncthreads();
     if (warp == MMA1_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(F_TMEM_COLS));
@@ -550,9 +561,9 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
     }
     __syncthreads();
     for (int m = blockIdx.x; m < n_models; m += gridDim.x) {
+        const float* pm = partial + (size_t)m * n_tiles * 8;
         double s = 0.0;
-        for (int i = tid; i < (int)gridDim.x * 256; i += NT_F)       // fixed order: thread-strided, then warps in order
-            s += (double)__ldcg(partial + ((size_t)(i >> 8) * n_models + m) * 256 + (i & 255));
+        for (int i = tid; i < n_tiles * 8; i += NT_F) s += (double)__ldcg(pm + i);
         s = warp_sum(s);
         if (lane == 0) S.red[warp] = s;
         __syncthreads();
@@ -595,8 +606,7 @@ int encode_x_map_f(CUtensorMap* map, const float* base, int64_t rows) {
 
 extern "C" int64_t fm_score_fused_scratch_floats(int64_t x_rows, int32_t n_models) {
     const int64_t n_tiles = (x_rows + fm::tc::TROWS - 1) / fm::tc::TROWS;
-    (void)n_tiles;                                   // per-thread running sums: [CTAs <= 160][models][256]
-    return 160 * 256 * (int64_t)(n_models > 0 ? n_models : 1);
+    return n_tiles * 8 * (int64_t)(n_models > 0 ? n_models : 1);
 }
 
 extern "C" int fm_score_fused_f16(const FmFusedScoreArgs* a, void* stream) {

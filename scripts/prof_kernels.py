@@ -81,7 +81,7 @@ for it in range(a.iters):
                  "B:wait D2", "B:hold D2", "B:rest", "B:unit entry", "total", "A:e1 wait", "A:e1b wait"]
         tot = cyc[20] or 1
         print("  fused f16 kernel, CTA 0 (k cycles, % of the MMA1 thread's loop): " +
-              ", ".join(f"{n} {c / 1e3:.0f}k ({100 * c / tot:.0f}%)" for n, c in zip(names, cyc[:23])))
+              ", ".join(f"{n} {c / 1e3:.0f}k ({100 * c / tot:.0f}%)" for n, c in zip(names, cyc[:23]) if c))
     elif a.phase_cycles and a.what == "score" and be.tc:
         names = ["issue MMA1(g+1)", "wait MMA2(g-1)", "wait epi1(g)", "wait w4 image", "wait D2 free", "issue MMA2(g)",
                  "wait X in TMEM", "wait X staging free",
