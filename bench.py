@@ -155,48 +155,89 @@ def bench_loop(eng, pin_train, pin_valid, n_rounds, r0=0):
     return out
 
 
+def _compare_runs(multi, single, strict_from=0):
+    """Differences between two lists of RoundResult.  Rounds >= ``strict_from`` are not required to agree on the discrete
+    outcomes (see run_check); returns (mismatch messages, max |AUC diff| over the strict rounds, max |mean-AUC diff|)."""
+    bad, worst, worst_mean = [], 0.0, 0.0
+    for r, (a, b) in enumerate(zip(multi, single)):
+        ma, mb = sum(a.client_metrics) / len(a.client_metrics), sum(b.client_metrics) / len(b.client_metrics)
+        worst_mean = max(worst_mean, abs(ma - mb))
+        if not abs(ma - mb) < 5e-3: bad.append(f"round {r}: mean AUC {ma:.5f} vs {mb:.5f}")
+        if a.selected != b.selected: bad.append(f"round {r}: selection differs ({a.selected[:4]} vs {b.selected[:4]})")
+        if r >= strict_from:
+            continue
+        if a.aggregator != b.aggregator: bad.append(f"round {r}: aggregator {a.aggregator} vs {b.aggregator}")
+        if a.epochs_run != b.epochs_run:
+            df = [(g, a.epochs_run.get(g), b.epochs_run.get(g)) for g in sorted(set(a.epochs_run) | set(b.epochs_run))
+                  if a.epochs_run.get(g) != b.epochs_run.get(g)]
+            bad.append(f"round {r}: epochs run differ for {len(df)} clients, e.g. {df[:3]}")
+        if [v["is_verified"] for v in a.verification] != [v["is_verified"] for v in b.verification]:
+            bad.append(f"round {r}: verification verdicts differ")
+        d = max(abs(x - y) for x, y in zip(a.client_metrics, b.client_metrics))
+        worst = max(worst, d)
+        if not d < 1e-6: bad.append(f"round {r}: max |AUC difference| {d:.3e}")
+    return bad, worst, worst_mean
+
+
 def run_check(args, comm, n_global, first, cnt):
     """--check: the SAME global scenario (clients_per_gpu x N clients) for ``--check-rounds`` rounds through the
-    bench's pipelined loop (staged uploads included), once on the N ranks and once on rank 0's GPU alone; the two runs
-    must agree on aggregator ids, epochs run, verification verdicts and every client's AUC (1e-6).  Prints one JSON
-    line; exit status 1 on a mismatch.  This anchors the multi-GPU path at the benchmark's scale."""
+    bench's pipelined loop (staged uploads included) on the N ranks and on rank 0's GPU alone.  Prints one JSON line;
+    exit status 1 on a mismatch.  This anchors the multi-GPU path at the benchmark's scale.
+
+    Two multi-GPU arms.  (1) STRICT, with the merge pulling rows over NVLink (``FEDMSE_NVLS=0``): every rank adds the
+    selected models in selection order, exactly like one GPU, so aggregator ids, epochs run, verification verdicts and
+    every client's AUC (1e-6) must agree in every round.  (2) The default merge through the NVSwitch adds per-rank
+    partial sums, i.e. the merged model differs from the one-GPU sum in the last bits.  All clients restart from that same
+    model and their validation curves flatten at the same epoch, so from the second round on such a perturbation moves
+    many patience-1 early stops by one epoch (seen at 250 clients: 72 clients stop one epoch earlier) and the runs then
+    follow different, equally valid trajectories; this arm is therefore held to exact agreement in round 0 (where
+    nothing has been merged yet) and to the 0.005 AUC parity bound on the per-round mean afterwards.  Gossip has no
+    cross-rank sum (each client's merge is one CTA's arithmetic), so it is checked strictly in one arm."""
     import torch
     from fedmse_decentralized_b200.parallel import Comm
     R = args.check_rounds
-    eng, sh, pt, pv = build_engine(args, comm, n_global, first, cnt)
-    seed_all(args.seed + 17)     # the round loop's host RNG (selection, tie-break jitter) starts from the same state in both arms
-    multi = bench_loop(eng, pt, pv, R)
-    if comm.device.type == "cuda":
-        torch.cuda.synchronize(comm.device)
-    eng.close()
-    comm.barrier()
+    sync = (lambda: torch.cuda.synchronize(comm.device)) if comm.device.type == "cuda" else (lambda: None)
+
+    def run(c, f, n, nvls):
+        old = os.environ.get("FEDMSE_NVLS")
+        os.environ["FEDMSE_NVLS"] = "1" if nvls else "0"
+        try:
+            eng, _, pt, pv = build_engine(args, c, n_global, f, n)
+            seed_all(args.seed + 17)     # the round loop's host RNG starts from the same state in every arm
+            out = bench_loop(eng, pt, pv, R)
+            sync()
+            path = "nvls" if getattr(eng.backend, "nvls", None) is not None else "p2p"
+            eng.close()
+        finally:
+            if old is None:
+                os.environ.pop("FEDMSE_NVLS", None)
+            else:
+                os.environ["FEDMSE_NVLS"] = old
+        return out, path
+
+    arms = [("p2p", False)] if (args.aggregation == "gossip" or comm.world == 1) else [("p2p", False), ("nvls", True)]
+    multi = {}
+    for name, nvls in arms:
+        multi[name] = run(comm, first, cnt, nvls)
+        comm.barrier()
     verdict = None
     if comm.rank == 0:
-        solo = Comm(rank=0, world=1, device=comm.device)
-        eng1, sh1, pt1, pv1 = build_engine(args, solo, n_global, 0, n_global)
-        seed_all(args.seed + 17)
-        single = bench_loop(eng1, pt1, pv1, R)
-        if comm.device.type == "cuda":
-            torch.cuda.synchronize(comm.device)
-        bad = []
-        worst = 0.0
-        for r, (a, b) in enumerate(zip(multi, single)):
-            if a.selected != b.selected: bad.append(f"round {r}: selection differs ({a.selected[:4]} vs {b.selected[:4]})")
-            if a.aggregator != b.aggregator: bad.append(f"round {r}: aggregator {a.aggregator} vs {b.aggregator}")
-            if a.epochs_run != b.epochs_run:
-                df = [(g, a.epochs_run.get(g), b.epochs_run.get(g)) for g in sorted(set(a.epochs_run) | set(b.epochs_run))
-                      if a.epochs_run.get(g) != b.epochs_run.get(g)]
-                bad.append(f"round {r}: epochs run differ for {len(df)} clients, e.g. {df[:3]}")
-            if [v["is_verified"] for v in a.verification] != [v["is_verified"] for v in b.verification]:
-                bad.append(f"round {r}: verification verdicts differ")
-            d = max(abs(x - y) for x, y in zip(a.client_metrics, b.client_metrics))
-            worst = max(worst, d)
-            if not d < 1e-6: bad.append(f"round {r}: max |AUC difference| {d:.3e}")
-        verdict = {"check": "pass" if not bad else "FAIL", "n_gpus": comm.world, "clients": n_global, "rounds": R,
-                   "aggregation": args.aggregation, "score_precision": args.score_precision,
-                   "max_abs_auc_diff": worst, "aggregators": [a.aggregator for a in multi],
-                   "auc_mean_per_round": [sum(a.client_metrics) / len(a.client_metrics) for a in multi],
-                   "auc_min_per_round": [min(a.client_metrics) for a in multi], "mismatches": bad[:10]}
+        single, _ = run(Comm(rank=0, world=1, device=comm.device), 0, n_global, False)
+        verdict = {"check": "pass", "n_gpus": comm.world, "clients": n_global, "rounds": R, "aggregation": args.aggregation,
+                   "score_precision": args.score_precision, "arms": {}}
+        for name, _ in arms:
+            res, path = multi[name]
+            lenient = name == "nvls" and path == "nvls"
+            bad, worst, worst_mean = _compare_runs(res, single, strict_from=1 if lenient else R)
+            verdict["arms"][name] = {"merge_path": path, "strict_rounds": 1 if lenient else R, "max_abs_auc_diff_strict_rounds": worst,
+                                     "max_abs_mean_auc_diff": worst_mean, "mismatches": bad[:10],
+                                     "aggregators": [a.aggregator for a in res]}
+            if bad:
+                verdict["check"] = "FAIL"
+        ref = multi[arms[-1][0]][0]
+        verdict["auc_mean_per_round"] = [sum(a.client_metrics) / len(a.client_metrics) for a in ref]
+        verdict["auc_min_per_round"] = [min(a.client_metrics) for a in ref]
+        verdict["rejected_clients_per_round"] = [sum(1 for v in a.verification if not v["is_verified"]) for a in ref]
         print(json.dumps(verdict))
     comm.barrier()
     if verdict is not None and verdict["check"] != "pass":
