@@ -41,11 +41,14 @@ def allocate(comm: Comm, n_floats: int) -> Optional[NvlsBuffer]:
         import torch.distributed._symmetric_memory as symm_mem
         group = comm.group if comm.group is not None else dist.group.WORLD
         enable = getattr(symm_mem, "enable_symm_mem_for_group", None)
-        if enable is not None:
-            try:
-                enable(group.group_name)
-            except Exception:                       # newer torch: not needed / deprecated
-                pass
+        if enable is not None:                      # needed by older torch builds, a deprecated no-op in newer ones
+            import warnings
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                try:
+                    enable(group.group_name)
+                except Exception:
+                    pass
         t = symm_mem.empty(n_floats, dtype=torch.float32, device=comm.device)
         t.zero_()
         hdl = symm_mem.rendezvous(t, group)

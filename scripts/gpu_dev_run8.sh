@@ -14,9 +14,7 @@ PY
 }
 timeout 400 $TR bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/s_elected_n$N.json 2> gpurun_out/s_elected_n$N.err; show gpurun_out/s_elected_n$N.json; tail -2 gpurun_out/s_elected_n$N.err
 timeout 400 $TR bench.py --gpus $N --steps 20 --warmup 5 --aggregation gossip > gpurun_out/s_gossip_n$N.json 2> gpurun_out/s_gossip_n$N.err; show gpurun_out/s_gossip_n$N.json; tail -2 gpurun_out/s_gossip_n$N.err
-FEDMSE_NVLS=0 timeout 400 $TR bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/s_elected_p2p_n$N.json 2> gpurun_out/s_elected_p2p_n$N.err; show gpurun_out/s_elected_p2p_n$N.json
 timeout 600 $TR bench.py --gpus $N --check > gpurun_out/s_check_elected_n$N.json 2> gpurun_out/s_check_elected_n$N.err; cat gpurun_out/s_check_elected_n$N.json; tail -2 gpurun_out/s_check_elected_n$N.err
-timeout 600 $TR bench.py --gpus $N --check --aggregation gossip > gpurun_out/s_check_gossip_n$N.json 2> gpurun_out/s_check_gossip_n$N.err; cat gpurun_out/s_check_gossip_n$N.json; tail -2 gpurun_out/s_check_gossip_n$N.err
-timeout 400 $TR scripts/bench_bandwidth_sweep.py --sizes-mb 1 16 128 512 > gpurun_out/s_sweep_n$N.jsonl 2> gpurun_out/s_sweep_n$N.err; cat gpurun_out/s_sweep_n$N.jsonl; tail -2 gpurun_out/s_sweep_n$N.err
+timeout 400 $TR scripts/bench_bandwidth_sweep.py --sizes-mb 1 64 512 > gpurun_out/s_sweep_n$N.jsonl 2> gpurun_out/s_sweep_n$N.err; cat gpurun_out/s_sweep_n$N.jsonl; tail -2 gpurun_out/s_sweep_n$N.err
 timeout 300 $TR scripts/run_configs.py 3 > gpurun_out/s_config3_n$N.jsonl 2> gpurun_out/s_config3_n$N.err; cat gpurun_out/s_config3_n$N.jsonl; tail -2 gpurun_out/s_config3_n$N.err
 timeout 300 $TR scripts/run_configs.py 2 --data_root data_cache/N-BaIoT/IID-10-Client_Data > gpurun_out/s_config2_n$N.jsonl 2> gpurun_out/s_config2_n$N.err; cat gpurun_out/s_config2_n$N.jsonl; tail -2 gpurun_out/s_config2_n$N.err
