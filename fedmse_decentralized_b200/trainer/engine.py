@@ -245,10 +245,20 @@ class FederationEngine:
                 scores = be.vote_scores(st, sh, ctl, self.spec)
                 if not getattr(be, "exchanges_scores", False):     # CUDA multi-GPU exchanges in-kernel (P2P boards)
                     scores = cm.sum_(scores)
+            # The election waits for every rank's vote scores, i.e. for the slowest rank's local training.  The
+            # merge weights do not depend on who is elected, so their scoring (the heavy part of the merge) is
+            # enqueued first and the cross-rank wait hides under it.
+            early_scores = getattr(be, "exchanges_scores", False) and self.update_type == "mse_avg"
+            mse = None
+            if early_scores:
+                with tm.phase("merge"):
+                    mse = be.merge_scores(st, sh, ctl)
+            with tm.phase("elect"):
                 agg_pos = be.elect(st, scores, ctl, self.spec)
             with tm.phase("merge"):
-                mse = None
-                if self.update_type == "mse_avg":
+                if early_scores:
+                    pass
+                elif self.update_type == "mse_avg":
                     mse = be.merge_scores(st, sh, ctl)
                     if not getattr(be, "exchanges_scores", False):
                         mse = cm.sum_(mse)
