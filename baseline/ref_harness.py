@@ -37,6 +37,16 @@ REF_SRC = os.environ.get("FEDMSE_REFERENCE_SRC", "/root/reference")
 _REF_PKGS = ("Model", "Trainer", "Evaluator", "DataLoader", "Utils")
 
 
+def client_seed(seed0: int, i: int) -> int:
+    """numpy seed the harness sets before client ``i``'s shuffles (same on every rank)."""
+    return (int(seed0) * 1000003 + i) % (2 ** 32)
+
+
+def dev_seed(seed0: int) -> int:
+    """numpy seed the harness sets before the dev-set sampling."""
+    return (int(seed0) * 1000003 + 999983) % (2 ** 32)
+
+
 def _installed() -> bool:
     return all(os.path.isfile(os.path.join(REF_DIR, p, "__init__.py")) for p in _REF_PKGS)
 
@@ -128,7 +138,7 @@ class ReferenceFederation:
             # that the shuffles of a client are the same on every rank (ranks only shuffle the abnormal rows of the
             # clients they own, which would otherwise shift the stream of all later clients and give every rank a
             # different replica of the validation / dev data)
-            np.random.seed((seed0 * 1000003 + i) % (2 ** 32))
+            np.random.seed(client_seed(seed0, i))
             normal = pd.DataFrame(cl.normal).sample(frac=1).reset_index(drop=True)
             n = len(normal)
             n_tr, n_va, n_dv = int(0.4 * n), int(0.1 * n), int(0.4 * n)
@@ -152,7 +162,7 @@ class ReferenceFederation:
                 info["valid_loader"] = DataLoader(RDL.IoTDataset(p_va, l_va), batch_size=bs, pin_memory=True)
                 info["test_loader"] = DataLoader(test_ds, batch_size=bs, pin_memory=True)
             self.client_info.append(info)
-        np.random.seed((seed0 * 1000003 + 999983) % (2 ** 32))
+        np.random.seed(dev_seed(seed0))
         min_len = min(len(c["dev_normal_dataset"]) for c in self.client_info)     # src/main.py:214-223
         dev = pd.concat([c["dev_normal_dataset"].sample(n=min_len) for c in self.client_info], axis=0)
         processed_dev, _ = RDL.IoTDataProccessor(scaler="standard").fit_transform(dev)

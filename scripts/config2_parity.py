@@ -52,8 +52,8 @@ def main():
            "rounds": a.rounds, "epochs": a.epochs, "lr": a.lr, "shrink_lambda": a.shrink_lambda, "update": a.update,
            "device": str(dev), "score_precision": a.score_precision}
     ref_metrics = None
+    import ref_harness
     if not a.skip_reference:
-        import ref_harness
         why = ref_harness.available()
         if why:
             out["reference"] = why
@@ -74,11 +74,11 @@ def main():
     # ours: the same shuffles as the harness (per-client re-seeded numpy generator behind DataFrame.sample)
     pcs = []
     for i, cl in enumerate(raw):
-        np.random.seed((1234 * 1000003 + i) % (2 ** 32))
+        np.random.seed(ref_harness.client_seed(1234, i))
         normal = pd.DataFrame(cl.normal).sample(frac=1).reset_index(drop=True).to_numpy()
         abnormal = pd.DataFrame(cl.abnormal).sample(frac=1).reset_index(drop=True).to_numpy()
         pcs.append(prepare_client(cl.name, normal, abnormal, cl.test_normal, True))
-    np.random.seed((1234 * 1000003 + 999983) % (2 ** 32))
+    np.random.seed(ref_harness.dev_seed(1234))
     devset = pool_dev_set(pcs, sampler=lambda x, k: pd.DataFrame(x).sample(n=k).to_numpy())
     random.seed(1234); torch.manual_seed(0)
     cfg = ExperimentConfig(epoch=a.epochs, num_rounds=a.rounds, lr_rate=a.lr, shrink_lambda=a.shrink_lambda,

@@ -199,19 +199,15 @@ def test_full_experiment_matches_reference_round_loop(reference_modules, tmp_pat
     ref_metrics = [fed.run_round(r) for r in range(3)]
     fed.close()
     # --- ours, same RNG consumption order ---
-    random.seed(1234); np.random.seed(1234); torch.manual_seed(0)
-    prepared = []
-    for cl in raw:
-        normal = pd.DataFrame(cl.normal).sample(frac=1).reset_index(drop=True).to_numpy()
-        abnormal = pd.DataFrame(cl.abnormal).sample(frac=1).reset_index(drop=True).to_numpy()
-        prepared.append((normal, abnormal, cl))
-    # the harness shuffles abnormal right after normal per client; replay in the same order
+    # the harness re-seeds numpy per client (rank-independent shuffles) and shuffles abnormal right after normal
     random.seed(1234); np.random.seed(1234); torch.manual_seed(0)
     pcs = []
-    for cl in raw:
+    for i, cl in enumerate(raw):
+        np.random.seed(ref_harness.client_seed(1234, i))
         normal = pd.DataFrame(cl.normal).sample(frac=1).reset_index(drop=True).to_numpy()
         abnormal = pd.DataFrame(cl.abnormal).sample(frac=1).reset_index(drop=True).to_numpy()
         pcs.append(prepare_client(cl.name, normal, abnormal, cl.test_normal, True))
+    np.random.seed(ref_harness.dev_seed(1234))
     dev = pool_dev_set(pcs, sampler=lambda a, n: pd.DataFrame(a).sample(n=n).to_numpy())
     sh = ShardStore.build(pcs, dev)
     from fedmse_decentralized_b200 import ExperimentConfig
@@ -258,10 +254,12 @@ def test_real_nbaiot_scenario_auc_parity(reference_modules, tmp_path, update_typ
     fed.close()
     random.seed(1234); np.random.seed(1234); torch.manual_seed(0)
     pcs = []
-    for cl in raw:
+    for i, cl in enumerate(raw):
+        np.random.seed(ref_harness.client_seed(1234, i))
         normal = pd.DataFrame(cl.normal).sample(frac=1).reset_index(drop=True).to_numpy()
         abnormal = pd.DataFrame(cl.abnormal).sample(frac=1).reset_index(drop=True).to_numpy()
         pcs.append(prepare_client(cl.name, normal, abnormal, cl.test_normal, True))
+    np.random.seed(ref_harness.dev_seed(1234))
     dev = pool_dev_set(pcs, sampler=lambda a, n: pd.DataFrame(a).sample(n=n).to_numpy())
     cfg = ExperimentConfig(epoch=2, num_rounds=2, network_size=6, backend="oracle", output_root=str(tmp_path),
                            reference_compat=True, write_latents=False, save_client_models=False)
