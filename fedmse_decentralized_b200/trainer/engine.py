@@ -251,7 +251,7 @@ class FederationEngine:
             early_scores = getattr(be, "exchanges_scores", False) and self.update_type == "mse_avg"
             mse = None
             if early_scores:
-                with tm.phase("merge"):
+                with tm.phase("score"):
                     mse = be.merge_scores(st, sh, ctl)
             with tm.phase("elect"):
                 agg_pos = be.elect(st, scores, ctl, self.spec)
