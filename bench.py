@@ -357,6 +357,9 @@ def run_ours(args):
             "wall_ms_per_step": wall * 1e3 / args.steps,
             "phases_ms": phases,
             "auc_mean_last_round": sum(res_e.client_metrics) / len(res_e.client_metrics),
+            "auc_note": "the hybrid model's mean AUC falls with the client count on one GPU and on N alike (bench.py --check): "
+                        "averaging many independently initialised SAEs shrinks the weights until the shrink loss collapses the "
+                        "latents; the reference arm shows the same trend (profiles/r2/gossip_dynamics_1000clients.txt)",
             "setup_s": round(setup_s, 1),
         }
         print(json.dumps(out))
