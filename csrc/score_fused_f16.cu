@@ -7,10 +7,13 @@
 // GPUs; score_multi_tc.cu (3xTF32) spent 1.6 k tensor cycles and 1.6 k CUDA-core cycles per (128-row tile, model).
 //
 // What changed against score_multi_tc.cu:
-//  * fp16 hi/lo instead of 3xTF32.  Every operand is split as v = hi + lo with hi = fp16(v), lo = fp16(v - hi)
-//    (22 mantissa bits together, |v| clamped to the fp16 range first) and every GEMM is the three products
-//    hi*hi + hi*lo + lo*hi with fp32 accumulation in TMEM: kind::f16 runs at twice the TF32 rate and K = 16 per
-//    instruction, so a pair costs 24 + 6 + 6 MMAs (~0.86 k tensor cycles) instead of 45 + 12 (~1.5 k).
+//  * fp16 operands instead of 3xTF32, fp32 accumulation in TMEM (kind::f16: twice the TF32 rate, K = 16 per
+//    instruction).  Weights and the input tile are split as v = hi + lo with hi = fp16(v), lo = fp16(v - hi) (22 mantissa
+//    bits together, |v| saturated at the fp16 range first); GEMM 1 is the three products hi*hi + hi*lo + lo*hi.  The
+//    hidden activations h1 / h2 travel as ONE fp16: their rounding error (2^-11, unbiased, different in every row)
+//    averages out over the 10^5..10^6 rows of an MSE, whereas a rounding of the weights would be the same in every row.
+//    GEMMs 1b / 2 are therefore two products (h * W_hi + h * W_lo): 24 + 4 + 4 MMAs (~0.74 k tensor cycles) per pair
+//    instead of 45 + 12 (~1.5 k), and the epilogues between the GEMMs are one convert per pair of values.
 //  * The 27 -> 7 -> 27 bottleneck left the CUDA cores.  There is no activation between the two inner layers, so
 //    h2 = relu(W3 (W2 h1 + b2) + b3) = relu(W32 h1 + b32) with W32 = W3 W2 (27 x 27, rank 7) and b32 = W3 b2 + b3,
 //    formed once per model by the prep kernel: ONE extra small GEMM (M128 N32 K32) between the two big ones.
@@ -21,8 +24,9 @@
 //    the loop MMA2 -> squared error -> release -> next MMA2 set the pace of the kernel (ncu of the first two versions:
 //    1.7 k cycles per pair, tensor pipe 55 % active).  D1 / D1b are double buffered, the parked tile is single buffered
 //    in exchange (a unit boundary costs one parking, ~3 % at 62 models per unit).
-//  * No [models x rows] SSE matrix: each epilogue warp writes one partial sum per (model, tile); after a grid-wide
-//    barrier the CTAs reduce them in a fixed order to the per-model MSE (deterministic, replaces chunk_mean).
+//  * No [models x rows] SSE matrix: every squared-error thread adds its row's error to its own running sum per model
+//    (a fire-and-forget RED to a slot nobody else writes); after a grid-wide barrier the CTAs add those sums in a fixed
+//    order to the per-model MSE (deterministic, replaces chunk_mean).
 //
 // TMEM map (512 columns): X hi 0..63, lo 64..127 | D1/h1[r] 128+32r | D1b/h2[r] 192+32r (r = pair mod 2) | D2[b] 256+128b.
 // Warp roles: 0-3 epilogues 1a/1b + tile parking, 4-11 epilogue 2 (squared error; two warps per TMEM lane quarter, half
@@ -247,6 +251,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)), "r"(F_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
+    for (int i = tid; i < n_models * 256; i += NT_F) partial[(size_t)blockIdx.x * n_models * 256 + i] = 0.f;
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -317,14 +322,13 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     if (q >= NB) mbar_wait(&S.bar_d1bfree[r], (uint32_t)(((q - NB) >> 1) & 1));
                     FT(TK_1B_FREE);
                     tc_fence_after();
-                    const uint32_t d = tmem + C_D1B + 32 * r, ah = tmem + C_D1 + 32 * r, al = ah + 16;
+                    const uint32_t d = tmem + C_D1B + 32 * r, ah = tmem + C_D1 + 32 * r;
                     const uint64_t bw = dw32 + (uint64_t)((s * 2 * W32_BYTES) >> 4);
 #pragma unroll
                     for (int ks = 0; ks < 2; ++ks) {
                         const uint64_t bh = bw + (uint64_t)((ks * 32) >> 4), bl = bh + (uint64_t)(W32_BYTES >> 4);
                         mma_ts_f16(d, ah + ks * 8, bh, IDESC_N32, ks ? 1u : 0u);
                         mma_ts_f16(d, ah + ks * 8, bl, IDESC_N32, 1u);
-                        mma_ts_f16(d, al + ks * 8, bh, IDESC_N32, 1u);
                     }
                     tc_commit(&S.bar_d1b[r]);
                     tc_commit(&S.bar_w32free[s]);
@@ -343,14 +347,13 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     if (q >= 2) mbar_wait(&S.bar_d2free[r], (uint32_t)(((q - 2) >> 1) & 1));
                     FT(TK_2_FREE);
                     tc_fence_after();
-                    const uint32_t d = tmem + C_D2 + 128 * r, ah = tmem + C_D1B + 32 * r, al = ah + 16;
+                    const uint32_t d = tmem + C_D2 + 128 * r, ah = tmem + C_D1B + 32 * r;
                     const uint64_t bw = dw4 + (uint64_t)((s * 2 * W4_BYTES) >> 4);
 #pragma unroll
                     for (int ks = 0; ks < 2; ++ks) {
                         const uint64_t bh = bw + (uint64_t)((ks * 32) >> 4), bl = bh + (uint64_t)(W4_BYTES >> 4);
                         mma_ts_f16(d, ah + ks * 8, bh, IDESC_N128, ks ? 1u : 0u);
                         mma_ts_f16(d, ah + ks * 8, bl, IDESC_N128, 1u);
-                        mma_ts_f16(d, al + ks * 8, bh, IDESC_N128, 1u);
                     }
                     tc_commit(&S.bar_d2[r]);
                     tc_commit(&S.bar_w4free[s]);
@@ -400,7 +403,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         // ---- group A: parks tiles in TMEM, epilogues 1a (h1) and 1b (h2) of every pair ----
         const int r = warp * 32 + lane;
         const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
-        uint32_t v[32], hi[16], lo[16];
+        uint32_t v[32], hi[16], lo[16];     // lo: tile parking only
         auto park_x = [&](int ut) {                   // fp32 tile -> fp16 head + remainder, one row per thread, k = 115 := 1
             mbar_wait(&S.bar_x, (uint32_t)(ut & 1));
             const uint32_t xb_t = lane_base;
@@ -426,10 +429,12 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             mbar_wait(bar_in, ph);
             tc_fence_after();
             tmem_ld32(lane_base + col, v);
+            // activations travel as ONE fp16 (ReLU + saturation + packing in a single convert per pair of values): their
+            // rounding (2^-11, unbiased, different for every row) averages out over the 10^5..10^6 rows of an MSE, unlike a
+            // rounding of the weights, which is the same for every row -- the weights keep head + remainder
 #pragma unroll
-            for (int j = 0; j < 16; ++j) split2_relu(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]), hi[j], lo[j]);
+            for (int j = 0; j < 16; ++j) hi[j] = pack_f16x2_relu_sat(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
             tmem_st16(lane_base + col, hi);            // in place: the fp16 operand replaces the fp32 accumulator it came from
-            tmem_st16(lane_base + col + 16, lo);
             tmem_st_wait();
             tc_fence_before();
             mbar_arrive(bar_out);
@@ -486,6 +491,9 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         const uint32_t lane_base = tmem + ((uint32_t)(wq * 32) << 16);
         uint32_t v[32];
         float2 nx[32];                              // -x of this thread's half row (64 floats), for the whole unit
+        // per-thread running sums lanes[cta][model][256]: every slot has exactly one writer, in program order, so the
+        // fire-and-forget reductions below are deterministic and cost no shuffle, no wait and no address arithmetic
+        float* my_lane = partial + ((size_t)blockIdx.x * n_models) * 256 + (warp - 4) * 32 + lane;
         PairCursor c = first_pair();
         int g = 0, ut = 0;
         bool fresh = true;
@@ -529,9 +537,8 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             FT(TK_B_HOLD);
             acc_block(1);
             const int row = c.tile * TROWS + r;
-            float sse = row < x_rows ? ((acc[0].x + acc[0].y) + (acc[1].x + acc[1].y)) + ((acc[2].x + acc[2].y) + (acc[3].x + acc[3].y)) : 0.f;
-            sse = warp_sum(sse);
-            if (lane == 0) partial[((size_t)c.m * n_tiles + c.tile) * 8 + half * 4 + wq] = sse;
+            const float sse = row < x_rows ? ((acc[0].x + acc[0].y) + (acc[1].x + acc[1].y)) + ((acc[2].x + acc[2].y) + (acc[3].x + acc[3].y)) : 0.f;
+            atomicAdd(my_lane + (size_t)c.m * 256, sse);              // result unused: a RED; nobody else writes this slot
             PairCursor cn = c;
             next_pair(cn);
             if (!cn.ok || cn.i != c.i) { ++ut; fresh = true; }
@@ -540,6 +547,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         }
         if (tk_on) for (int i = TK_B_WAIT; i <= TK_B_ENTRY; ++i) dbg[i] = (unsigned long long)tk[i];
     }
+    __threadfence();                         // this thread's running sums are visible device-wide before the grid barrier
     tc_fence_before();
     __syncthreads();
     if (warp == MMA1_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(F_TMEM_COLS));
@@ -561,9 +569,9 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
     }
     __syncthreads();
     for (int m = blockIdx.x; m < n_models; m += gridDim.x) {
-        const float* pm = partial + (size_t)m * n_tiles * 8;
         double s = 0.0;
-        for (int i = tid; i < n_tiles * 8; i += NT_F) s += (double)__ldcg(pm + i);
+        for (int i = tid; i < (int)gridDim.x * 256; i += NT_F)       // fixed order: thread-strided, then warps in order
+            s += (double)__ldcg(partial + ((size_t)(i >> 8) * n_models + m) * 256 + (i & 255));
         s = warp_sum(s);
         if (lane == 0) S.red[warp] = s;
         __syncthreads();
@@ -606,7 +614,8 @@ int encode_x_map_f(CUtensorMap* map, const float* base, int64_t rows) {
 
 extern "C" int64_t fm_score_fused_scratch_floats(int64_t x_rows, int32_t n_models) {
     const int64_t n_tiles = (x_rows + fm::tc::TROWS - 1) / fm::tc::TROWS;
-    return n_tiles * 8 * (int64_t)(n_models > 0 ? n_models : 1);
+    (void)n_tiles;                                   // per-thread running sums: [CTAs <= 160][models][256]
+    return 160 * 256 * (int64_t)(n_models > 0 ? n_models : 1);
 }
 
 extern "C" int fm_score_fused_f16(const FmFusedScoreArgs* a, void* stream) {

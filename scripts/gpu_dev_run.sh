@@ -1,7 +1,13 @@
 #!/usr/bin/env bash
 mkdir -p gpurun_out
-echo "== hybrid mse_avg random-k (baseline)"; timeout 300 python scripts/gossip_dynamics.py --rounds 21 2>&1 | tail -8
-echo "== hybrid avg"; timeout 300 python scripts/gossip_dynamics.py --rounds 21 --update avg 2>&1 | tail -4
-echo "== autoencoder mse_avg"; timeout 300 python scripts/gossip_dynamics.py --rounds 21 --model autoencoder 2>&1 | tail -4
-echo "== hybrid mse_avg, no gossip merging: elected"; timeout 300 python scripts/gossip_dynamics.py --rounds 21 --aggregation elected 2>&1 | tail -4
-echo "== hybrid mse_avg participation 1.0"; timeout 300 python scripts/gossip_dynamics.py --rounds 21 --participation 1.0 2>&1 | tail -4
+timeout 300 python -m pytest tests -m gpu -x -q -s --timeout 200 -k "fused" > gpurun_out/t11_tests.log 2>&1; grep -E "worst relative|passed|failed|Error" gpurun_out/t11_tests.log | tail -6
+for mult in 1 8; do
+  echo "score phase: dev rows x$mult, fp16x3"; timeout 200 python scripts/prof_kernels.py score --score-precision fp16x3 --iters 4 --dev-rows-mult $mult 2>&1 | tail -1
+  timeout 200 python scripts/prof_kernels.py score --score-precision fp16x3 --iters 3 --dev-rows-mult $mult --phase-cycles 2>&1 | tail -1
+done
+timeout 300 python bench.py --steps 20 --warmup 5 > gpurun_out/t11_bench.json 2> gpurun_out/t11_bench.err
+python - <<PY
+import json
+d = json.load(open("gpurun_out/t11_bench.json"))
+print("bench ms/step", round(d["ms_per_step"], 4), "e2e ms", round(d["e2e"]["ms_per_step"], 4), "phases", d["phases_ms"], "auc", d["auc_mean_last_round"])
+PY
