@@ -287,7 +287,12 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                 int unit1 = -1;
                 for (int q = 0; q < n_pairs; ++q) {
                     const int r = q & 1;
-                    if (c1.ord != unit1) { mbar_wait(&S.bar_xt, (uint32_t)(c1.ord & 1)); unit1 = c1.ord; }   // tile parked
+                    if (c1.ord != unit1) {
+                        if (tk_on && c1.ord >= 1 && c1.ord <= 4) dbg[32 + 8 * (c1.ord - 1)] = (unsigned long long)clock64();
+                        mbar_wait(&S.bar_xt, (uint32_t)(c1.ord & 1));                                     // tile parked
+                        if (tk_on && c1.ord >= 1 && c1.ord <= 4) dbg[33 + 8 * (c1.ord - 1)] = (unsigned long long)clock64();
+                        unit1 = c1.ord;
+                    }
                     FT(TK_1_XT);
                     mbar_wait(&S.bar_w1[s], sph);
                     FT(TK_1_W);
@@ -385,6 +390,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     mbar_expect_tx(&S.bar_x, 4u * XBLK);
 #pragma unroll
                     for (int kb = 0; kb < 4; ++kb) tma_load_2d(S.x + kb * XBLK, &xmap, kb * 32, cx.tile * TROWS, &S.bar_x);
+                    if (TIMING && blockIdx.x == 0 && lx >= 1 && lx <= 4) dbg[37 + 8 * (lx - 1)] = (unsigned long long)clock64();
                     next_unit(cx); ++lx;
                 }
                 if (l1 < n_pairs && (l1 < NW || mbar_test(&S.bar_w1free[l1 % NW], (uint32_t)((l1 / NW - 1) & 1)))) {
@@ -461,14 +467,17 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             FT(TK_A_IDLE);
             if (parked < n_units_ne && (qe1 >= n_pairs || ce1.ord >= parked) &&
                 uniform(mbar_test(&S.bar_x, (uint32_t)(parked & 1)))) {
+                if (tk_on && parked >= 1 && parked <= 4) dbg[34 + 8 * (parked - 1)] = (unsigned long long)clock64();
                 park_x(parked);
+                if (tk_on && parked >= 1 && parked <= 4) dbg[35 + 8 * (parked - 1)] = (unsigned long long)clock64();
                 ++parked;
                 did = true;
                 FT(TK_A_PARK);
             }
             if (qe1 < n_pairs && uniform(mbar_test(&S.bar_d1[qe1 & (NB - 1)], (uint32_t)((qe1 / NB) & 1)))) {
                 e1(qe1);
-                next_pair(ce1);
+                { const int o0 = ce1.ord; next_pair(ce1);
+                  if (tk_on && ce1.ord != o0 && o0 < 4) dbg[36 + 8 * o0] = (unsigned long long)clock64(); }   // last e1 of unit o0 done
                 ++qe1;
                 did = true;
                 FT(TK_A_E1);

@@ -43,7 +43,7 @@ eng = FederationEngine(cfg, sh, "hybrid", "mse_avg")
 be, st = eng.backend, eng.state
 if a.phase_cycles:
     be.phase_cycles = torch.zeros(16, dtype=torch.int64, device=dev)
-    be.mm_cycles = torch.zeros(32, dtype=torch.int64, device=dev)
+    be.mm_cycles = torch.zeros(96, dtype=torch.int64, device=dev)
 ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
 for it in range(a.iters):
     ctl = eng.make_control(it)
@@ -82,6 +82,11 @@ for it in range(a.iters):
         tot = cyc[20] or 1
         print("  fused f16 kernel, CTA 0 (k cycles, % of the MMA1 thread's loop): " +
               ", ".join(f"{n} {c / 1e3:.0f}k ({100 * c / tot:.0f}%)" for n, c in zip(names, cyc[:23]) if c))
+        for k in range(4):
+            w0, w1, p0, p1, e_last, xl = cyc[32 + 8 * k: 38 + 8 * k]
+            if w0:
+                print(f"  boundary {k + 1}: MMA1 thread waits {w1 - w0} cycles for the tile; relative to its arrival: last e1 of the unit "
+                      f"{e_last - w0:+d}, parking starts {p0 - w0:+d}, ends {p1 - w0:+d}, TMA load of this tile was issued {xl - w0:+d}")
     elif a.phase_cycles and a.what == "score" and be.tc:
         names = ["issue MMA1(g+1)", "wait MMA2(g-1)", "wait epi1(g)", "wait w4 image", "wait D2 free", "issue MMA2(g)",
                  "wait X in TMEM", "wait X staging free",
