@@ -1,6 +1,5 @@
 #!/usr/bin/env bash
 mkdir -p gpurun_out
-timeout 200 python scripts/prof_kernels.py score --score-precision fp16x3 --iters 3 --dev-rows-mult 8 2>&1 | tail -3
-timeout 400 ncu --set full --clock-control none --import-source on -k regex:score_fused_f16 -s 2 -c 1 -o gpurun_out/prof_fused_v8 \
-    python scripts/prof_kernels.py score --score-precision fp16x3 --iters 2 --dev-rows-mult 8 > gpurun_out/ncu_fused_v8.log 2>&1
-tail -2 gpurun_out/ncu_fused_v8.log
+for m in 0 1 7 11 13 3 5 9; do
+  echo "probe mode $m"; timeout 100 python scripts/prof_kernels.py score --score-precision fp16x3 --iters 3 --dev-rows-mult 8 --phase-cycles --probe-mode $m 2>&1 | grep -E "score iter 2|fused f16 kernel" | cut -c1-900
+done

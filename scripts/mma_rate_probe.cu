@@ -1,0 +1,289 @@
+// Probe: how many cycles does ONE tcgen05.mma (kind::f16, M = 128, K = 16, fp32 accumulate) cost on an SM as a function of N
+// and of where A comes from (TMEM "TS" vs shared memory "SS")?
+//
+// The fused scoring kernel (csrc/score_fused_f16.cu) issues, per (tile, model) pair, 24 MMAs of N = 32 (layer 1), 4 of
+// N = 32 (bottleneck) and 4 of N = 128 (output layer), all with A in TMEM.  Nominal math time is N / 2 cycles per MMA
+// (8192 dense fp16 FLOP / clk / SM), i.e. 16 cycles at N = 32 -- but with the epilogues switched off the kernel's
+// layer-1 GEMM alone ran at ~28 cycles per MMA.  This probe issues a back-to-back train of R identical MMAs from one
+// thread, commits, waits, and reports (retire - first issue) / R for N in {16, 32, 64, 128, 256} x {TS, SS}, with the
+// accumulator alternating between two column ranges (as the kernel's rings do) or staying on one.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -Icsrc scripts/mma_rate_probe.cu -o build/mma_rate_probe
+#include <cstdio>
+#include <cstdlib>
+#include "tc_common.cuh"
+
+using namespace fm;
+using namespace fm::tc;
+
+__host__ __device__ constexpr uint32_t idesc_f16(int M, int N) {
+    return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void mma_ts_f16(uint32_t d, uint32_t a, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, {%5, %5, %5, %5}, p;\n\t}\n"
+                 ::"r"(d), "r"(a), "l"(bdesc), "r"(idesc), "r"(accum), "r"(0u) : "memory");
+}
+__device__ __forceinline__ void mma_ss_f16(uint32_t d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}\n"
+                 ::"r"(d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum), "r"(0u) : "memory");
+}
+
+struct PSmem {
+    alignas(1024) unsigned char a[128 * 128];        // A: 128 rows x 64 fp16, 128-B swizzle (contents irrelevant)
+    alignas(1024) unsigned char b[256 * 128];        // B: up to 256 rows x 64 fp16
+    alignas(1024) unsigned char img[6][16384];       // image ring for the protocol test
+    alignas(8) uint64_t bar;
+    uint64_t full[6], freeb[6], dummy;
+    uint32_t tmem_base;
+};
+
+constexpr int R = 512;
+
+// NACC independent accumulators used round-robin (dependent distance NACC)
+template <int N, int NACC>
+__device__ long long run_rr(PSmem& S, uint32_t tmem, uint32_t& phase) {
+    constexpr uint32_t idesc = idesc_f16(128, N);
+    const uint64_t db = smem_desc_sw128(S.b);
+    const uint32_t a_t = tmem + 480;
+    const long long t0 = clock64();
+#pragma unroll 8
+    for (int i = 0; i < R; ++i) {
+        const uint32_t d = tmem + (uint32_t)((i % NACC) * N);
+        const uint64_t ko = (uint64_t)(((i & 3) * 32) >> 4);
+        mma_ts_f16(d, a_t, db + ko, idesc, 1u);
+    }
+    tc_commit(&S.bar);
+    mbar_wait(&S.bar, phase);
+    phase ^= 1u;
+    return clock64() - t0;
+}
+
+// the kernel's layer-1 pattern: per k-step three MMAs (A0.B0, A0.B1, A1.B0), A walking 8 columns per k-step, B walking the
+// k-steps of two images; AMODE 0 = A fixed, 1 = A walks; BMODE 0 = B fixed, 1 = B walks
+template <int N, int AMODE, int BMODE>
+__device__ long long run_l1(PSmem& S, uint32_t tmem, uint32_t& phase) {
+    constexpr uint32_t idesc = idesc_f16(128, N);
+    const uint64_t db = smem_desc_sw128(S.b);
+    const uint32_t a_h = tmem + 384, a_l = tmem + 448;       // 64 columns each, as X hi / lo in the kernel
+    const long long t0 = clock64();
+    for (int g = 0; g < R / 24; ++g) {
+        const uint32_t d = tmem + (uint32_t)((g & 1) * N);
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {
+            const uint32_t ao = AMODE ? (uint32_t)(kk * 8) : 0u;
+            const uint64_t bh = db + (BMODE ? (uint64_t)(((kk >> 2) * 4096 + (kk & 3) * 32) >> 4) : 0ull);
+            const uint64_t bl = bh + (BMODE ? (uint64_t)(8192 >> 4) : 0ull);
+            mma_ts_f16(d, a_h + ao, bh, idesc, kk ? 1u : 0u);
+            mma_ts_f16(d, a_h + ao, bl, idesc, 1u);
+            mma_ts_f16(d, (AMODE ? a_l : a_h) + ao, bh, idesc, 1u);
+        }
+    }
+    tc_commit(&S.bar);
+    mbar_wait(&S.bar, phase);
+    phase ^= 1u;
+    return (clock64() - t0) * R / ((R / 24) * 24);
+}
+
+// The kernel's layer-1 protocol in isolation: G groups of 24 MMAs (N = 32), each group waits for "its" 16 KB image in a
+// ring of NWP stages, commits "group done" and "stage free"; a second thread refills a stage as soon as it is free.
+// MODE 0: no images at all (commits only); 1: images stream in the background but the MMA thread never waits for them;
+// 2: the full protocol.  Returns cycles per group.
+constexpr int G = 400;
+template <int NWP, int MODE>
+__device__ void l1_protocol(PSmem& S, uint32_t tmem, const unsigned char* gimg, int n_img, int warp, long long* out_slot) {
+    if (warp == 1) {
+        if (elect_one()) {
+            constexpr uint32_t idesc = idesc_f16(128, 32);
+            const uint32_t a_h = tmem + 384, a_l = tmem + 448;
+            int s = 0; uint32_t sph = 0;
+            const long long t0 = clock64();
+            for (int g = 0; g < G; ++g) {
+                if (MODE == 2) mbar_wait(&S.full[s], sph);
+                tc_fence_after();
+                const uint64_t db = smem_desc_sw128(MODE == 2 ? S.img[s] : S.b);
+                const uint32_t d = tmem + (uint32_t)((g & 1) * 32);
+#pragma unroll
+                for (int kk = 0; kk < 8; ++kk) {
+                    const uint64_t bh = db + (uint64_t)(((kk >> 2) * 4096 + (kk & 3) * 32) >> 4), bl = bh + (uint64_t)(8192 >> 4);
+                    mma_ts_f16(d, a_h + kk * 8, bh, idesc, kk ? 1u : 0u);
+                    mma_ts_f16(d, a_h + kk * 8, bl, idesc, 1u);
+                    mma_ts_f16(d, a_l + kk * 8, bh, idesc, 1u);
+                }
+                tc_commit(&S.dummy);
+                tc_commit(&S.freeb[s]);
+                if (++s == NWP) { s = 0; sph ^= 1u; }
+            }
+            tc_commit(&S.bar);
+            mbar_wait(&S.bar, 0);
+            *out_slot = (clock64() - t0) / G;
+        }
+        __syncwarp();
+    } else if (warp == 2 && MODE != 0) {
+        if (elect_one()) {
+            for (int l = 0; l < G; ++l) {
+                const int st = l % NWP;
+                if (l >= NWP) mbar_wait(&S.freeb[st], (uint32_t)((l / NWP - 1) & 1));
+                mbar_expect_tx(&S.full[st], 16384u);
+                bulk_g2s(S.img[st], gimg + (size_t)(l % n_img) * 36864, 16384u, &S.full[st]);
+            }
+            for (int l = G - NWP; l < G; ++l) mbar_wait(&S.full[l % NWP], (uint32_t)((l / NWP) & 1));   // nothing in flight at exit
+        }
+        __syncwarp();
+    }
+}
+
+template <int NWP, int MODE>
+__global__ void __launch_bounds__(128, 1) probe_protocol(long long* out, const unsigned char* gimg, int n_img) {
+    extern __shared__ __align__(1024) unsigned char smem_dyn[];
+    PSmem& S = *reinterpret_cast<PSmem*>(smem_dyn);
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    for (int i = tid; i < (int)sizeof(PSmem) / 4; i += 128) reinterpret_cast<uint32_t*>(smem_dyn)[i] = 0u;
+    __syncthreads();
+    if (tid == 0) {
+        mbar_init(&S.bar, 1); mbar_init(&S.dummy, 1);
+        for (int i = 0; i < 6; ++i) { mbar_init(&S.full[i], 1); mbar_init(&S.freeb[i], 1); }
+        fence_mbar_init();
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)), "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = S.tmem_base;
+    l1_protocol<NWP, MODE>(S, tmem, gimg, n_img, warp, out + blockIdx.x);
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
+}
+
+template <int NWP, int MODE>
+void run_protocol(long long* out, const unsigned char* gimg, const char* what) {
+    cudaFuncSetAttribute(probe_protocol<NWP, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem) + 1024);
+    for (int grid : {1, 148}) {
+        probe_protocol<NWP, MODE><<<grid, 128, sizeof(PSmem) + 1024>>>(out, gimg, 62);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("error: %s\n", cudaGetErrorString(e)); return; }
+        long long h[148];
+        cudaMemcpy(h, out, sizeof(long long) * grid, cudaMemcpyDeviceToHost);
+        long long mx = 0, sum = 0;
+        for (int i = 0; i < grid; ++i) { mx = h[i] > mx ? h[i] : mx; sum += h[i]; }
+        printf("  %-58s grid %3d: %5lld cycles per group of 24 MMAs (max over CTAs %lld; nominal 394)\n", what, grid, sum / grid, mx);
+    }
+}
+
+template <int N, bool TS, bool ALT>
+__device__ long long run(PSmem& S, uint32_t tmem, uint32_t& phase) {
+    constexpr uint32_t idesc = idesc_f16(128, N);
+    const uint64_t da = smem_desc_sw128(S.a), db = smem_desc_sw128(S.b);
+    const uint32_t a_t = tmem + 480;                  // 8 columns of packed fp16 (K = 16), whatever they hold
+    const long long t0 = clock64();
+#pragma unroll 8
+    for (int i = 0; i < R; ++i) {
+        const uint32_t d = tmem + ((ALT && (i & 8)) ? 256u : 0u);
+        const uint64_t ko = (uint64_t)(((i & 3) * 32) >> 4);                                // walk the 4 k-steps of the block
+        if (TS) mma_ts_f16(d, a_t, db + ko, idesc, 1u); else mma_ss_f16(d, da + ko, db + ko, idesc, 1u);
+    }
+    tc_commit(&S.bar);
+    const long long t1 = clock64();
+    mbar_wait(&S.bar, phase);
+    phase ^= 1u;
+    const long long t2 = clock64();
+    (void)t1;
+    return t2 - t0;
+}
+
+__global__ void __launch_bounds__(128, 1) probe(long long* out) {
+    extern __shared__ __align__(1024) unsigned char smem_dyn[];
+    PSmem& S = *reinterpret_cast<PSmem*>(smem_dyn);
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < (int)sizeof(PSmem) / 4; i += 128) reinterpret_cast<uint32_t*>(smem_dyn)[i] = 0u;
+    __syncthreads();
+    if (tid == 0) { mbar_init(&S.bar, 1); fence_mbar_init(); }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)), "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = S.tmem_base;
+    if (__shfl_sync(0xffffffffu, warp, 0) == 1 && elect_one()) {       // the kernel's issue pattern: no per-MMA election loop in the SASS
+        uint32_t phase = 0;
+        long long* o = out + blockIdx.x * 32;
+        int k = 0;
+        for (int rep = 0; rep < 2; ++rep) {           // second pass is the one reported (first warms the instruction cache)
+            k = 0;
+            o[k++] = run<16, true, true>(S, tmem, phase);
+            o[k++] = run<32, true, true>(S, tmem, phase);
+            o[k++] = run<64, true, true>(S, tmem, phase);
+            o[k++] = run<128, true, true>(S, tmem, phase);
+            o[k++] = run<256, true, false>(S, tmem, phase);
+            o[k++] = run<16, false, true>(S, tmem, phase);
+            o[k++] = run<32, false, true>(S, tmem, phase);
+            o[k++] = run<64, false, true>(S, tmem, phase);
+            o[k++] = run<128, false, true>(S, tmem, phase);
+            o[k++] = run<256, false, false>(S, tmem, phase);
+            o[k++] = run<32, true, false>(S, tmem, phase);
+            o[k++] = run<32, false, false>(S, tmem, phase);
+            o[k++] = run<128, true, false>(S, tmem, phase);
+            o[k++] = run_rr<32, 1>(S, tmem, phase);
+            o[k++] = run_rr<32, 2>(S, tmem, phase);
+            o[k++] = run_rr<32, 3>(S, tmem, phase);
+            o[k++] = run_rr<32, 4>(S, tmem, phase);
+            o[k++] = run_rr<32, 8>(S, tmem, phase);
+            o[k++] = run_rr<64, 2>(S, tmem, phase);
+            o[k++] = run_rr<64, 4>(S, tmem, phase);
+            o[k++] = run_rr<16, 4>(S, tmem, phase);
+            o[k++] = run_rr<16, 8>(S, tmem, phase);
+            o[k++] = run_l1<32, 0, 0>(S, tmem, phase);
+            o[k++] = run_l1<32, 1, 0>(S, tmem, phase);
+            o[k++] = run_l1<32, 0, 1>(S, tmem, phase);
+            o[k++] = run_l1<32, 1, 1>(S, tmem, phase);
+            o[k++] = run_l1<64, 1, 1>(S, tmem, phase);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
+}
+
+int main(int argc, char** argv) {
+    const int which = argc > 1 ? atoi(argv[1]) : -1;
+    long long* out;
+    cudaMalloc(&out, 148 * 32 * sizeof(long long));
+    cudaMemset(out, 0, 148 * 32 * sizeof(long long));
+    cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem) + 1024);
+    const char* names[27] = {"TS N=16", "TS N=32", "TS N=64", "TS N=128", "TS N=256", "SS N=16", "SS N=32", "SS N=64", "SS N=128",
+                             "SS N=256", "TS N=32 one accumulator", "SS N=32 one accumulator", "TS N=128 one accumulator",
+                             "TS N=32 round-robin 1", "TS N=32 round-robin 2", "TS N=32 round-robin 3", "TS N=32 round-robin 4",
+                             "TS N=32 round-robin 8", "TS N=64 round-robin 2", "TS N=64 round-robin 4", "TS N=16 round-robin 4",
+                             "TS N=16 round-robin 8", "layer-1 pattern N=32 A,B fixed", "layer-1 N=32 A walks", "layer-1 N=32 B walks",
+                             "layer-1 N=32 A and B walk", "layer-1 N=64 A and B walk"};
+    const int nominal[27] = {8, 16, 32, 64, 128, 8, 16, 32, 64, 128, 16, 16, 64, 16, 16, 16, 16, 16, 32, 32, 8, 8, 16, 16, 16, 16, 32};
+    for (int grid : {1}) {
+        if (which >= 0) break;
+        probe<<<grid, 128, sizeof(PSmem) + 1024>>>(out);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("error: %s\n", cudaGetErrorString(e)); return 1; }
+        long long h[32];
+        cudaMemcpy(h, out, sizeof(h), cudaMemcpyDeviceToHost);
+        printf("grid %d, %d back-to-back MMAs (M=128, K=16, kind::f16), cycles per MMA incl. commit + wake-up / %d:\n", grid, R, R);
+        for (int i = 0; i < 27; ++i) printf("  %-32s %7.1f   (nominal %d)\n", names[i], (double)h[i] / R, nominal[i]);
+    }
+    unsigned char* gimg;
+    cudaMalloc(&gimg, 62 * 36864);
+    cudaMemset(gimg, 0, 62 * 36864);
+    printf("layer-1 protocol (group = 24 MMAs N=32 + 2 commits; 16 KB image per group through a ring):\n");
+    if (which < 0 || which == 0) run_protocol<3, 0>(out, gimg, "no images");
+    if (which == 1) run_protocol<3, 1>(out, gimg, "images stream in the background, never waited for");
+    if (which == 2) run_protocol<2, 2>(out, gimg, "full protocol, ring of 2");
+    if (which == 3) run_protocol<3, 2>(out, gimg, "full protocol, ring of 3");
+    if (which == 4) run_protocol<4, 2>(out, gimg, "full protocol, ring of 4");
+    if (which == 6) run_protocol<6, 2>(out, gimg, "full protocol, ring of 6");
+    return 0;
+}
