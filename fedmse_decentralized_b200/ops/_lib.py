@@ -51,6 +51,12 @@ class FmScoreGenericArgs(C.Structure):
                 ("lat_pitch", C.c_int32), ("dim", C.c_int32), ("hidden", C.c_int32), ("latent", C.c_int32)]
 
 
+class FmKdeJsArgs(C.Structure):
+    _fields_ = [("slab", c_vp), ("slot_client", c_vp), ("first_client", C.c_int32), ("n_local", C.c_int32),
+                ("n_slots", C.c_int32), ("X", c_vp), ("n_rows", C.c_int32), ("rec_scratch", c_vp), ("dens", c_vp),
+                ("dist_out", c_vp)]
+
+
 class FmScoreArgs(C.Structure):
     _fields_ = [("slab", c_vp), ("slot_client", c_vp), ("first_client", C.c_int32), ("n_local", C.c_int32),
                 ("X", c_vp), ("tiles", c_vp), ("n_tiles", C.c_int32), ("out_sse", c_vp), ("out_lat", c_vp)]
@@ -186,6 +192,7 @@ def load() -> C.CDLL:
         ("fm_train_clients", [C.POINTER(FmTrainArgs), c_vp]),
         ("fm_train_generic", [C.POINTER(FmTrainGenericArgs), c_vp]),
         ("fm_score_generic", [C.POINTER(FmScoreGenericArgs), c_vp]),
+        ("fm_kde_js", [C.POINTER(FmKdeJsArgs), c_vp]),
         ("fm_score_rows", [C.POINTER(FmScoreArgs), c_vp]),
         ("fm_score_rows_tc", [C.POINTER(FmScoreArgs), C.c_int64, C.c_int32, c_vp, c_vp]),
         ("fm_split_residual", [c_vp, c_vp, C.c_int64, c_vp]),
@@ -226,6 +233,8 @@ def load() -> C.CDLL:
     lib.fm_score_fused_scratch_floats.restype = C.c_int64
     lib.fm_train_generic_scratch_floats.argtypes = [C.c_int32] * 4
     lib.fm_train_generic_scratch_floats.restype = C.c_int64
+    lib.fm_kde_js_scratch_floats.argtypes = [C.c_int32, C.c_int32]
+    lib.fm_kde_js_scratch_floats.restype = C.c_int64
     lib.fm_auc_scratch_keys.argtypes = [C.c_int32]
     lib.fm_auc_scratch_keys.restype = C.c_int64
     lib.fm_vote_scores_static_error.argtypes = []

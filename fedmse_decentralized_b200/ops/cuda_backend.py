@@ -330,17 +330,26 @@ class CudaBackend:
         return self.mse[:n]
 
     def fusion_scores(self, st, sh, ctl: RoundControl, max_rows: int) -> torch.Tensor:
-        """``fusion_avg`` weights (the reference's orphaned KDE / Jensen-Shannon similarity): batched
-        torch GEMM + logsumexp on the device (a library path by design: O(n_sel x rows^2 x 115) on <= 512 rows);
-        the distances then ride the same board exchange and merge kernel as the MSE scores."""
-        from ..utils.similarity import fusion_distances
+        """``fusion_avg`` weights (the reference's orphaned KDE / Jensen-Shannon similarity) on the device:
+        ``csrc/similarity_kernel.cu`` reconstructs the first ``max_rows`` dev rows with every locally owned selected
+        model, takes the Gaussian-KDE self log-density of each reconstruction and its JS distance to that of the rows
+        themselves; the distances then ride the same board exchange and merge kernel as the MSE scores.
+        (fp64 torch oracle of the same quantity: ``utils.similarity.fusion_distances``.)"""
         n = len(ctl.sel)
-        f, C_ = sh.first_client, st.n_clients
-        own = [(pos, g - f) for pos, g in enumerate(ctl.sel) if f <= g < f + C_]
+        rows = int(min(max_rows, self.dev_rows))
+        if rows < 2:
+            raise ValueError("fusion_avg needs at least two dev rows")
+        key = (n, rows)
+        if getattr(self, "_kde_key", None) != key:
+            need = int(self.lib.fm_kde_js_scratch_floats(n, rows))
+            self._kde_rec = torch.empty(need, dtype=torch.float32, device=self.device)
+            self._kde_dens = torch.empty((n + 1) * rows, dtype=torch.float32, device=self.device)
+            self._kde_key = key
         self.mse.zero_()
-        if own:
-            d = fusion_distances(st.params[[c for _, c in own]], sh.dev, self.layout, max_rows)
-            self.mse[torch.tensor([pos for pos, _ in own], device=self.device)] = d
+        a = _lib.FmKdeJsArgs(_ptr(st.params), _ptr(self.ctl_sel), sh.first_client, st.n_clients, n, _ptr(sh.dev), rows,
+                             _ptr(self._kde_rec), _ptr(self._kde_dens), _ptr(self.mse))
+        _lib.check(self.lib.fm_kde_js(C.byref(a), self._stream()), "kde_js")
+        self.launches += 2
         if self.exchanges_scores:
             return self._publish(self.mse, n, 1)
         return self.mse[:n]

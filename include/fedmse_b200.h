@@ -96,6 +96,19 @@ typedef struct FmScoreGenericArgs {
 } FmScoreGenericArgs;
 int fm_score_generic(const FmScoreGenericArgs* args, void* stream);
 
+/* ---- T6: fusion_avg weight function (reference: src/Utils/utils.py:10-24) ---------------------
+ * For every slot whose client is local: reconstruct the first n_rows rows of X with the slot's model, take the Gaussian
+ * KDE (Scott bandwidth) self log-density of those n_rows points, and write the Jensen-Shannon distance between its
+ * exp() and that of the rows themselves to dist_out[slot] (+1e-12, so 1/d is finite).  rec_scratch needs
+ * fm_kde_js_scratch_floats(n_slots, n_rows) floats, dens (n_slots + 1) * n_rows floats. */
+typedef struct FmKdeJsArgs {
+    const float* slab; const int32_t* slot_client; int32_t first_client; int32_t n_local; int32_t n_slots;
+    const float* X; int32_t n_rows;
+    float* rec_scratch; float* dens; float* dist_out;
+} FmKdeJsArgs;
+int fm_kde_js(const FmKdeJsArgs* args, void* stream);
+int64_t fm_kde_js_scratch_floats(int32_t n_slots, int32_t n_rows);
+
 /* ---- row scoring forward (shared by T2 vote/merge scoring, T3 verification, T4 evaluation) --
  * For every tile {slot, row0, nrows<=64, out0}: run the model of `slot` over rows
  * X[row0 .. row0+nrows) and write per-row sum of squared reconstruction error to

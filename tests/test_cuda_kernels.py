@@ -333,6 +333,41 @@ def test_fused_f16_scoring_matches_oracle(tmp_path, dev, n_clients, rows):
     print(f"fused f16 scoring: worst relative MSE error {worst:.2e}")
 
 
+@pytest.mark.parametrize("rows", [40, 300])
+def test_kde_js_kernel_matches_fp64_oracle(tiny_clients, tmp_path, dev, rows):
+    """T6 (csrc/similarity_kernel.cu): KDE self log-density + Jensen-Shannon distance of every selected model's
+    reconstruction of the dev rows, against the fp64 torch form of the reference's weight function."""
+    from fedmse_decentralized_b200.utils.similarity import fusion_distances
+    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "hybrid", "fusion_avg", update_types=["fusion_avg"],
+                         fusion_rows=rows, num_participants=0.7)
+    ctl = e_ref.make_control(0)
+    e_gpu.backend.begin_round(ctl)
+    for e in (e_ref, e_gpu):
+        e.backend.train(e.state, e.sh, e._sel_local(ctl.sel), e.hp)
+    got = e_gpu.backend.fusion_scores(e_gpu.state, e_gpu.sh, ctl, rows)
+    torch.cuda.synchronize()
+    n = min(rows, e_gpu.sh.dev.shape[0])
+    want = fusion_distances(e_gpu.state.params[ctl.sel].double().float(), e_gpu.sh.dev, L, n)
+    assert got.shape == want.shape and bool(torch.isfinite(got).all()) and float(got.min()) > 0
+    assert_close(got, want, 2e-3, 1e-6, "JS distances")
+    w_got, w_want = (1 / got) / (1 / got).sum(), (1 / want) / (1 / want).sum()
+    assert_close(w_got, w_want, 2e-3, 1e-6, "fusion_avg weights")
+
+
+def test_full_round_with_fusion_avg(tiny_clients, tmp_path, dev):
+    e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "hybrid", "fusion_avg", update_types=["fusion_avg"],
+                         fusion_rows=64, num_participants=0.7)
+    for r in range(2):
+        random.seed(70 + r); torch.manual_seed(70 + r)
+        ctl = e_ref.make_control(r)
+        res_ref = e_ref.run_round(r, copy.deepcopy(ctl))
+        res_gpu = e_gpu.run_round(r, copy.deepcopy(ctl))
+        assert res_gpu.aggregator == res_ref.aggregator
+        # the fp32 kernel's JS distances agree with the fp64 oracle to ~1e-3 relative, and so do the merge weights
+        assert_close(e_gpu.state.params, e_ref.state.params, 3e-3, 2e-4, f"params r{r}")
+        assert_close(torch.tensor(res_gpu.client_metrics), torch.tensor(res_ref.client_metrics), 0, 2e-3, "auc")
+
+
 def test_full_round_with_fused_f16_scoring(tiny_clients, tmp_path, dev):
     e_ref, e_gpu = _pair(tiny_clients, tmp_path, dev, "hybrid", "mse_avg", score_precision="fp16x3",
                          num_participants=0.7)
