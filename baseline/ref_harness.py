@@ -226,10 +226,15 @@ class ReferenceFederation:
         if aggregator:
             state = aggregator.aggregate_models(sel_tr, sel_info[0]["validation_data"], rnd)
             if state:
-                for client in trainers:
+                # src/main.py:298-306 hands the state to every client.  A rank only ever reads the models of the clients
+                # it owns (their next training, their evaluation) and of the SELECTED clients (refreshed from their
+                # owners by the all_gather above), so with world > 1 it runs the reference's receive + CPU verification
+                # for its own clients only -- not N times the same 1000 verifications on every rank.
+                mine = trainers if self.world == 1 else [trainers[i] for i in self.owned]
+                for client in mine:
                     if client != aggregator:
                         client.receive_model(aggregator, state)
-                for client in trainers:
+                for client in mine:
                     if client != aggregator:
                         client.update_from_peers()
         metrics = []
