@@ -31,3 +31,4 @@ probes:
 	$(NVCC) $(ARCH) -O3 -std=c++17 -Icsrc scripts/train_step_tc_probe.cu -o build/train_step_tc_probe -lcuda
 	$(NVCC) $(ARCH) -O3 -std=c++17 -Icsrc scripts/mma_rate_probe.cu -o build/mma_rate_probe
 	$(NVCC) $(ARCH) -O3 -std=c++17 -Icsrc scripts/l2_to_smem_probe.cu -o build/l2_to_smem_probe
+	$(NVCC) $(ARCH) -O3 -std=c++17 -Icsrc scripts/tmem_port_probe.cu -o build/tmem_port_probe
