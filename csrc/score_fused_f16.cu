@@ -65,6 +65,7 @@ constexpr float F16_MAX = 65504.f;
 // parking+epilogue warp 0: park, e1, e1b, idle polling; squared-error warp 4: wait D2, until D2 released, rest, unit entry
 enum { TK_1_XT = 0, TK_1_W, TK_1_FREE, TK_1_ISSUE, TK_1B_H, TK_1B_W, TK_1B_FREE, TK_1B_ISSUE, TK_2_H, TK_2_W, TK_2_FREE, TK_2_ISSUE,
        TK_A_PARK, TK_A_E1, TK_A_E1B, TK_A_IDLE, TK_B_WAIT, TK_B_HOLD, TK_B_REST, TK_B_ENTRY, TK_TOTAL, TK_N };
+constexpr int TRACE_N = 96, TRACE_BASE = 128;      // TIMING: time line of the first TRACE_N pairs of CTA 0, 13 events each
 #define FT(slot) do { if (TIMING && tk_on) { const long long now_ = clock64(); tk[slot] += now_ - tk_t; tk_t = now_; } } while (0)
 
 struct FSmem {
@@ -298,6 +299,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     FT(TK_1_W);
                     if (q >= NB) mbar_wait(&S.bar_d1free[r], (uint32_t)(((q - NB) >> 1) & 1));
                     FT(TK_1_FREE);
+                    if (TIMING && tk_on && (q) < TRACE_N) dbg[TRACE_BASE + 0 * TRACE_N + (q)] = (unsigned long long)clock64();
                     tc_fence_after();
                     const uint32_t d1 = tmem + C_D1 + 32 * r, xh = tmem + C_X, xl = tmem + C_XLO;
                     const uint64_t bw = dw1 + (uint64_t)((s * 2 * W1_BYTES) >> 4);
@@ -314,6 +316,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     next_pair(c1);
                     if (++s == NW) { s = 0; sph ^= 1u; }
                     FT(TK_1_ISSUE);
+                    if (TIMING && tk_on && (q) < TRACE_N) dbg[TRACE_BASE + 1 * TRACE_N + (q)] = (unsigned long long)clock64();
                 }
                 if (tk_on) tk[TK_TOTAL] = clock64() - tk_0;
             } else if (warp == MMA1B_WARP) {
@@ -322,6 +325,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     const int r = q & 1;
                     mbar_wait(&S.bar_h1[r], (uint32_t)((q >> 1) & 1));
                     FT(TK_1B_H);
+                    if (TIMING && tk_on && (q) < TRACE_N) dbg[TRACE_BASE + 4 * TRACE_N + (q)] = (unsigned long long)clock64();
                     mbar_wait(&S.bar_w32[s], sph);
                     FT(TK_1B_W);
                     if (q >= NB) mbar_wait(&S.bar_d1bfree[r], (uint32_t)(((q - NB) >> 1) & 1));
@@ -340,6 +344,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     tc_commit(&S.bar_d1free[r]);
                     if (++s == NW) { s = 0; sph ^= 1u; }
                     FT(TK_1B_ISSUE);
+                    if (TIMING && tk_on && (q) < TRACE_N) dbg[TRACE_BASE + 5 * TRACE_N + (q)] = (unsigned long long)clock64();
                 }
             } else {
                 const uint64_t dw4 = smem_desc_sw64(S.w4[0]);
@@ -347,6 +352,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     const int r = q & 1;
                     mbar_wait(&S.bar_h2[r], (uint32_t)((q >> 1) & 1));
                     FT(TK_2_H);
+                    if (TIMING && tk_on && (q) < TRACE_N) dbg[TRACE_BASE + 8 * TRACE_N + (q)] = (unsigned long long)clock64();
                     mbar_wait(&S.bar_w4[s], sph);
                     FT(TK_2_W);
                     if (q >= 2) mbar_wait(&S.bar_d2free[r], (uint32_t)(((q - 2) >> 1) & 1));
@@ -365,6 +371,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     tc_commit(&S.bar_d1bfree[r]);
                     if (++s == NW) { s = 0; sph ^= 1u; }
                     FT(TK_2_ISSUE);
+                    if (TIMING && tk_on && (q) < TRACE_N) dbg[TRACE_BASE + 9 * TRACE_N + (q)] = (unsigned long long)clock64();
                 }
             }
             if (tk_on) for (int i = 0; i < TK_N; ++i) if (tk[i]) dbg[i] = (unsigned long long)tk[i];
@@ -475,18 +482,22 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                 FT(TK_A_PARK);
             }
             if (qe1 < n_pairs && uniform(mbar_test(&S.bar_d1[qe1 & (NB - 1)], (uint32_t)((qe1 / NB) & 1)))) {
+                if (TIMING && tk_on && (qe1) < TRACE_N) dbg[TRACE_BASE + 2 * TRACE_N + (qe1)] = (unsigned long long)clock64();
                 e1(qe1);
                 { const int o0 = ce1.ord; next_pair(ce1);
                   if (tk_on && ce1.ord != o0 && o0 < 4) dbg[36 + 8 * o0] = (unsigned long long)clock64(); }   // last e1 of unit o0 done
                 ++qe1;
                 did = true;
                 FT(TK_A_E1);
+                if (TIMING && tk_on && (qe1 - 1) < TRACE_N) dbg[TRACE_BASE + 3 * TRACE_N + (qe1 - 1)] = (unsigned long long)clock64();
             }
             if (qe1b < qe1 && uniform(mbar_test(&S.bar_d1b[qe1b & (NB - 1)], (uint32_t)((qe1b / NB) & 1)))) {
+                if (TIMING && tk_on && (qe1b) < TRACE_N) dbg[TRACE_BASE + 6 * TRACE_N + (qe1b)] = (unsigned long long)clock64();
                 e1b(qe1b);
                 ++qe1b;
                 did = true;
                 FT(TK_A_E1B);
+                if (TIMING && tk_on && (qe1b - 1) < TRACE_N) dbg[TRACE_BASE + 7 * TRACE_N + (qe1b - 1)] = (unsigned long long)clock64();
             }
             if (!did) __nanosleep(20);
         }
@@ -529,6 +540,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             mbar_wait(&S.bar_d2[b], (uint32_t)((g >> 1) & 1));
             tc_fence_after();
             FT(TK_B_WAIT);
+            if (TIMING && tk_on && (g) < TRACE_N) dbg[TRACE_BASE + 10 * TRACE_N + (g)] = (unsigned long long)clock64();
             float2 acc[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
             auto acc_block = [&](int cb) {            // four independent chains: the FMAs pipeline
 #pragma unroll
@@ -544,10 +556,12 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             tc_fence_before();
             mbar_arrive(&S.bar_d2free[b]);            // this thread's share of D2[b] is in registers
             FT(TK_B_HOLD);
+            if (TIMING && tk_on && (g) < TRACE_N) dbg[TRACE_BASE + 11 * TRACE_N + (g)] = (unsigned long long)clock64();
             acc_block(1);
             const int row = c.tile * TROWS + r;
             const float sse = row < x_rows ? ((acc[0].x + acc[0].y) + (acc[1].x + acc[1].y)) + ((acc[2].x + acc[2].y) + (acc[3].x + acc[3].y)) : 0.f;
             atomicAdd(my_lane + (size_t)c.m * 256, sse);              // result unused: a RED; nobody else writes this slot
+            if (TIMING && tk_on && (g) < TRACE_N) dbg[TRACE_BASE + 12 * TRACE_N + (g)] = (unsigned long long)clock64();
             PairCursor cn = c;
             next_pair(cn);
             if (!cn.ok || cn.i != c.i) { ++ut; fresh = true; }

@@ -160,6 +160,65 @@ __global__ void __launch_bounds__(128, 1) probe_protocol(long long* out, const u
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
 }
 
+template <int K>
+__device__ long long run_commit_latency(PSmem& S, uint32_t tmem, uint32_t& phase);
+
+// Does mbarrier polling by other warps delay a commit's arrival?  Warp 1 measures "K MMAs + commit + spin until seen" while
+// n_poll other warps spin on a barrier that never completes (try_wait, or test_wait with no hardware suspend).
+template <int K>
+__global__ void __launch_bounds__(512, 1) probe_poll(long long* out, int n_poll, int use_test_wait) {
+    extern __shared__ __align__(1024) unsigned char smem_dyn[];
+    PSmem& S = *reinterpret_cast<PSmem*>(smem_dyn);
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    volatile int* stop = reinterpret_cast<volatile int*>(&S.tmem_base + 1);
+    for (int i = tid; i < (int)sizeof(PSmem) / 4; i += 512) reinterpret_cast<uint32_t*>(smem_dyn)[i] = 0u;
+    __syncthreads();
+    if (tid == 0) { mbar_init(&S.bar, 1); mbar_init(&S.dummy, 1); fence_mbar_init(); }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)), "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = S.tmem_base;
+    if (warp == 1) {
+        if (elect_one()) {
+            uint32_t phase = 0;
+            out[0] = run_commit_latency<K>(S, tmem, phase) / R;
+            *stop = 1;
+        }
+        __syncwarp();
+    } else if (warp >= 2 && warp < 2 + n_poll) {
+        while (*stop == 0) {
+            uint32_t ok;
+            if (use_test_wait)
+                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}\n"
+                             : "=r"(ok) : "r"(smem_u32(&S.dummy)), "r"(0u) : "memory");
+            else
+                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}\n"
+                             : "=r"(ok) : "r"(smem_u32(&S.dummy)), "r"(0u) : "memory");
+            if (ok) break;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
+}
+
+template <int K>
+void run_poll(long long* out, int n_poll, int use_test_wait) {
+    cudaFuncSetAttribute(probe_poll<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem) + 1024);
+    probe_poll<K><<<1, 512, sizeof(PSmem) + 1024>>>(out, n_poll, use_test_wait);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { printf("error: %s\n", cudaGetErrorString(e)); exit(1); }
+    long long h = 0;
+    cudaMemcpy(&h, out, sizeof(h), cudaMemcpyDeviceToHost);
+    printf("  %2d MMAs + commit + spin: %5lld cycles with %2d other warps polling an mbarrier (%s)\n", K, h, n_poll,
+           use_test_wait ? "test_wait" : "try_wait");
+}
+
 template <int NWP, int MODE>
 void run_protocol(long long* out, const unsigned char* gimg, const char* what) {
     cudaFuncSetAttribute(probe_protocol<NWP, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem) + 1024);
@@ -173,6 +232,25 @@ void run_protocol(long long* out, const unsigned char* gimg, const char* what) {
         for (int i = 0; i < grid; ++i) { mx = h[i] > mx ? h[i] : mx; sum += h[i]; }
         printf("  %-58s grid %3d: %5lld cycles per group of 24 MMAs (max over CTAs %lld; nominal 394)\n", what, grid, sum / grid, mx);
     }
+}
+
+// latency of one hand-over: K MMAs (N = 32) + commit, then spin on the barrier; returns cycles from the first issue to the
+// moment the issuing thread sees the barrier complete, averaged over 64 repetitions
+template <int K>
+__device__ long long run_commit_latency(PSmem& S, uint32_t tmem, uint32_t& phase) {
+    constexpr uint32_t idesc = idesc_f16(128, 32);
+    const uint64_t db = smem_desc_sw128(S.b);
+    long long tot = 0;
+    for (int rep = 0; rep < 64; ++rep) {
+        const long long t0 = clock64();
+#pragma unroll
+        for (int i = 0; i < K; ++i) mma_ts_f16(tmem, tmem + 480, db + (uint64_t)(((i & 3) * 32) >> 4), idesc, 1u);
+        tc_commit(&S.bar);
+        mbar_wait(&S.bar, phase);
+        phase ^= 1u;
+        tot += clock64() - t0;
+    }
+    return tot / 64 * R;      // the caller divides by R
 }
 
 template <int N, bool TS, bool ALT>
@@ -245,6 +323,9 @@ __global__ void __launch_bounds__(128, 1) probe(long long* out) {
             o[k++] = run_l1<32, 0, 1>(S, tmem, phase);
             o[k++] = run_l1<32, 1, 1>(S, tmem, phase);
             o[k++] = run_l1<64, 1, 1>(S, tmem, phase);
+            o[k++] = run_commit_latency<1>(S, tmem, phase);
+            o[k++] = run_commit_latency<4>(S, tmem, phase);
+            o[k++] = run_commit_latency<24>(S, tmem, phase);
         }
     }
     tc_fence_before();
@@ -258,13 +339,14 @@ int main(int argc, char** argv) {
     cudaMalloc(&out, 148 * 32 * sizeof(long long));
     cudaMemset(out, 0, 148 * 32 * sizeof(long long));
     cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem) + 1024);
-    const char* names[27] = {"TS N=16", "TS N=32", "TS N=64", "TS N=128", "TS N=256", "SS N=16", "SS N=32", "SS N=64", "SS N=128",
+    const char* names[30] = {"TS N=16", "TS N=32", "TS N=64", "TS N=128", "TS N=256", "SS N=16", "SS N=32", "SS N=64", "SS N=128",
                              "SS N=256", "TS N=32 one accumulator", "SS N=32 one accumulator", "TS N=128 one accumulator",
                              "TS N=32 round-robin 1", "TS N=32 round-robin 2", "TS N=32 round-robin 3", "TS N=32 round-robin 4",
                              "TS N=32 round-robin 8", "TS N=64 round-robin 2", "TS N=64 round-robin 4", "TS N=16 round-robin 4",
                              "TS N=16 round-robin 8", "layer-1 pattern N=32 A,B fixed", "layer-1 N=32 A walks", "layer-1 N=32 B walks",
-                             "layer-1 N=32 A and B walk", "layer-1 N=64 A and B walk"};
-    const int nominal[27] = {8, 16, 32, 64, 128, 8, 16, 32, 64, 128, 16, 16, 64, 16, 16, 16, 16, 16, 32, 32, 8, 8, 16, 16, 16, 16, 32};
+                             "layer-1 N=32 A and B walk", "layer-1 N=64 A and B walk",
+                             "1 MMA + commit + wait (total)", "4 MMAs + commit + wait (total)", "24 MMAs + commit + wait (total)"};
+    const int nominal[30] = {8, 16, 32, 64, 128, 8, 16, 32, 64, 128, 16, 16, 64, 16, 16, 16, 16, 16, 32, 32, 8, 8, 16, 16, 16, 16, 32, 16, 64, 384};
     for (int grid : {1}) {
         if (which >= 0) break;
         probe<<<grid, 128, sizeof(PSmem) + 1024>>>(out);
@@ -273,12 +355,18 @@ int main(int argc, char** argv) {
         long long h[32];
         cudaMemcpy(h, out, sizeof(h), cudaMemcpyDeviceToHost);
         printf("grid %d, %d back-to-back MMAs (M=128, K=16, kind::f16), cycles per MMA incl. commit + wake-up / %d:\n", grid, R, R);
-        for (int i = 0; i < 27; ++i) printf("  %-32s %7.1f   (nominal %d)\n", names[i], (double)h[i] / R, nominal[i]);
+        for (int i = 0; i < 30; ++i) printf("  %-32s %7.1f   (nominal %d)\n", names[i], (double)h[i] / R, nominal[i]);
     }
     unsigned char* gimg;
     cudaMalloc(&gimg, 62 * 36864);
     cudaMemset(gimg, 0, 62 * 36864);
     printf("layer-1 protocol (group = 24 MMAs N=32 + 2 commits; 16 KB image per group through a ring):\n");
+    if (which == 7) {
+        for (int tw = 0; tw < 2; ++tw)
+            for (int np : {0, 4, 8, 12}) { run_poll<4>(out, np, tw); }
+        run_poll<24>(out, 0, 0); run_poll<24>(out, 12, 0); run_poll<24>(out, 12, 1);
+        return 0;
+    }
     if (which < 0 || which == 0) run_protocol<3, 0>(out, gimg, "no images");
     if (which == 1) run_protocol<3, 1>(out, gimg, "images stream in the background, never waited for");
     if (which == 2) run_protocol<2, 2>(out, gimg, "full protocol, ring of 2");

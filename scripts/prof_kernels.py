@@ -43,7 +43,7 @@ eng = FederationEngine(cfg, sh, "hybrid", "mse_avg")
 be, st = eng.backend, eng.state
 if a.phase_cycles:
     be.phase_cycles = torch.zeros(16, dtype=torch.int64, device=dev)
-    be.mm_cycles = torch.zeros(96, dtype=torch.int64, device=dev)
+    be.mm_cycles = torch.zeros(2048, dtype=torch.int64, device=dev)
 ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
 for it in range(a.iters):
     ctl = eng.make_control(it)
@@ -82,6 +82,20 @@ for it in range(a.iters):
         tot = cyc[20] or 1
         print("  fused f16 kernel, CTA 0 (k cycles, % of the MMA1 thread's loop): " +
               ", ".join(f"{n} {c / 1e3:.0f}k ({100 * c / tot:.0f}%)" for n, c in zip(names, cyc[:23]) if c))
+        TN, TB = 96, 128
+        if len(cyc) >= TB + 13 * TN and cyc[TB + 40]:
+            import numpy as _np
+            tl = _np.array(cyc[TB:TB + 13 * TN], dtype=_np.int64).reshape(13, TN)
+            names_ev = ["1 issue start", "1 issued", "A sees D1", "h1 ready", "1b woke", "1b issued", "A sees D1b", "h2 ready",
+                        "2 woke", "2 issued", "B woke", "B freed D2", "B done"]
+            q0, q1 = 16, 56                     # steady state, inside the first unit (62 pairs)
+            print(f"  time line, CTA 0, pairs {q0}..{q1 - 1}: period {(tl[0, q1] - tl[0, q0]) / (q1 - q0):.0f} cycles; mean gap to the previous event of the same pair:")
+            for e in range(1, 13):
+                d = tl[e, q0:q1] - tl[e - 1, q0:q1]
+                print(f"    {names_ev[e - 1]:>14} -> {names_ev[e]:<14} {d.mean():7.0f}  (min {d.min()}, max {d.max()})")
+            print(f"    whole chain (1 issue start -> B done): {(tl[12, q0:q1] - tl[0, q0:q1]).mean():.0f} cycles = {(tl[12, q0:q1] - tl[0, q0:q1]).mean() / ((tl[0, q1] - tl[0, q0]) / (q1 - q0)):.2f} pairs in flight")
+            for q in range(24, 28):
+                print("    pair %d: " % q + " ".join("%d" % (tl[e, q] - tl[0, 24]) for e in range(13)))
         for k in range(4):
             w0, w1, p0, p1, e_last, xl = cyc[32 + 8 * k: 38 + 8 * k]
             if w0:

@@ -24,6 +24,15 @@ __device__ __forceinline__ void mma_ts_f16(uint32_t d, uint32_t a, uint64_t bdes
                  ::"r"(d), "r"(a), "l"(bdesc), "r"(idesc), "r"(accum), "r"(0u) : "memory");
 }
 
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+                 "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};\n"
+                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
 struct PSmem {
     alignas(1024) unsigned char b[128 * 128];
     alignas(8) uint64_t bar;
@@ -56,9 +65,22 @@ __global__ void __launch_bounds__(320, 1) probe(long long* out, int mode, int n_
             constexpr uint32_t idesc = idesc_f16(128, N);
             const uint64_t db = smem_desc_sw128(S.b);
             const long long t0 = clock64();
+            if (mode & 8) {               // the kernel's layer-1 pattern: A walks over 2 x 64 columns (x hi | x lo), 3 MMAs per k-step
+                for (int g = 0; g < R_MMA / 24; ++g) {
+                    const uint32_t d = tmem + (uint32_t)((g & 1) ? 128 : 0);
+#pragma unroll
+                    for (int kk = 0; kk < 8; ++kk) {
+                        const uint64_t bh = db + (uint64_t)(((kk & 3) * 32) >> 4);
+                        mma_ts_f16(d, tmem + 384 + kk * 8, bh, idesc, 1u);
+                        mma_ts_f16(d, tmem + 384 + kk * 8, bh, idesc, 1u);
+                        mma_ts_f16(d, tmem + 448 + kk * 8, bh, idesc, 1u);
+                    }
+                }
+            } else {
 #pragma unroll 8
-            for (int i = 0; i < R_MMA; ++i)
-                mma_ts_f16(tmem + (uint32_t)((i & 8) ? 128 : 0), tmem + 480, db + (uint64_t)(((i & 3) * 32) >> 4), idesc, 1u);
+                for (int i = 0; i < R_MMA; ++i)
+                    mma_ts_f16(tmem + (uint32_t)((i & 8) ? 128 : 0), tmem + 480, db + (uint64_t)(((i & 3) * 32) >> 4), idesc, 1u);
+            }
             tc_commit(&S.bar);
             mbar_wait(&S.bar, 0);
             out[0] = clock64() - t0;
@@ -70,9 +92,21 @@ __global__ void __launch_bounds__(320, 1) probe(long long* out, int mode, int n_
         uint32_t v[32], x = 0;
         const long long t0 = clock64();
         for (int i = 0; i < R_LD; ++i) {
-            tmem_ld32(base + (uint32_t)((i & 1) * 32), v);
+            if (mode & 16) {              // the kernel's ReLU hop: load 32 columns, convert, store 16 columns in place, wait, fence
+                tc_fence_after();
+                tmem_ld32(base + (uint32_t)((i & 1) * 32), v);
+                uint32_t hi[16];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) x ^= v[j];
+                for (int j = 0; j < 16; ++j) hi[j] = v[2 * j] ^ (v[2 * j + 1] >> 1);
+                tmem_st16(base + (uint32_t)((i & 1) * 32), hi);
+                tmem_st_wait();
+                tc_fence_before();
+                x ^= hi[3];
+            } else {
+                tmem_ld32(base + (uint32_t)((i & 1) * 32), v);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) x ^= v[j];
+            }
         }
         const long long t1 = clock64();
         if (x == 0xdeadbeefu) S.stop = 1;
@@ -93,7 +127,7 @@ void run(long long* out, int mode, int n_ld, const char* what) {
     long long h[16];
     cudaMemcpy(h, out, sizeof(h), cudaMemcpyDeviceToHost);
     printf("  %-64s", what);
-    if (mode & 2) printf(" MMA N=%-3d %6.1f cycles each (nominal %d)", N, (double)h[0] / R_MMA, N / 2);
+    if (mode & 2) printf(" MMA N=%-3d %6.1f cycles each (nominal %d)", N, (double)h[0] / ((mode & 8) ? (R_MMA / 24) * 24 : R_MMA), N / 2);
     if (mode & 1) {
         long long mx = 0;
         for (int w = 0; w < n_ld; ++w) mx = h[1 + w] > mx ? h[1 + w] : mx;
@@ -116,5 +150,14 @@ int main() {
     run<32>(out, 3, 4, "N = 32 MMAs + 4 load warps");
     run<32>(out, 3, 8, "N = 32 MMAs + 8 load warps");
     run<32>(out, 7, 8, "N = 32 MMAs + 8 load warps reading OTHER columns");
+    run<32>(out, 2 | 8, 4, "N = 32 MMAs, A walking over 128 columns (layer-1 pattern), alone");
+    run<32>(out, 1 | 2 | 4 | 8, 4, "  the same + 4 load warps (other columns)");
+    run<32>(out, 1 | 2 | 4 | 8, 8, "  the same + 8 load warps (other columns)");
+    run<32>(out, 1 | 4 | 16, 4, "ReLU hops only (ld x32 + st x16 + wait + fences), 4 warps");
+    run<32>(out, 1 | 2 | 4 | 8 | 16, 4, "N = 32 layer-1 MMAs + 4 warps doing ReLU hops (other columns)");
+    run<32>(out, 1 | 2 | 8 | 16, 4, "N = 32 layer-1 MMAs + 4 warps doing ReLU hops IN the accumulator columns");
+    run<32>(out, 1 | 2 | 4 | 8 | 16, 8, "N = 32 layer-1 MMAs + 8 warps doing ReLU hops (other columns)");
+    run<64>(out, 1 | 2 | 4 | 8, 8, "N = 64, A walking + 8 load warps");
+    run<128>(out, 1 | 2 | 4 | 8, 8, "N = 128, A walking + 8 load warps");
     return 0;
 }
