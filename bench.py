@@ -257,6 +257,11 @@ def run_ours(args):
     t0 = time.time()
     if args.check:
         return run_check(args, comm, n_global, first, cnt)
+    if dev.type != "cuda":
+        if comm.rank == 0:
+            print(json.dumps({"impl": "ours", "unavailable": "bench.py times on the device with CUDA events and there is no GPU "
+                              "here; the CPU path is `bench.py --check --backend oracle`"}))
+        return
     eng, sh, pin_train, pin_valid = build_engine(args, comm, n_global, first, cnt)
     setup_s = time.time() - t0
     result_bytes = 8 * cnt + 4 * cnt * 2 + 8   # AUC (f64) + epochs_run + rejected (i32) + aggregator
@@ -268,7 +273,7 @@ def run_ours(args):
 
     def timed(n_rounds, r0, with_h2d):
         """Returns (device ms over n_rounds [max over ranks], wall s, samples, launches)."""
-        launches0 = eng.backend.launches
+        launches0 = getattr(eng.backend, "launches", 0)
         samples = 0
         sync_all()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -295,7 +300,7 @@ def run_ours(args):
         ms = torch.tensor([e0.elapsed_time(e1), wall * 1e3, float(samples)], dtype=torch.float64, device=dev)
         mx = comm.max_(ms.clone())
         tot = comm.sum_(ms.clone())
-        return float(mx[0]), float(mx[1]) / 1e3, int(tot[2]), eng.backend.launches - launches0, res
+        return float(mx[0]), float(mx[1]) / 1e3, int(tot[2]), getattr(eng.backend, "launches", 0) - launches0, res
 
     timed(args.warmup, 0, False)
     eng.timer.reset()               # phase means below are steady state (first-use costs stay in the warm-up)
@@ -322,9 +327,9 @@ def run_ours(args):
                                 "on mma.sync, scoring forwards on tcgen05; GPU tests hold scores to 2e-4 and trained "
                                 "parameters to 2e-3 relative of the fp32 oracle)",
                       "fp16x3": "fp32 (parameters, Adam, accumulation in fp32; training GEMMs error-compensated 3xTF32 on "
-                                "mma.sync; MSE-weight scoring on tcgen05 kind::f16 with fp16 head+remainder operands, three "
-                                "products per GEMM; other scoring forwards 3xTF32 on tcgen05; GPU tests hold the MSE to 1e-4 "
-                                "relative of the fp32 oracle)"}[args.score_precision],
+                                "mma.sync; MSE-weight scoring on tcgen05 kind::f16: x and weights as fp16 head+remainder, "
+                                "activations as one fp16, fp32 accumulation in TMEM, measured 1e-7 relative on the MSE against "
+                                "the fp64 oracle (the GPU test allows 1e-4); other scoring forwards 3xTF32 on tcgen05)"}[args.score_precision],
             "data": "synthetic", "impl": "ours",
             "rounds_per_sec": args.steps / (ms / 1e3),
             "config": {"model": f"SAE-CEN 115-27-7 ({args.model}) + {args.update}",
