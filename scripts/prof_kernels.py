@@ -27,6 +27,7 @@ ap.add_argument("--score-precision", default="fp32")
 ap.add_argument("--phase-cycles", action="store_true")
 ap.add_argument("--aggregation", default="elected", choices=["elected", "gossip"])
 ap.add_argument("--participation", type=float, default=0.5)
+ap.add_argument("--dev-scale", type=float, default=None, help="multiply the dev matrix (timing experiments: 0 = all zeros, 1024 = fp16 remainders out of the subnormal range)")
 ap.add_argument("--dev-rows-mult", type=int, default=1,
                 help="repeat the pooled dev matrix: 8 reproduces on one GPU the per-GPU scoring work of an 8-GPU run")
 a = ap.parse_args()
@@ -35,6 +36,8 @@ random.seed(0); np.random.seed(0); torch.manual_seed(0)
 clients, devset = prepare_from_raw(make_clients(a.clients, NBAIOT_SPEC, seed=1234), True, seed=1)
 if a.dev_rows_mult > 1:
     devset = np.tile(devset, (a.dev_rows_mult, 1))
+if a.dev_scale is not None:
+    devset = (devset * a.dev_scale).astype(devset.dtype)
 sh = ShardStore.build(clients, devset).to(dev)
 cfg = ExperimentConfig(epoch=a.epochs, network_size=a.clients, backend="cuda", write_latents=False,
                        save_client_models=False, local_patience=a.patience, score_precision=a.score_precision,
