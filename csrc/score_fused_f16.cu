@@ -53,6 +53,12 @@ constexpr int C_X = 0, C_XLO = 64, C_D1 = 128, C_D1B = C_D1 + 32 * NB, C_D2 = 25
 // W32 and W4 (K = 32): 64-B swizzle, one 64-byte row per output feature -- no padding travels.  The images are what
 // every SM pulls from L2 for every (tile, model) pair, and at ~42 B / clk / SM of L2 bandwidth the 56 KB of the first
 // layout (128-B rows everywhere, K padded to 64) cost 1.35 k cycles per pair, more than the 0.93 k of tensor work.
+// ONE commit per group of MMAs: "layer 1 / bottleneck / output GEMM of pair q has retired" completes bar_m1 / bar_m1b /
+// bar_m2[q % RB], and every consumer of that event waits on it with parity (q / RB) & 1 -- the epilogue warps (accumulator
+// ready), the loader (image stage free) and the upstream MMA thread (accumulator slot free).  A commit costs its thread
+// ~50-100 cycles, and the bottleneck / output threads used to issue three each for four MMAs.  RB is a multiple of both
+// ring depths; no consumer can fall RB pairs behind its producer (each of them gates a ring of depth <= 3).
+constexpr int RB = 6;
 constexpr int NW = 3;                       // shared-memory stages per image kind
 constexpr int W1_BYTES = 2 * 4096;          // [32 n][128 k]  = two K-blocks of 32 rows x 128 B
 constexpr int W32_BYTES = 32 * 64;          // [32 n][32 k]
@@ -73,8 +79,8 @@ struct FSmem {
     alignas(1024) unsigned char w1[NW][2 * W1_BYTES];        // hi | lo
     alignas(1024) unsigned char w32[NW][2 * W32_BYTES];
     alignas(1024) unsigned char w4[NW][2 * W4_BYTES];
-    alignas(8) uint64_t bar_x, bar_xfree, bar_xt, bar_w1[NW], bar_w32[NW], bar_w4[NW], bar_w1free[NW], bar_w32free[NW], bar_w4free[NW], bar_d1[NB], bar_h1[NB], bar_d1b[NB], bar_d1free[NB], bar_d1bfree[NB],
-        bar_h2[NB], bar_d2[2], bar_d2free[2];
+    alignas(8) uint64_t bar_x, bar_xfree, bar_xt, bar_w1[NW], bar_w32[NW], bar_w4[NW], bar_m1[RB], bar_m1b[RB], bar_m2[RB], bar_h1[NB],
+        bar_h2[NB], bar_d2free[2];
     uint32_t tmem_base;
     double red[16];
 };
@@ -239,12 +245,11 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         mbar_init(&S.bar_x, 1); mbar_init(&S.bar_xfree, 384); mbar_init(&S.bar_xt, 128);
         for (int b = 0; b < NW; ++b) {
             mbar_init(&S.bar_w1[b], 1); mbar_init(&S.bar_w32[b], 1); mbar_init(&S.bar_w4[b], 1);
-            mbar_init(&S.bar_w1free[b], 1); mbar_init(&S.bar_w32free[b], 1); mbar_init(&S.bar_w4free[b], 1);
         }
-        for (int b = 0; b < 2; ++b) { mbar_init(&S.bar_d2[b], 1); mbar_init(&S.bar_d2free[b], 256); }
+        for (int b = 0; b < 2; ++b) mbar_init(&S.bar_d2free[b], 256);
+        for (int b = 0; b < RB; ++b) { mbar_init(&S.bar_m1[b], 1); mbar_init(&S.bar_m1b[b], 1); mbar_init(&S.bar_m2[b], 1); }
         for (int b = 0; b < NB; ++b) {
-            mbar_init(&S.bar_d1[b], 1); mbar_init(&S.bar_d1b[b], 1); mbar_init(&S.bar_h1[b], 128); mbar_init(&S.bar_h2[b], 128);
-            mbar_init(&S.bar_d1free[b], 1); mbar_init(&S.bar_d1bfree[b], 1);
+            mbar_init(&S.bar_h1[b], 128); mbar_init(&S.bar_h2[b], 128);
         }
         fence_mbar_init();
     }
@@ -269,8 +274,8 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         // producer does bookkeeping, so period = math + issue overhead, whatever the buffering.  With one issuer per
         // stage the bookkeeping of one overlaps the MMAs of the others.  Each thread walks the pairs in order with
         // blocking waits; every cross-thread hazard is covered by a commit barrier ("these MMAs have RETIRED"):
-        //   MMA1(q)  overwrites D1[q&1]   -> waits bar_d1free  (MMA1b(q-2) retired, committed by the MMA1b thread)
-        //   MMA1b(q) overwrites D1b[q&1]  -> waits bar_d1bfree (MMA2(q-2) retired, committed by the MMA2 thread)
+        //   MMA1(q)  overwrites D1[q&1]   -> waits bar_m1b of pair q-2 (MMA1b(q-2) retired)
+        //   MMA1b(q) overwrites D1b[q&1]  -> waits bar_m2 of pair q-2  (MMA2(q-2) retired)
         //   MMA2(q)  overwrites D2[q&1]   -> waits bar_d2free  (epilogue 2 of pair q-2 has read it)
         // No thread ever waits for something that needs its own later work, so units of any length are safe.
         if (elect_one()) {
@@ -297,7 +302,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     FT(TK_1_XT);
                     mbar_wait(&S.bar_w1[s], sph);
                     FT(TK_1_W);
-                    if (q >= NB) mbar_wait(&S.bar_d1free[r], (uint32_t)(((q - NB) >> 1) & 1));
+                    if (q >= NB) mbar_wait(&S.bar_m1b[(q - NB) % RB], (uint32_t)(((q - NB) / RB) & 1));
                     FT(TK_1_FREE);
                     if (TIMING && tk_on && (q) < TRACE_N) dbg[TRACE_BASE + 0 * TRACE_N + (q)] = (unsigned long long)clock64();
                     tc_fence_after();
@@ -311,8 +316,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                         mma_ts_f16(d1, xh + kk * 8, bl, IDESC_N32, 1u);
                         mma_ts_f16(d1, xl + kk * 8, bh, IDESC_N32, 1u);
                     }
-                    tc_commit(&S.bar_d1[r]);
-                    tc_commit(&S.bar_w1free[s]);
+                    tc_commit(&S.bar_m1[q % RB]);
                     next_pair(c1);
                     if (++s == NW) { s = 0; sph ^= 1u; }
                     FT(TK_1_ISSUE);
@@ -328,7 +332,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     if (TIMING && tk_on && (q) < TRACE_N) dbg[TRACE_BASE + 4 * TRACE_N + (q)] = (unsigned long long)clock64();
                     mbar_wait(&S.bar_w32[s], sph);
                     FT(TK_1B_W);
-                    if (q >= NB) mbar_wait(&S.bar_d1bfree[r], (uint32_t)(((q - NB) >> 1) & 1));
+                    if (q >= NB) mbar_wait(&S.bar_m2[(q - NB) % RB], (uint32_t)(((q - NB) / RB) & 1));
                     FT(TK_1B_FREE);
                     tc_fence_after();
                     const uint32_t d = tmem + C_D1B + 32 * r, ah = tmem + C_D1 + 32 * r;
@@ -339,9 +343,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                         mma_ts_f16(d, ah + ks * 8, bh, IDESC_N32, ks ? 1u : 0u);
                         mma_ts_f16(d, ah + ks * 8, bl, IDESC_N32, 1u);
                     }
-                    tc_commit(&S.bar_d1b[r]);
-                    tc_commit(&S.bar_w32free[s]);
-                    tc_commit(&S.bar_d1free[r]);
+                    tc_commit(&S.bar_m1b[q % RB]);
                     if (++s == NW) { s = 0; sph ^= 1u; }
                     FT(TK_1B_ISSUE);
                     if (TIMING && tk_on && (q) < TRACE_N) dbg[TRACE_BASE + 5 * TRACE_N + (q)] = (unsigned long long)clock64();
@@ -366,9 +368,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                         mma_ts_f16(d, ah + ks * 8, bh, IDESC_N128, ks ? 1u : 0u);
                         mma_ts_f16(d, ah + ks * 8, bl, IDESC_N128, 1u);
                     }
-                    tc_commit(&S.bar_d2[r]);
-                    tc_commit(&S.bar_w4free[s]);
-                    tc_commit(&S.bar_d1bfree[r]);
+                    tc_commit(&S.bar_m2[q % RB]);
                     if (++s == NW) { s = 0; sph ^= 1u; }
                     FT(TK_2_ISSUE);
                     if (TIMING && tk_on && (q) < TRACE_N) dbg[TRACE_BASE + 9 * TRACE_N + (q)] = (unsigned long long)clock64();
@@ -400,13 +400,13 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                     if (TIMING && blockIdx.x == 0 && lx >= 1 && lx <= 4) dbg[37 + 8 * (lx - 1)] = (unsigned long long)clock64();
                     next_unit(cx); ++lx;
                 }
-                if (l1 < n_pairs && (l1 < NW || mbar_test(&S.bar_w1free[l1 % NW], (uint32_t)((l1 / NW - 1) & 1)))) {
+                if (l1 < n_pairs && (l1 < NW || mbar_test(&S.bar_m1[(l1 - NW) % RB], (uint32_t)(((l1 - NW) / RB) & 1)))) {
                     load_img(S.w1[l1 % NW], cw1.m, IMG_W1, 2 * W1_BYTES, &S.bar_w1[l1 % NW]); next_pair(cw1); ++l1;
                 }
-                if (l32 < n_pairs && (l32 < NW || mbar_test(&S.bar_w32free[l32 % NW], (uint32_t)((l32 / NW - 1) & 1)))) {
+                if (l32 < n_pairs && (l32 < NW || mbar_test(&S.bar_m1b[(l32 - NW) % RB], (uint32_t)(((l32 - NW) / RB) & 1)))) {
                     load_img(S.w32[l32 % NW], cw32.m, IMG_W32, 2 * W32_BYTES, &S.bar_w32[l32 % NW]); next_pair(cw32); ++l32;
                 }
-                if (l4 < n_pairs && (l4 < NW || mbar_test(&S.bar_w4free[l4 % NW], (uint32_t)((l4 / NW - 1) & 1)))) {
+                if (l4 < n_pairs && (l4 < NW || mbar_test(&S.bar_m2[(l4 - NW) % RB], (uint32_t)(((l4 - NW) / RB) & 1)))) {
                     load_img(S.w4[l4 % NW], cw4.m, IMG_W4, 2 * W4_BYTES, &S.bar_w4[l4 % NW]); next_pair(cw4); ++l4;
                 }
             }
@@ -438,7 +438,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             mbar_arrive(&S.bar_xt);
             mbar_arrive(&S.bar_xfree);
         };
-        auto relu_split = [&](uint32_t col, uint64_t* bar_in, uint64_t* bar_out, uint32_t ph) {
+        auto relu_split = [&](uint32_t col, uint64_t* bar_in, uint32_t ph, uint64_t* bar_out) {
             mbar_wait(bar_in, ph);
             tc_fence_after();
             tmem_ld32(lane_base + col, v);
@@ -452,8 +452,8 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
             tc_fence_before();
             mbar_arrive(bar_out);
         };
-        auto e1 = [&](int q) { const int rb = q & (NB - 1); relu_split(C_D1 + 32 * rb, &S.bar_d1[rb], &S.bar_h1[rb], (uint32_t)((q / NB) & 1)); };
-        auto e1b = [&](int q) { const int rb = q & (NB - 1); relu_split(C_D1B + 32 * rb, &S.bar_d1b[rb], &S.bar_h2[rb], (uint32_t)((q / NB) & 1)); };
+        auto e1 = [&](int q) { const int rb = q & (NB - 1); relu_split(C_D1 + 32 * rb, &S.bar_m1[q % RB], (uint32_t)((q / RB) & 1), &S.bar_h1[rb]); };
+        auto e1b = [&](int q) { const int rb = q & (NB - 1); relu_split(C_D1B + 32 * rb, &S.bar_m1b[q % RB], (uint32_t)((q / RB) & 1), &S.bar_h2[rb]); };
         int n_pairs = 0, n_units_ne = 0;
         { PairCursor t = first_pair(); while (t.ok) { ++n_pairs; n_units_ne = t.ord + 1; next_pair(t); } }
         // Three kinds of work, each taken in order as soon as its input is there (warp-uniform non-blocking tests):
@@ -481,7 +481,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                 did = true;
                 FT(TK_A_PARK);
             }
-            if (qe1 < n_pairs && uniform(mbar_test(&S.bar_d1[qe1 & (NB - 1)], (uint32_t)((qe1 / NB) & 1)))) {
+            if (qe1 < n_pairs && uniform(mbar_test(&S.bar_m1[qe1 % RB], (uint32_t)((qe1 / RB) & 1)))) {
                 if (TIMING && tk_on && (qe1) < TRACE_N) dbg[TRACE_BASE + 2 * TRACE_N + (qe1)] = (unsigned long long)clock64();
                 e1(qe1);
                 { const int o0 = ce1.ord; next_pair(ce1);
@@ -491,7 +491,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                 FT(TK_A_E1);
                 if (TIMING && tk_on && (qe1 - 1) < TRACE_N) dbg[TRACE_BASE + 3 * TRACE_N + (qe1 - 1)] = (unsigned long long)clock64();
             }
-            if (qe1b < qe1 && uniform(mbar_test(&S.bar_d1b[qe1b & (NB - 1)], (uint32_t)((qe1b / NB) & 1)))) {
+            if (qe1b < qe1 && uniform(mbar_test(&S.bar_m1b[qe1b % RB], (uint32_t)((qe1b / RB) & 1)))) {
                 if (TIMING && tk_on && (qe1b) < TRACE_N) dbg[TRACE_BASE + 6 * TRACE_N + (qe1b)] = (unsigned long long)clock64();
                 e1b(qe1b);
                 ++qe1b;
@@ -537,7 +537,7 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
                 FT(TK_B_ENTRY);
             }
             const int b = g & 1;
-            mbar_wait(&S.bar_d2[b], (uint32_t)((g >> 1) & 1));
+            mbar_wait(&S.bar_m2[g % RB], (uint32_t)((g / RB) & 1));
             tc_fence_after();
             FT(TK_B_WAIT);
             if (TIMING && tk_on && (g) < TRACE_N) dbg[TRACE_BASE + 10 * TRACE_N + (g)] = (unsigned long long)clock64();
