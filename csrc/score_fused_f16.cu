@@ -379,9 +379,9 @@ score_fused_f16_kernel(const __grid_constant__ CUtensorMap xmap, const unsigned 
         __syncwarp();
     } else if (warp == LOAD_WARP) {
         // One thread feeds the shared memory: weight images NW pairs ahead (image l of a kind goes into stage l % NW
-        // once the MMAs that read image l - NW have retired -- the issuing thread commits a "stage free" barrier behind
-        // them, and its next completion needs the image requested right after the test succeeded, so no phase can be
-        // missed) and the fp32 tile of the next unit (once the parking warps and the squared-error warps both have
+        // once the MMAs that read image l - NW have retired: the group's completion barrier bar_m*[(l - NW) % RB]; the
+        // same slot's next completion, RB pairs later, needs images this thread requests only after the test succeeded,
+        // so no phase can be missed) and the fp32 tile of the next unit (once the parking warps and the squared-error warps both have
         // their copy of the current one).  Everything is polled, so no kind of load can hold back another.
         if (elect_one()) {
             int n_pairs = 0, n_units_ne = 0;
