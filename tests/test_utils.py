@@ -81,3 +81,18 @@ def test_random_k_hash_matches_the_device_function():
     nb = topology.random_k(50, 4, seed=1, round_idx=2)
     assert all(len(set(r)) == 4 and i not in r for i, r in enumerate(nb))
     assert nb != topology.random_k(50, 4, seed=1, round_idx=3)
+
+
+def test_numa_binding_is_best_effort():
+    """No GPU / no NVML here: the per-rank CPU binding must decline quietly and leave the affinity alone."""
+    import os
+    from fedmse_decentralized_b200.parallel.world import bind_to_gpu_numa
+    before = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else None
+    assert bind_to_gpu_numa(0) is None or isinstance(bind_to_gpu_numa(0), int)
+    os.environ["FEDMSE_NO_NUMA_BIND"] = "1"
+    try:
+        assert bind_to_gpu_numa(0) is None
+    finally:
+        del os.environ["FEDMSE_NO_NUMA_BIND"]
+    if before is not None:
+        assert os.sched_getaffinity(0) <= before
