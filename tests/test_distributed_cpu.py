@@ -23,8 +23,9 @@ sh, names = build_shards(clients, dev, comm, torch.device("cpu"))
 random.seed(1); np.random.seed(1); torch.manual_seed(1)
 cfg = ExperimentConfig(epoch=1, num_rounds=2, network_size=5, backend="oracle", output_root=os.environ["FM_OUT"],
                        aggregation=os.environ.get("FM_AGG", "elected"), topology="ring", num_participants=0.8,
-                       write_latents=True, save_client_models=False)
-eng = FederationEngine(cfg, sh, "hybrid", "mse_avg", comm=comm, names_global=names)
+                       write_latents=True, save_client_models=False, fusion_rows=48,
+                       update_types=[os.environ.get("FM_UPD", "mse_avg")])
+eng = FederationEngine(cfg, sh, "hybrid", os.environ.get("FM_UPD", "mse_avg"), comm=comm, names_global=names)
 out = [eng.run_round(r) for r in range(2)]
 if comm.rank == 0:
     print("RESULT " + json.dumps({"metrics": [r.client_metrics for r in out], "agg": [r.aggregator for r in out],
@@ -34,8 +35,8 @@ shutdown()
 '''
 
 
-def _run(world, tmp_path, agg):
-    env = dict(os.environ, FM_ROOT=ROOT, FM_OUT=str(tmp_path), FM_AGG=agg, MASTER_ADDR="127.0.0.1")
+def _run(world, tmp_path, agg, upd="mse_avg"):
+    env = dict(os.environ, FM_ROOT=ROOT, FM_OUT=str(tmp_path), FM_AGG=agg, FM_UPD=upd, MASTER_ADDR="127.0.0.1")
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
     if world == 1:
@@ -49,10 +50,10 @@ def _run(world, tmp_path, agg):
     return json.loads(line[7:])
 
 
-@pytest.mark.parametrize("agg", ["elected", "gossip"])
-def test_two_ranks_match_one(tmp_path, agg):
-    one = _run(1, tmp_path, agg)
-    two = _run(2, tmp_path, agg)
+@pytest.mark.parametrize("agg,upd", [("elected", "mse_avg"), ("gossip", "mse_avg"), ("elected", "fusion_avg")])
+def test_two_ranks_match_one(tmp_path, agg, upd):
+    one = _run(1, tmp_path, agg, upd)
+    two = _run(2, tmp_path, agg, upd)
     assert one["agg"] == two["agg"] and one["ver"] == two["ver"] and one["lat"] == two["lat"]
     for a, b in zip(one["metrics"], two["metrics"]):
         assert len(a) == 5 and max(abs(x - y) for x, y in zip(a, b)) < 1e-9
