@@ -30,7 +30,8 @@ random.seed(1); np.random.seed(1); torch.manual_seed(1)
 cfg = ExperimentConfig(epoch=2, num_rounds=n_rounds, network_size=n_clients, backend="cuda", output_root=E["FM_OUT"],
                        aggregation=E.get("FM_AGG", "elected"), topology=E.get("FM_TOPO", "ring"), topology_k=3,
                        num_participants=float(E.get("FM_PART", "0.7")), score_precision=E.get("FM_PREC", "fp32"),
-                       write_latents=False, save_client_models=False)
+                       write_latents=False, save_client_models=False, fusion_rows=96,
+                       update_types=[E.get("FM_UPD", "mse_avg")])
 eng = FederationEngine(cfg, sh, "hybrid", E.get("FM_UPD", "mse_avg"), comm=comm, names_global=names)
 out = []
 if pipe:      # the bench's loop: pipelined rounds with fresh local rows staged from pinned host memory every round
@@ -93,6 +94,13 @@ def _same(one, many, n_clients, auc_tol=1e-6):
 def test_n_gpus_match_one_gpu(tmp_path, agg, upd):
     world = _world()
     _same(_run(1, tmp_path, agg, upd), _run(world, tmp_path, agg, upd), 9)
+
+
+def test_n_gpus_match_one_gpu_fusion_avg(tmp_path):
+    """fusion_avg: every rank computes the JS distances of the models it owns (csrc/similarity_kernel.cu), the distances
+    travel over the same peer-mapped board as the MSE scores, and the merge must not depend on the partition."""
+    world = _world()
+    _same(_run(1, tmp_path, "elected", "fusion_avg"), _run(world, tmp_path, "elected", "fusion_avg"), 9, auc_tol=1e-5)
 
 
 def test_n_gpus_match_one_gpu_gossip_random_k(tmp_path):
