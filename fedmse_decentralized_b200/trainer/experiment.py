@@ -50,6 +50,9 @@ def prepare_data(cfg: ExperimentConfig):
     if cfg.synthetic_clients > 0:
         spec = KITSUNE_SPEC if cfg.synthetic_spec == "kitsune" else NBAIOT_SPEC
         raw = make_clients(cfg.synthetic_clients, spec, seed=cfg.data_seed)
+        if cfg.network_size > len(raw):
+            raise ValueError(f"--network_size {cfg.network_size} exceeds --synthetic_clients {cfg.synthetic_clients}: the "
+                             "experiment samples network_size devices from the scenario (src/main.py:126-129)")
         raw = random.sample(raw, cfg.network_size)
         return prepare_from_raw(raw, cfg.new_device)
     scen = load_scenario(cfg.config_file)
