@@ -220,7 +220,6 @@ __global__ void __launch_bounds__(GNT) train_generic_kernel(const FmTrainGeneric
 constexpr int GT = 16;
 __global__ void __launch_bounds__(GNT) score_generic_kernel(const FmScoreGenericArgs a) {
     extern __shared__ __align__(16) float gsm[];
-    __shared__ double red[34];
     const Lay L = make_lay(a.dim, a.hidden, a.latent);
     const int* tl = a.tiles + 4 * (size_t)blockIdx.x;
     const int slot = tl[0], row0 = tl[1], nrows = tl[2], out0 = tl[3];
@@ -258,7 +257,6 @@ __global__ void __launch_bounds__(GNT) score_generic_kernel(const FmScoreGeneric
         s = warp_sum(s);
         if (lane == 0) a.out_sse[out0 + b] = s;
     }
-    (void)red;
 }
 
 }  // namespace gen
