@@ -118,3 +118,54 @@ def test_evaluator_metrics_and_time(tiny_clients):
         f1 = f1[0] if isinstance(f1, tuple) else f1
         assert 0.0 <= f1 <= 1.0
         assert compat.Evaluator(m, mt, "time").evaluate(te, tl) >= 0.0
+
+
+def test_global_aggregator_central_server_rules(tiny_clients, tmp_path):
+    """The central-server surface the fork deleted (names from its leftover bytecode): four merge rules + update()."""
+    from fedmse_decentralized_b200.ops import oracle
+    from fedmse_decentralized_b200.utils.similarity import fusion_distances
+    logging.disable(logging.CRITICAL)
+    clients, dev = tiny_clients
+    trainers, loaders = _federation(compat, tiny_clients, tmp_path, "avg", "cpu")
+    for t, (tl, vl, _) in zip(trainers[:3], loaders[:3]):
+        t.run(tl, vl)
+    rows = torch.stack([t.params for t in trainers[:3]])
+    local = [(t.state_dict(), n) for t, n in zip(trainers[:3], (10.0, 30.0, 60.0))]
+    mk = lambda rule: compat.GlobalAggregator(model=compat.Shrink_Autoencoder(input_dim=115, output_dim=115, shrink_lambda=5),
+                                              update_type=rule, device="cpu", fusion_rows=64)
+    # FedAvg / FedProx: sample-count weights
+    g = mk("avg")
+    want = 0.1 * rows[0] + 0.3 * rows[1] + 0.6 * rows[2]
+    assert_close(L.pack(g.fed_avg(local)), want, 1e-6, 1e-7, "fed_avg")
+    assert_close(L.pack(mk("fedprox").fedprox(local)), want, 1e-6, 1e-7, "fedprox")
+    # MSEAvg: the same state as the decentralized trainer's own fed_mse_avg
+    g = mk("mse_avg")
+    with pytest.raises(RuntimeError):
+        g.fed_mse_avg(local)
+    g.create_dev_dataset({"dataset": dev})
+    assert_close(L.pack(g.fed_mse_avg(local)), L.pack(trainers[0].fed_mse_avg(local)), 1e-6, 1e-7, "fed_mse_avg")
+    assert abs(float(g.last_weights.sum()) - 1) < 1e-6
+    # fusion_avg: inverse Jensen-Shannon distance weights
+    g = mk("fusion_avg")
+    g.create_dev_dataset(dev)
+    merged = g.fusion_avg(local)
+    from fedmse_decentralized_b200.trainer.model_verifier import _pad
+    d = fusion_distances(rows, _pad(torch.as_tensor(dev, dtype=torch.float32)), L, 64)
+    w = (1 / d) / (1 / d).sum()
+    assert_close(g.last_weights, w, 1e-5, 1e-7, "fusion weights")
+    assert_close(L.pack(merged), oracle.weighted_reduce(rows, range(3), w), 1e-6, 1e-7, "fusion_avg")
+    # update(): merged model becomes the global model and lands in every receiver
+    out = g.update(trainers[:3], receivers=trainers)
+    assert_close(g.params, L.pack(out), 0, 0, "global model")
+    for t in trainers:
+        assert_close(t.params, g.params, 0, 0, "client got the global model")
+        assert_close(t.anchor, g.params, 0, 0, "FedProx anchor follows")
+    # election helper: lowest validation MSE under quota
+    torch.manual_seed(3)
+    pick = g.select_aggregator(trainers, torch.Tensor(clients[0].valid), 1)
+    assert pick in trainers
+    for t in trainers:
+        t.aggregation_count = t.max_aggregation_threshold
+    assert g.select_aggregator(trainers, torch.Tensor(clients[0].valid), 2) is None
+    with pytest.raises(ValueError):
+        compat.GlobalAggregator(model=trainers[0].model, update_type="nope")
