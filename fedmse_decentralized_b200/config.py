@@ -64,6 +64,8 @@ class ExperimentConfig:
     synthetic_spec: str = "nbaiot"        # "nbaiot" | "kitsune"
     score_precision: str = "fp32"         # "fp32" (exact FFMA) | "tf32" | "tf32x3" | "bf16x3" (tcgen05 scoring forwards)
     fusion_rows: int = 512                # fusion_avg: dev rows used for the KDE / JS-distance weights
+    checkpoint_every: int = 0             # write a resumable engine checkpoint every K rounds (0 = never; not in the reference)
+    resume: bool = False                  # continue every (model, update, run) combination from its last checkpoint
     log_level: str = "INFO"
 
     def __post_init__(self):

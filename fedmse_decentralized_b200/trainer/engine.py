@@ -23,6 +23,7 @@ all-to-all API the reference defines but never calls, quirk Q21).
 from __future__ import annotations
 
 import logging
+import os
 import random
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple
@@ -395,7 +396,15 @@ class FederationEngine:
                                           self.update_type)
         ver_file = f"{root}/{cfg.checkpoint_dir}/Run_{self.run}/verification_results.json"
         out = []
-        for r in range(cfg.num_rounds):
+        ckpt = f"{root}/{cfg.checkpoint_dir}/Run_{self.run}/resume_{self.model_type}_{self.update_type}.pt"
+        r0 = 0
+        if cfg.resume and os.path.exists(ckpt if self.comm.world == 1 else f"{ckpt}.rank{self.comm.rank}"):
+            r0 = self.load_checkpoint(ckpt)
+            stop.min_val_loss, stop.worse = self.checkpoint_extra.get("stop", (stop.min_val_loss, stop.worse))
+            log.info("Resumed %s + %s run %d at round %d from %s", self.model_type, self.update_type, self.run, r0 + 1, ckpt)
+            if self.checkpoint_extra.get("stopped"):
+                r0 = cfg.num_rounds                      # this combination had already stopped early
+        for r in range(r0, cfg.num_rounds):
             log.info("Starting round %d/%d", r + 1, cfg.num_rounds)
             res = self.run_round(r, prefetch_next=r + 1 < cfg.num_rounds)
             out.append(res)
@@ -413,7 +422,10 @@ class FederationEngine:
                         artefacts.append_verification(ver_file, r + 1, res.verification)
                     artefacts.append_round_metrics(res_file, r + 1, res.client_metrics,
                                                    self.update_type, self.model_type)
-            if stop.update(res.client_metrics):
+            stopped = stop.update(res.client_metrics)
+            if cfg.checkpoint_every > 0 and ((r + 1) % cfg.checkpoint_every == 0 or stopped or r + 1 == cfg.num_rounds):
+                self.save_checkpoint(ckpt, extra={"stop": (stop.min_val_loss, stop.worse), "stopped": bool(stopped)})
+            if stopped:
                 log.info("Early stopping in global round!")
                 break
         if write and self.comm.rank == 0 and self.latents:
@@ -527,7 +539,7 @@ class FederationEngine:
             raise RuntimeError("a pipelined round is in flight (run_round(..., pipeline_next=True)); finish it first")
         return {"state": self.state.state_dict(), "agg_count_host": list(self.agg_count_host),
                 "py_random": random.getstate(), "np_random": np.random.get_state(),
-                "torch_random": torch.get_rng_state(), "rounds_done": len(self.history),
+                "torch_random": torch.get_rng_state(), "rounds_done": getattr(self, "_rounds_offset", 0) + len(self.history),
                 "model_type": self.model_type, "update_type": self.update_type, "run": self.run,
                 "rand_fifo": list(self._rand_fifo), "prefetched": self._prefetched}
 
@@ -539,3 +551,37 @@ class FederationEngine:
         torch.set_rng_state(snap["torch_random"])
         self._rand_fifo = list(snap.get("rand_fifo", []))
         self._prefetched = snap.get("prefetched")
+        self._rounds_offset = int(snap.get("rounds_done", 0)) - len(self.history)
+
+    def save_checkpoint(self, path: str, extra: Optional[Dict] = None) -> str:
+        """``snapshot()`` on disk: parameters, Adam state, verifier history, quotas, RNG streams, rounds done.  The
+        reference never reloads anything; ``load_checkpoint`` on an engine built from the same config
+        and data continues the experiment with the rounds it would have run.  On several ranks every rank writes its own
+        file (``path`` + ``.rank<r>``): a rank's state holds only the clients it owns."""
+        snap = self.snapshot()
+        snap["format"] = 1
+        snap["n_clients"] = int(self.state.n_clients)
+        snap["extra"] = dict(extra or {})
+        if self.comm is not None and getattr(self.comm, "world", 1) > 1:
+            path = f"{path}.rank{self.comm.rank}"
+        os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+        tmp = path + ".tmp"
+        torch.save(snap, tmp)
+        os.replace(tmp, path)                      # never leave a half-written checkpoint behind
+        return path
+
+    def load_checkpoint(self, path: str) -> int:
+        """Restore a ``save_checkpoint`` file; returns the index of the next round to run."""
+        if self.comm is not None and getattr(self.comm, "world", 1) > 1:
+            path = f"{path}.rank{self.comm.rank}"
+        snap = torch.load(path, map_location="cpu", weights_only=False)
+        if snap.get("format") != 1:
+            raise ValueError(f"{path}: not a checkpoint of this engine")
+        if (snap["model_type"], snap["update_type"]) != (self.model_type, self.update_type) or \
+                snap["n_clients"] != int(self.state.n_clients):
+            raise ValueError(f"{path}: written for {snap['model_type']} + {snap['update_type']} with {snap['n_clients']} "
+                             f"local clients, this engine is {self.model_type} + {self.update_type} with "
+                             f"{int(self.state.n_clients)}")
+        self.restore(snap)
+        self.checkpoint_extra = dict(snap.get("extra", {}))
+        return int(snap["rounds_done"])

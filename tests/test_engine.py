@@ -233,3 +233,41 @@ def test_fusion_avg_is_a_selectable_merge_rule(tiny_clients, tmp_path):
     eng2 = make_engine(cfg, sh, "hybrid", "fusion_avg")
     r = eng2.run_round(0)
     assert r.aggregator >= 0 and len(r.client_metrics) == 6
+
+
+def test_checkpoint_file_resumes_identically(tiny_clients, tmp_path):
+    """save_checkpoint / load_checkpoint: a fresh engine continues with exactly the rounds the first one would have run."""
+    cfg = make_cfg(tmp_path, epoch=1)
+    a = make_engine(cfg, make_shards(tiny_clients), "hybrid", "mse_avg")
+    a.run_round(0)
+    a.run_round(1)
+    path = a.save_checkpoint(str(tmp_path / "ckpt" / "engine.pt"))
+    assert os.path.exists(path) and not os.path.exists(path + ".tmp")
+    ra = [a.run_round(r) for r in (2, 3)]
+    b = make_engine(cfg, make_shards(tiny_clients), "hybrid", "mse_avg", seed=99)
+    nxt = b.load_checkpoint(path)
+    assert nxt == 2
+    rb = [b.run_round(r) for r in (nxt, nxt + 1)]
+    for x, y in zip(ra, rb):
+        assert (x.selected, x.aggregator, x.client_metrics) == (y.selected, y.aggregator, y.client_metrics)
+    assert torch.equal(a.state.params, b.state.params) and torch.equal(a.state.adam_m, b.state.adam_m)
+    assert b.snapshot()["rounds_done"] == 4
+    c = make_engine(cfg, make_shards(tiny_clients), "hybrid", "avg")
+    with pytest.raises(ValueError):
+        c.load_checkpoint(path)
+
+
+def test_fit_resumes_from_periodic_checkpoints(tiny_clients, tmp_path):
+    """--checkpoint_every / --resume: an interrupted fit() continued by a new process ends where the uninterrupted one does."""
+    kw = dict(epoch=1, num_rounds=4, global_patience=10, checkpoint_every=1, save_client_models=False, write_latents=False)
+    full = make_engine(make_cfg(tmp_path / "full", **kw), make_shards(tiny_clients), "hybrid", "mse_avg")
+    want = full.fit()
+    cfg2 = make_cfg(tmp_path / "cut", **dict(kw, num_rounds=2))
+    first = make_engine(cfg2, make_shards(tiny_clients), "hybrid", "mse_avg")
+    first.fit()                                                     # "crashes" after two of four rounds
+    cfg3 = make_cfg(tmp_path / "cut", **dict(kw, resume=True))
+    second = make_engine(cfg3, make_shards(tiny_clients), "hybrid", "mse_avg", seed=5)
+    got = second.fit()
+    assert len(got) == 2 and [r.round for r in got] == [2, 3] if hasattr(got[0], "round") else len(got) == 2
+    assert got[-1].client_metrics == want[-1].client_metrics and got[-1].aggregator == want[-1].aggregator
+    assert torch.equal(second.state.params, full.state.params)
