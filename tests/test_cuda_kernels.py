@@ -437,3 +437,18 @@ def test_staged_upload_swaps_shards_and_refreshes_residuals(tiny_clients, tmp_pa
         x = eng.sh.train.x
         hi = (x.view(torch.int32) & -8192).view(torch.float32)
         assert torch.equal(lo, x - hi)
+
+
+def test_checkpoint_file_resumes_identically_on_the_device(tiny_clients, tmp_path, dev):
+    """save_checkpoint / load_checkpoint with the CUDA backend: device-resident state round-trips through the file."""
+    cfg = make_cfg(tmp_path, epoch=1, score_precision="fp16x3")
+    a = make_engine(cfg, make_shards(tiny_clients, dev), "hybrid", "mse_avg", "cuda")
+    a.run_round(0)
+    path = a.save_checkpoint(str(tmp_path / "engine.pt"))
+    ra = [a.run_round(r) for r in (1, 2)]
+    b = make_engine(cfg, make_shards(tiny_clients, dev), "hybrid", "mse_avg", "cuda", seed=31)
+    assert b.load_checkpoint(path) == 1
+    rb = [b.run_round(r) for r in (1, 2)]
+    for x, y in zip(ra, rb):
+        assert (x.selected, x.aggregator, x.client_metrics) == (y.selected, y.aggregator, y.client_metrics)
+    assert torch.equal(a.state.params, b.state.params) and torch.equal(a.state.adam_v, b.state.adam_v)
