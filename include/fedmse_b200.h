@@ -159,14 +159,14 @@ typedef struct FmMultiScoreArgs {
 int fm_score_multi_tc(const FmMultiScoreArgs* args, void* stream);
 
 /* ---- MSE-weight scoring, second generation: every layer on tcgen05 with fp16 hi/lo operands ------------
- * Same job as fm_score_multi_tc (reference: fed_mse_avg, client_trainer.py:115-130) but (1) fp16 head + fp16
- * remainder operands, three products per GEMM, fp32 accumulation (kind::f16, twice the TF32 rate; relative error
- * ~1e-6 like 3xTF32; operands are clamped to +-65504 first, so data beyond ~1.3e5 in magnitude loses accuracy --
- * callers with such data use fm_score_multi_tc); (2) the 27->7->27 bottleneck as one fused 27x27 GEMM
- * (W32 = W3 W2, no activation between the two inner layers) and all biases folded into the GEMMs;
- * (3) out_mse[slot] = mean squared error of the slot's model over all x_rows x 115 elements is finished in the
- * kernel (per-(model, tile) partial sums reduced in a fixed order behind a grid-wide barrier): no SSE matrix,
- * no fm_chunk_mean.  Slots owned by other ranks are left untouched.
+ * Same job as fm_score_multi_tc (reference: fed_mse_avg, client_trainer.py:115-130) but (1) x and the weights as
+ * an fp16 head + fp16 remainder (three products in layer 1), the hidden activations as one fp16 (two products in the
+ * other GEMMs), fp32 accumulation (kind::f16, twice the TF32 rate; measured ~1e-7 relative on the MSE; operands are
+ * clamped to +-65504 first, so data beyond ~1.3e5 in magnitude loses accuracy -- callers with such data use
+ * fm_score_multi_tc); (2) the 27->7->27 bottleneck as one fused 27x27 GEMM (W32 = W3 W2, no activation between the
+ * two inner layers) and all biases folded into the GEMMs; (3) out_mse[slot] = mean squared error of the slot's model
+ * over all x_rows x 115 elements is finished in the kernel (per-thread running sums, added in a fixed order behind a
+ * grid-wide barrier): no SSE matrix, no fm_chunk_mean.  Slots owned by other ranks are left untouched.
  * Scratch (caller): images >= owned * FM_TC_IMAGE_BYTES bytes, owned_slots[n_slots], n_owned[1],
  * partial[fm_score_fused_scratch_floats(x_rows, owned)] floats, grid_barrier[2] uint32 zeroed once. */
 typedef struct FmFusedScoreArgs {
