@@ -219,6 +219,80 @@ void run_poll(long long* out, int n_poll, int use_test_wait) {
            use_test_wait ? "test_wait" : "try_wait");
 }
 
+// Does a second issuing thread that works in "issue a small group, commit, wait for it" round trips slow down a thread that
+// streams MMAs back to back?  Warp 1: RX MMAs (N = 32) in one stream, timed.  Warps 2..1+n_y: groups of KY MMAs + commit +
+// spin on their own barrier, each into its own accumulator, until the stream has finished.
+constexpr int RX = 4096;
+template <int KY>
+__global__ void __launch_bounds__(256, 1) probe_two_issuers(long long* out, int n_y) {
+    extern __shared__ __align__(1024) unsigned char smem_dyn[];
+    PSmem& S = *reinterpret_cast<PSmem*>(smem_dyn);
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    volatile int* stop = reinterpret_cast<volatile int*>(&S.tmem_base + 1);
+    for (int i = tid; i < (int)sizeof(PSmem) / 4; i += 256) reinterpret_cast<uint32_t*>(smem_dyn)[i] = 0u;
+    __syncthreads();
+    if (tid == 0) { mbar_init(&S.bar, 1); for (int i = 0; i < 6; ++i) mbar_init(&S.full[i], 1); fence_mbar_init(); }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)), "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = S.tmem_base;
+    constexpr uint32_t idesc = idesc_f16(128, 32);
+    const uint64_t db = smem_desc_sw128(S.b);
+    if (warp == 1) {
+        if (elect_one()) {
+            const long long t0 = clock64();
+#pragma unroll 8
+            for (int i = 0; i < RX; ++i) mma_ts_f16(tmem + (uint32_t)((i & 8) ? 32 : 0), tmem + 480, db + (uint64_t)(((i & 3) * 32) >> 4), idesc, 1u);
+            tc_commit(&S.bar);
+            mbar_wait(&S.bar, 0);
+            out[0] = clock64() - t0;
+            *stop = 1;
+        }
+        __syncwarp();
+    } else if (warp >= 2 && warp < 2 + n_y) {
+        if (elect_one()) {
+            uint32_t ph = 0;
+            long long groups = 0;
+            const uint32_t d = tmem + 64 + 32 * (uint32_t)(warp - 2);
+            while (*stop == 0) {
+#pragma unroll
+                for (int i = 0; i < KY; ++i) mma_ts_f16(d, tmem + 488, db + (uint64_t)(((i & 3) * 32) >> 4), idesc, 1u);
+                tc_commit(&S.full[warp - 2]);
+                mbar_wait(&S.full[warp - 2], ph);
+                ph ^= 1u;
+                ++groups;
+            }
+            out[1 + (warp - 2)] = groups;
+        }
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
+}
+
+template <int KY>
+void run_two(long long* out, int n_y) {
+    cudaFuncSetAttribute(probe_two_issuers<KY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem) + 1024);
+    cudaMemset(out, 0, 8 * sizeof(long long));
+    probe_two_issuers<KY><<<1, 256, sizeof(PSmem) + 1024>>>(out, n_y);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { printf("error: %s\n", cudaGetErrorString(e)); exit(1); }
+    long long h[8];
+    cudaMemcpy(h, out, sizeof(h), cudaMemcpyDeviceToHost);
+    long long g = 0;
+    for (int i = 0; i < n_y; ++i) g += h[1 + i];
+    const double others = (double)g * KY * 16.4;
+    printf("  stream of %d MMAs next to %d round-trip issuer(s) of %d MMAs: %7lld cycles = %5.1f per streamed MMA; the others ran %lld "
+           "groups (%.0f cycles of MMA work): sum of all MMA work %.0f %% of the time\n", RX, n_y, KY, h[0], (double)h[0] / RX, g, others,
+           100.0 * (RX * 16.4 + others) / (double)h[0]);
+}
+
 template <int NWP, int MODE>
 void run_protocol(long long* out, const unsigned char* gimg, const char* what) {
     cudaFuncSetAttribute(probe_protocol<NWP, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PSmem) + 1024);
@@ -361,6 +435,11 @@ int main(int argc, char** argv) {
     cudaMalloc(&gimg, 62 * 36864);
     cudaMemset(gimg, 0, 62 * 36864);
     printf("layer-1 protocol (group = 24 MMAs N=32 + 2 commits; 16 KB image per group through a ring):\n");
+    if (which == 8) {
+        run_two<4>(out, 0); run_two<4>(out, 1); run_two<4>(out, 2); run_two<4>(out, 4);
+        run_two<24>(out, 1); run_two<24>(out, 2);
+        return 0;
+    }
     if (which == 7) {
         for (int tw = 0; tw < 2; ++tw)
             for (int np : {0, 4, 8, 12}) { run_poll<4>(out, np, tw); }
